@@ -1,0 +1,94 @@
+// C-ABI: peft_gemm_bf16 — host launcher of the tcgen05/TMA GEMM (gemm_sm100.cuh).
+#include "common.cuh"
+#include "gemm_sm100.cuh"
+
+namespace peft {
+
+template <int BN, int EPI>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, EPI>;
+  static bool configured = false;  // per (BN,EPI) instantiation
+  if (!configured) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
+  const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, p);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BN>
+static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t s) {
+  switch (epi) {
+    case EPI_STORE: return launch_gemm<BN, EPI_STORE>(ta, tb, p, s);
+    case EPI_GELU: return launch_gemm<BN, EPI_GELU>(ta, tb, p, s);
+    case EPI_QUICKGELU: return launch_gemm<BN, EPI_QUICKGELU>(ta, tb, p, s);
+    case EPI_RESID_F32: return launch_gemm<BN, EPI_RESID_F32>(ta, tb, p, s);
+    case EPI_DGELU: return launch_gemm<BN, EPI_DGELU>(ta, tb, p, s);
+    case EPI_DQUICKGELU: return launch_gemm<BN, EPI_DQUICKGELU>(ta, tb, p, s);
+    case EPI_STORE_F32: return launch_gemm<BN, EPI_STORE_F32>(ta, tb, p, s);
+    case EPI_RELU: return launch_gemm<BN, EPI_RELU>(ta, tb, p, s);
+    case EPI_DRELU: return launch_gemm<BN, EPI_DRELU>(ta, tb, p, s);
+    case EPI_GELU_TANH: return launch_gemm<BN, EPI_GELU_TANH>(ta, tb, p, s);
+    case EPI_DGELU_TANH: return launch_gemm<BN, EPI_DGELU_TANH>(ta, tb, p, s);
+    case EPI_RESID_BF16: return launch_gemm<BN, EPI_RESID_BF16>(ta, tb, p, s);
+    default: return fail(PEFT_ERR_INVALID, "unknown epilogue %d", epi);
+  }
+}
+
+// Tile-width heuristic: widest tile that still gives >= ~2 waves over the SMs; narrow outputs get BN=32.
+static int pick_bn(int M, int N) {
+  if (N <= 64) return 32;
+  const long long mt = (M + kBM - 1) / kBM;
+  const long long t256 = mt * ((N + 255) / 256);
+  if (N % 256 == 0 && t256 >= 2LL * sm_count()) return 256;
+  return 128;
+}
+
+}  // namespace peft
+
+using namespace peft;
+
+extern "C" int peft_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
+                              const float* bias, void* out, long long ldo, void* out2, long long ldo2,
+                              const void* aux, long long ldaux, int epilogue, void* stream) {
+  PEFT_REQUIRE(M > 0 && N > 0 && K > 0, "peft_gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
+  PEFT_REQUIRE(a && b && out, "peft_gemm_bf16: null operand");
+  PEFT_REQUIRE(K % 8 == 0, "peft_gemm_bf16: K must be a multiple of 8 (got %d)", K);
+  PEFT_REQUIRE(lda >= K && ldb >= K, "peft_gemm_bf16: pitch smaller than K");
+  const bool f32out = (epilogue == EPI_RESID_F32 || epilogue == EPI_STORE_F32);
+  const int oelt = f32out ? 4 : 2;
+  PEFT_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (ldo * oelt) % 16 == 0,
+               "peft_gemm_bf16: out must be 16-byte aligned with a 16-byte-multiple pitch");
+  const bool needs_out2 = (epilogue == EPI_GELU || epilogue == EPI_QUICKGELU || epilogue == EPI_GELU_TANH);
+  if (needs_out2)
+    PEFT_REQUIRE(out2 && (reinterpret_cast<uintptr_t>(out2) & 15) == 0 && (ldo2 * 2) % 16 == 0,
+                 "peft_gemm_bf16: activation epilogue needs an aligned out2");
+  const bool needs_aux = (epilogue == EPI_RESID_F32 || epilogue == EPI_DGELU || epilogue == EPI_DQUICKGELU ||
+                          epilogue == EPI_DRELU || epilogue == EPI_DGELU_TANH || epilogue == EPI_RESID_BF16);
+  if (needs_aux) {
+    const int aelt = (epilogue == EPI_RESID_F32) ? 4 : 2;
+    PEFT_REQUIRE(aux && (reinterpret_cast<uintptr_t>(aux) & 15) == 0 && (ldaux * aelt) % 16 == 0,
+                 "peft_gemm_bf16: epilogue %d needs an aligned aux operand", epilogue);
+  }
+  if (bias) PEFT_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "peft_gemm_bf16: bias must be 16-byte aligned");
+
+  const int bn = pick_bn(M, N);
+  CUtensorMap ta, tb;
+  int rc = make_tmap_bf16_2d(&ta, a, (unsigned long long)M, (unsigned long long)K, (unsigned long long)lda, kBM);
+  if (rc) return rc;
+  rc = make_tmap_bf16_2d(&tb, b, (unsigned long long)N, (unsigned long long)K, (unsigned long long)ldb, (unsigned)bn);
+  if (rc) return rc;
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
+  p.aux = aux; p.ldaux = ldaux;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  switch (bn) {
+    case 256: return dispatch_epi<256>(epilogue, ta, tb, p, s);
+    case 128: return dispatch_epi<128>(epilogue, ta, tb, p, s);
+    default: return dispatch_epi<32>(epilogue, ta, tb, p, s);
+  }
+}

@@ -1,0 +1,95 @@
+// Host-side helpers shared by the C-ABI translation units: thread-local error string, launch counter,
+// CUDA error checks, cached device properties and the cuTensorMapEncodeTiled entry point (resolved at run time
+// through cudart so that the library has no link-time dependency on libcuda and can be dlopen'ed on a CPU box).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include "../../include/peft_b200.h"
+
+namespace peft {
+
+inline char* tls_error() {
+  static thread_local char buf[512] = {0};
+  return buf;
+}
+inline int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(tls_error(), 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+inline std::atomic<unsigned long long>& launch_counter() {
+  static std::atomic<unsigned long long> c{0};
+  return c;
+}
+
+#define PEFT_CUDA_CHECK(expr)                                                                         \
+  do {                                                                                                \
+    cudaError_t _e = (expr);                                                                          \
+    if (_e != cudaSuccess)                                                                            \
+      return ::peft::fail(PEFT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define PEFT_LAUNCH_CHECK()                                                                           \
+  do {                                                                                                \
+    ::peft::launch_counter().fetch_add(1, std::memory_order_relaxed);                                 \
+    cudaError_t _e = cudaGetLastError();                                                              \
+    if (_e != cudaSuccess)                                                                            \
+      return ::peft::fail(PEFT_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define PEFT_REQUIRE(cond, ...)                                   \
+  do {                                                            \
+    if (!(cond)) return ::peft::fail(PEFT_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+inline int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, cols] with row pitch ld (elements); box = box_rows x 64 columns, 128-byte swizzle.
+// Coordinates outside [rows, cols] are zero-filled by the hardware, which is what handles every M/N/K tail.
+inline int make_tmap_bf16_2d(CUtensorMap* tm, const void* ptr, unsigned long long rows, unsigned long long cols,
+                             unsigned long long ld, unsigned box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail(PEFT_ERR_INVALID, "TMA base pointer must be 16-byte aligned");
+  if ((ld * 2) % 16 != 0) return fail(PEFT_ERR_INVALID, "TMA row pitch must be a multiple of 16 bytes (ld=%llu)", ld);
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+}  // namespace peft
