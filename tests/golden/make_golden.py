@@ -1,0 +1,239 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.pt from the UNMODIFIED reference modules (run in the build container only).
+
+    python tests/golden/make_golden.py            # needs /root/reference, writes next to this file
+
+The reference cannot travel to the GPU box, so its outputs are frozen here as small fixtures.  Weights and inputs
+are NOT stored: they are re-created from seeds by oracle/synth.py (deterministic torch CPU generators), only the
+reference's outputs (features, logits, loss, adapter gradients) are saved.
+
+Import recipe — none of it touches reference files:
+  * single-file import through importlib (bypasses evaluation/__init__.py, which needs vision_datasets / nltk);
+  * torch._C._add_docstr made tolerant (model.py re-docstrings torch._C._nn.linear, which torch 2.x rejects);
+  * stub `timm.models.layers` (DropPath = identity at rate 0, trunc_normal_) and stub parent packages for the
+    relative imports of the timm-dialect files.
+Deviations from the committed reference state that the harness applies:
+  * Q4: KAdaptation Attention hard-codes phm_dim=768 and never initialises phm_rule; after construction we replace
+    phm_rule / W_left* / W_right* with phm_dim=4 tensors from oracle/synth.py (forward code is generic in n);
+  * Q5: Compacter phm_rule tensors are uninitialised in the reference; they are loaded from synth;
+  * the per-block print/logging of the Houlsby / Compacter blocks is silenced.
+"""
+import contextlib
+import importlib.util
+import io
+import logging
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = os.environ.get("PEFT_REFERENCE", "/root/reference")
+FS = os.path.join(REF, "few_shot/vision_benchmark/evaluation")
+FL = os.path.join(REF, "full_shot/main")
+
+from oracle import synth  # noqa: E402
+from oracle.synth import VitCfg  # noqa: E402
+
+
+def _install_shims():
+    import transformers.activations  # noqa: F401  (must be imported before the timm stub exists)
+    orig = torch._C._add_docstr
+
+    def tolerant(obj, doc):
+        try:
+            return orig(obj, doc)
+        except RuntimeError:
+            return obj
+
+    torch._C._add_docstr = tolerant
+    if "timm" not in sys.modules:
+        timm = types.ModuleType("timm")
+        models = types.ModuleType("timm.models")
+        layers = types.ModuleType("timm.models.layers")
+
+        class DropPath(nn.Module):
+            def __init__(self, p=0.0):
+                super().__init__()
+                assert p == 0.0
+
+            def forward(self, x):
+                return x
+
+        layers.DropPath = DropPath
+        layers.trunc_normal_ = torch.nn.init.trunc_normal_
+        timm.models = models
+        models.layers = layers
+        sys.modules.update({"timm": timm, "timm.models": models, "timm.models.layers": layers})
+    # parent packages for `from .feature import ...`, `from ..optim import ...`, `from ..evaluation.metric import ...`
+    for name in ("vb", "vb.evaluation", "vb.optim", "vb.evaluation.feature", "vb.evaluation.metric", "vb.common",
+                 "vb.common.constants", "vb.config", "vb.datasets", "vb.evaluation.dataset"):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            m.__path__ = []
+            sys.modules[name] = m
+
+    class _Any:
+        def __getattr__(self, k):
+            return _Any()
+
+        def __call__(self, *a, **k):
+            return _Any()
+
+    for name in ("vb.evaluation.feature", "vb.optim", "vb.evaluation.metric", "vb.common.constants", "vb.config",
+                 "vb.datasets", "vb.evaluation.dataset"):
+        mod = sys.modules[name]
+        mod.__getattr__ = lambda k, _A=_Any: _A()  # any imported symbol resolves to a dummy
+
+
+def load_ref(path, modname, package=None):
+    spec = importlib.util.spec_from_file_location(modname, path, submodule_search_locations=None)
+    mod = importlib.util.module_from_spec(spec)
+    if package:
+        mod.__package__ = package
+    sys.modules[modname] = mod
+    with contextlib.redirect_stdout(io.StringIO()):
+        spec.loader.exec_module(mod)
+    return mod
+
+
+def _set_params(module, sd):
+    """Copy synth tensors into a reference module, replacing parameters whose shape differs (Q4)."""
+    own = dict(module.named_parameters())
+    missing = []
+    for k, v in sd.items():
+        if k not in own:
+            missing.append(k)
+            continue
+        if own[k].shape != v.shape:
+            parent = module
+            parts = k.split(".")
+            for p in parts[:-1]:
+                parent = getattr(parent, p)
+            setattr(parent, parts[-1], nn.Parameter(v.clone()))
+        else:
+            with torch.no_grad():
+                own[k].copy_(v)
+    return missing
+
+
+def _head_step(feat, head, labels):
+    mean = feat.mean(0, keepdim=True)
+    bn = nn.BatchNorm1d(feat.shape[1], affine=False)
+    bn.train()
+    logits = F.linear(bn(feat), head["layers.0.weight"], head["layers.0.bias"])
+    loss = F.cross_entropy(logits, labels)
+    return logits, loss
+
+
+def run_model_case(name, ref_model, cfg, batch, out):
+    sd = synth.make_state_dict(cfg, seed=0, grad_test=True)
+    head = synth.make_head(cfg)
+    for v in head.values():
+        v.requires_grad_(True)
+    images, labels = synth.make_batch(cfg, batch)
+    missing = _set_params(ref_model, sd)
+    assert not missing, f"{name}: synth keys missing in reference module: {missing[:5]}"
+    names = synth.trainable_names(cfg, sd)
+    params = dict(ref_model.named_parameters())
+    for k, p in params.items():
+        p.requires_grad_(k in names)
+    ref_model.train()
+    with contextlib.redirect_stdout(io.StringIO()):
+        feat = ref_model(images)
+    logits, loss = _head_step(feat, head, labels)
+    loss.backward()
+    res = {
+        "cfg": cfg.__dict__.copy(), "batch": batch,
+        "feature": feat.detach().clone(), "logits": logits.detach().clone(), "loss": loss.detach().clone(),
+        "grads": {k: params[k].grad.detach().clone() for k in names},
+        "head_grads": {k: v.grad.detach().clone() for k, v in head.items()},
+    }
+    out[name] = res
+    gn = sum(float(g.norm()) for g in res["grads"].values())
+    print(f"[golden] {name}: loss={float(loss):.6f} |feat|={float(feat.norm()):.4f} sum|grad|={gn:.4e} trainables={len(names)}")
+
+
+def main():
+    logging.disable(logging.CRITICAL)
+    torch.manual_seed(0)
+    np.random.seed(0)
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    _install_shims()
+    out = {}
+
+    # ------------------------------------------------------------------ timm dialect
+    kad = load_ref(os.path.join(FS, "kadaptation.py"), "vb.evaluation.kadaptation", "vb.evaluation")
+    lora = load_ref(os.path.join(FS, "lora.py"), "vb.evaluation.lora", "vb.evaluation")
+    adp = load_ref(os.path.join(FS, "adapter.py"), "vb.evaluation.adapter", "vb.evaluation")
+    from functools import partial
+
+    # function-level: matvec_product with n=4 and n=8, rank 2
+    g = torch.Generator().manual_seed(11)
+    for n, rk in ((4, 1), (8, 2)):
+        x = torch.randn(6, 768, generator=g)
+        rule = torch.randn(n, n, n, generator=g) * 0.3
+        Wl = torch.randn(n, 768 // n, rk, generator=g) * 0.3
+        Wr = torch.randn(n, rk, 768 // n, generator=g) * 0.3
+        y = kad.matvec_product(torch.bmm(Wl, Wr), x, None, rule)
+        out[f"matvec_n{n}_r{rk}"] = {"x": x, "rule": rule, "W_left": Wl, "W_right": Wr, "y": y}
+
+    small = dict(img=64, patch=32, width=768, depth=2, heads=12)
+    vit_kw = dict(img_size=64, patch_size=32, num_classes=10, embed_dim=768, depth=2, num_heads=12, mlp_ratio=4.0,
+                  qkv_bias=True, norm_layer=partial(nn.LayerNorm, eps=1e-6))
+    cfg = VitCfg(dialect="timm", adapter="kron", phm_dim=4, **small)
+    run_model_case("timm_kron_n4", kad.VisionTransformer(**vit_kw), cfg, 4, out)
+    cfg = VitCfg(dialect="timm", adapter="kron", phm_dim=8, phm_rank=2, **small)
+    run_model_case("timm_kron_n8_r2", kad.VisionTransformer(**vit_kw), cfg, 3, out)
+    cfg = VitCfg(dialect="timm", adapter="lora", **small)
+    run_model_case("timm_lora", lora.VisionTransformer(**vit_kw), cfg, 4, out)
+    cfg = VitCfg(dialect="timm", adapter="houlsby", **small)
+    run_model_case("timm_houlsby", adp.VisionTransformer(**vit_kw), cfg, 4, out)
+
+    # ------------------------------------------------------------------ CLIP dialect
+    clip_lora = load_ref(os.path.join(FS, "model.py"), "ref_clip_model")
+    clip_lora2 = load_ref(os.path.join(FS, "lora_model.py"), "ref_clip_lora_model")
+    clip_adp = load_ref(os.path.join(FS, "adapter_model.py"), "ref_clip_adapter_model")
+    clip_cmp = load_ref(os.path.join(FS, "compacter_model.py"), "ref_clip_compacter_model")
+    clip_kw = dict(input_resolution=64, patch_size=32, width=768, layers=2, heads=12, output_dim=512)
+    cfg = VitCfg(dialect="clip", adapter="lora", **small)
+    run_model_case("clip_lora_modelpy", clip_lora.VisionTransformer(**clip_kw), cfg, 4, out)
+    run_model_case("clip_lora_lorapy", clip_lora2.VisionTransformer(**clip_kw), cfg, 4, out)
+    run_model_case("clip_lora_b3", clip_lora.VisionTransformer(**clip_kw), cfg, 3, out)
+    cfg = VitCfg(dialect="clip", adapter="houlsby", **small)
+    run_model_case("clip_houlsby", clip_adp.VisionTransformer(**clip_kw), cfg, 4, out)
+    cfg = VitCfg(dialect="clip", adapter="compacter", **small)
+    run_model_case("clip_compacter", clip_cmp.VisionTransformer(**clip_kw), cfg, 4, out)
+
+    # ------------------------------------------------------------------ Fastfood
+    ff = load_ref(os.path.join(FL, "intrinsic/fastfood.py"), "ref_fastfood")
+    g = torch.Generator().manual_seed(5)
+    for n in (8, 1024, 4096):
+        x = torch.randn(n, generator=g)
+        out[f"fwht_{n}"] = {"x": x, "y": ff.fast_walsh_hadamard_torched(x, 0, normalize=False)}
+    for DD, d in ((1000, 16), (5000, 100), (20000, 1000)):
+        LL = 2 ** int(np.ceil(np.log(DD) / np.log(2)))
+        BB = (torch.rand(LL, generator=g) * 2).long().float() * 2 - 1
+        Pi = torch.from_numpy(np.random.RandomState(DD).permutation(LL)).long()
+        GG = torch.randn(LL, generator=g)
+        divisor = torch.sqrt(LL * torch.sum(GG ** 2))
+        V = torch.randn(d, generator=g, requires_grad=True)
+        ray = ff.fastfood_torched(V, DD, [BB, Pi, GG, divisor, LL], device="cpu")
+        w = torch.randn(DD, generator=g)
+        (ray * w).sum().backward()
+        out[f"fastfood_{DD}_{d}"] = {"V": V.detach().clone(), "BB": BB, "Pi": Pi, "GG": GG, "divisor": divisor, "LL": LL,
+                                     "DD": DD, "ray": ray.detach().clone(), "w": w, "dV": V.grad.detach().clone()}
+
+    path = os.path.join(HERE, "reference_outputs.pt")
+    torch.save(out, path)
+    print(f"[golden] wrote {path} ({os.path.getsize(path) / 1e6:.2f} MB), {len(out)} cases")
+
+
+if __name__ == "__main__":
+    main()
