@@ -53,6 +53,44 @@ int peft_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, i
                    const float* bias, void* out, long long ldo, void* out2, long long ldo2,
                    const void* aux, long long ldaux, int epilogue, void* stream);
 
+/* LayerNorm over the last dimension, one warp per token row, D % 128 == 0.
+ * replaces: nn.LayerNorm / CLIP LayerNorm forward — FS/kadaptation.py:274-276,538 (eps 1e-6), FS/model.py:156-162,1156-1157,1208,1214 (eps 1e-5).
+ * x: fp32 (x_is_bf16=0) or bf16 rows of pitch ldx; y: bf16 GEMM operand (y_is_f32=0) or fp32; mean/rstd: fp32 [M] or NULL. */
+int peft_layernorm_fwd(const void* x, long long ldx, int x_is_bf16, const float* gamma, const float* beta,
+                       void* y, long long ldy, int y_is_f32, float* mean, float* rstd, int M, int D, float eps,
+                       void* stream);
+/* g_out(bf16) = (g_in ? g_in : 0) + dLN/dx(dy); optional dgamma/dbeta accumulation (fp32 atomics, caller zeroes them).
+ * replaces: the autograd backward of the LayerNorms above, fused with the residual-gradient add of Block.forward
+ * (FS/kadaptation.py:273-277, FS/model.py:1155-1158). */
+int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32, const void* x, long long ldx, int x_is_bf16,
+                       const float* mean, const float* rstd, const float* gamma, const void* g_in, long long ldgi,
+                       void* g_out, long long ldgo, float* dgamma, float* dbeta, int M, int D, void* stream);
+
+/* softmax(q k^T * scale) v for every (batch, head), head_dim 64, reading the packed projection buffer
+ * qkv[B*L, >=3*H*64] (q | k | v column blocks, token row = b*L + l) and writing o[B*L, H*64]; lse2[B*H*L] receives
+ * rowmax*scale*log2e + log2(rowsum) for the backward.
+ * replaces: FS/kadaptation.py:202-205,223-235 and FS/model.py:907-918,990-1002 (head split, bmm, softmax, bmm, merge). */
+int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, long long ldo, float* lse2, int B, int H, int L,
+                       float scale, void* stream);
+/* dqkv[B*L, >=3*H*64] (dq | dk | dv) from d_o; delta[B*H*L] is scratch.  replaces: autograd of the above. */
+int peft_attention_bwd(const void* qkv, long long ldqkv, const void* o, long long ldo, const void* d_o, long long lddo,
+                       const float* lse2, float* delta, void* dqkv, long long lddqkv, int B, int H, int L, float scale,
+                       void* stream);
+
+/* images fp32 [B,3,img,img] -> bf16 patch rows [B*(img/patch)^2, 3*patch*patch] (the unfold half of the stride=kernel
+ * conv of FS/model.py:1203 / FS/kadaptation.py:300-307; the GEMM half is peft_gemm_bf16). */
+int peft_im2col_patches(const float* images, void* patches, int B, int img, int patch, void* stream);
+/* x fp32 [B,L,D]: row 0 = cls + pos[0], row 1+t = patch_embed[b*(L-1)+t] + pos[1+t]
+ * replaces: FS/kadaptation.py:524-529, FS/model.py:1206-1207. */
+int peft_assemble_tokens(const void* patch_embed, const float* cls, const float* pos, float* x, int B, int L, int D,
+                         void* stream);
+
+/* out[I, J] (fp32, pitch ldout) += sum_m x[m, i] * y[m, j]; I in {16,32,64}, J % 64 == 0.  The adapter-gradient
+ * reductions over all tokens: replaces the autograd dW of the LoRA / Kronecker / Houlsby / Compacter factors
+ * (FS/model.py:754-762, FS/kadaptation.py:81-115,211-219, FS/adapter_model.py:265-267). */
+int peft_tn_reduce(const void* x, long long ldx, int I, const void* y, long long ldy, int J, float* out,
+                   long long ldout, int M, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

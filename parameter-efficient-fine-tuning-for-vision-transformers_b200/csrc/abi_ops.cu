@@ -1,0 +1,188 @@
+// C-ABI: LayerNorm, attention, patch-embedding helpers and the skinny adapter-gradient reductions.
+#include "common.cuh"
+#include "ln_sm100.cuh"
+#include "attention_sm100.cuh"
+#include "reduce_sm100.cuh"
+
+using namespace peft;
+
+namespace {
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+inline int ln_grid(int M) {
+  const int blocks = (M + 7) / 8;
+  const int cap = sm_count() * 8;
+  return blocks < cap ? (blocks > 0 ? blocks : 1) : cap;
+}
+}  // namespace
+
+#define LN_DISPATCH_NV(NVVAL, ...)                         \
+  switch (NVVAL) {                                         \
+    case 1: { constexpr int NV = 1; __VA_ARGS__; break; }  \
+    case 2: { constexpr int NV = 2; __VA_ARGS__; break; }  \
+    case 3: { constexpr int NV = 3; __VA_ARGS__; break; }  \
+    case 4: { constexpr int NV = 4; __VA_ARGS__; break; }  \
+    case 6: { constexpr int NV = 6; __VA_ARGS__; break; }  \
+    case 8: { constexpr int NV = 8; __VA_ARGS__; break; }  \
+    case 10: { constexpr int NV = 10; __VA_ARGS__; break; } \
+    default: return fail(PEFT_ERR_UNSUPPORTED, "LayerNorm width %d unsupported (need D/128 in {1,2,3,4,6,8,10})", (NVVAL) * 128); \
+  }
+
+extern "C" int peft_layernorm_fwd(const void* x, long long ldx, int x_is_bf16, const float* gamma, const float* beta,
+                                  void* y, long long ldy, int y_is_f32, float* mean, float* rstd, int M, int D,
+                                  float eps, void* stream) {
+  PEFT_REQUIRE(M > 0 && D > 0 && D % 128 == 0, "peft_layernorm_fwd: bad shape M=%d D=%d", M, D);
+  PEFT_REQUIRE(aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta), "peft_layernorm_fwd: unaligned pointer");
+  PEFT_REQUIRE(ldx % 4 == 0 && ldy % 4 == 0, "peft_layernorm_fwd: pitches must be multiples of 4 elements");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = ln_grid(M);
+  LN_DISPATCH_NV(D / 128, {
+    if (!x_is_bf16 && !y_is_f32)
+      ln_fwd_kernel<NV, float, __nv_bfloat16><<<grid, 256, 0, s>>>((const float*)x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps);
+    else if (!x_is_bf16 && y_is_f32)
+      ln_fwd_kernel<NV, float, float><<<grid, 256, 0, s>>>((const float*)x, ldx, gamma, beta, (float*)y, ldy, mean, rstd, M, eps);
+    else if (x_is_bf16 && !y_is_f32)
+      ln_fwd_kernel<NV, __nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps);
+    else
+      ln_fwd_kernel<NV, __nv_bfloat16, float><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, ldx, gamma, beta, (float*)y, ldy, mean, rstd, M, eps);
+  });
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32, const void* x, long long ldx,
+                                  int x_is_bf16, const float* mean, const float* rstd, const float* gamma,
+                                  const void* g_in, long long ldgi, void* g_out, long long ldgo, float* dgamma,
+                                  float* dbeta, int M, int D, void* stream) {
+  PEFT_REQUIRE(M > 0 && D > 0 && D % 128 == 0, "peft_layernorm_bwd: bad shape M=%d D=%d", M, D);
+  PEFT_REQUIRE(aligned16(dy) && aligned16(x) && aligned16(g_out) && aligned16(gamma) && (g_in == nullptr || aligned16(g_in)),
+               "peft_layernorm_bwd: unaligned pointer");
+  PEFT_REQUIRE(lddy % 4 == 0 && ldx % 4 == 0 && ldgo % 4 == 0 && ldgi % 4 == 0, "peft_layernorm_bwd: pitches must be multiples of 4");
+  PEFT_REQUIRE((dgamma == nullptr) == (dbeta == nullptr), "peft_layernorm_bwd: dgamma and dbeta go together");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = ln_grid(M);
+  const bool pg = dgamma != nullptr;
+  using bf = __nv_bfloat16;
+#define LN_BWD_LAUNCH(DYT, XT, PG) \
+  ln_bwd_kernel<NV, DYT, XT, bf, PG><<<grid, 256, 0, s>>>((const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, (const bf*)g_in, ldgi, (bf*)g_out, ldgo, dgamma, dbeta, M)
+  LN_DISPATCH_NV(D / 128, {
+    if (dy_is_f32) {
+      if (x_is_bf16) { if (pg) LN_BWD_LAUNCH(float, bf, true); else LN_BWD_LAUNCH(float, bf, false); }
+      else { if (pg) LN_BWD_LAUNCH(float, float, true); else LN_BWD_LAUNCH(float, float, false); }
+    } else {
+      if (x_is_bf16) { if (pg) LN_BWD_LAUNCH(bf, bf, true); else LN_BWD_LAUNCH(bf, bf, false); }
+      else { if (pg) LN_BWD_LAUNCH(bf, float, true); else LN_BWD_LAUNCH(bf, float, false); }
+    }
+  });
+#undef LN_BWD_LAUNCH
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+static int attn_lp(int L) { return ((L + 63) / 64) * 64; }
+
+static int attn_check(const AttnParams& p) {
+  PEFT_REQUIRE(p.B > 0 && p.H > 0 && p.L > 0, "attention: empty problem");
+  PEFT_REQUIRE(p.D == p.H * kHd, "attention: head_dim must be 64 (D=%d, H=%d)", p.D, p.H);
+  PEFT_REQUIRE(p.L <= 512, "attention: L=%d exceeds the single-head-resident limit (512)", p.L);
+  PEFT_REQUIRE(p.ldqkv % 8 == 0 && aligned16(p.qkv), "attention: qkv must be 16-byte aligned with pitch % 8 == 0");
+  return 0;
+}
+
+extern "C" int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, long long ldo, float* lse2, int B, int H,
+                                  int L, float scale, void* stream) {
+  AttnParams p{};
+  p.qkv = (const __nv_bfloat16*)qkv; p.ldqkv = ldqkv; p.o = (__nv_bfloat16*)o; p.ldo = ldo; p.lse2 = lse2;
+  p.B = B; p.H = H; p.L = L; p.D = H * kHd; p.scale = scale;
+  int rc = attn_check(p);
+  if (rc) return rc;
+  PEFT_REQUIRE(o && lse2 && ldo % 8 == 0 && aligned16(o), "peft_attention_fwd: bad output");
+  const int Lp = attn_lp(L);
+  const int smem = (64 + 2 * Lp) * 128;
+  static int configured = 0;
+  if (configured < smem) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = smem;
+  }
+  dim3 grid((L + 63) / 64, B * H);
+  attn_fwd_kernel<<<grid, kAttnThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(p, Lp);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* o, long long ldo, const void* d_o,
+                                  long long lddo, const float* lse2, float* delta, void* dqkv, long long lddqkv, int B,
+                                  int H, int L, float scale, void* stream) {
+  AttnParams p{};
+  p.qkv = (const __nv_bfloat16*)qkv; p.ldqkv = ldqkv; p.o = (__nv_bfloat16*)const_cast<void*>(o); p.ldo = ldo;
+  p.d_o = (const __nv_bfloat16*)d_o; p.lddo = lddo; p.dqkv = (__nv_bfloat16*)dqkv; p.lddqkv = lddqkv;
+  p.lse2 = const_cast<float*>(lse2); p.delta = delta;
+  p.B = B; p.H = H; p.L = L; p.D = H * kHd; p.scale = scale;
+  int rc = attn_check(p);
+  if (rc) return rc;
+  PEFT_REQUIRE(o && d_o && lse2 && delta && dqkv, "peft_attention_bwd: null operand");
+  PEFT_REQUIRE(ldo % 8 == 0 && lddo % 8 == 0 && lddqkv % 8 == 0 && aligned16(o) && aligned16(d_o) && aligned16(dqkv),
+               "peft_attention_bwd: operands must be 16-byte aligned with pitch % 8 == 0");
+  const int Lp = attn_lp(L);
+  const int smem_dq = (128 + 2 * Lp) * 128;
+  const int smem_dkv = (128 + 2 * Lp) * 128 + 2 * Lp * 4;
+  static int conf_dq = 0, conf_dkv = 0;
+  if (conf_dq < smem_dq) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq));
+    conf_dq = smem_dq;
+  }
+  if (conf_dkv < smem_dkv) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv));
+    conf_dkv = smem_dkv;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  dim3 grid((L + 63) / 64, B * H);
+  attn_bwd_dq_kernel<<<grid, kAttnThreads, smem_dq, s>>>(p, Lp);
+  PEFT_LAUNCH_CHECK();
+  attn_bwd_dkv_kernel<<<grid, kAttnThreads, smem_dkv, s>>>(p, Lp);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_im2col_patches(const float* images, void* patches, int B, int img, int patch, void* stream) {
+  PEFT_REQUIRE(B > 0 && img > 0 && patch > 0 && img % patch == 0 && patch % 4 == 0, "peft_im2col_patches: bad shape");
+  PEFT_REQUIRE(aligned16(images) && aligned16(patches), "peft_im2col_patches: unaligned pointer");
+  const long long total = (long long)B * (img / patch) * (img / patch) * 3 * patch * patch / 4;
+  long long blocks = (total + 255) / 256;
+  if (blocks > sm_count() * 16) blocks = sm_count() * 16;
+  im2col_patch_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(images, (__nv_bfloat16*)patches, B, img, patch);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_assemble_tokens(const void* patch_embed, const float* cls, const float* pos, float* x, int B, int L,
+                                    int D, void* stream) {
+  PEFT_REQUIRE(B > 0 && L > 1 && D % 4 == 0, "peft_assemble_tokens: bad shape");
+  PEFT_REQUIRE(aligned16(patch_embed) && aligned16(cls) && aligned16(pos) && aligned16(x), "peft_assemble_tokens: unaligned pointer");
+  const long long total = (long long)B * L * D / 4;
+  long long blocks = (total + 255) / 256;
+  if (blocks > sm_count() * 16) blocks = sm_count() * 16;
+  assemble_tokens_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)patch_embed, cls, pos, x, B, L, D);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_tn_reduce(const void* x, long long ldx, int I, const void* y, long long ldy, int J, float* out,
+                              long long ldout, int M, void* stream) {
+  PEFT_REQUIRE(M > 0 && (I == 16 || I == 32 || I == 64) && J > 0 && J % 64 == 0, "peft_tn_reduce: need I in {16,32,64}, J %% 64 == 0 (I=%d J=%d)", I, J);
+  PEFT_REQUIRE(aligned16(x) && aligned16(y) && ldx % 8 == 0 && ldy % 8 == 0, "peft_tn_reduce: operands must be 16-byte aligned with pitch %% 8 == 0");
+  const int jt = J / 64;
+  int target_ctas = sm_count() * 4;
+  int my = (target_ctas + jt - 1) / jt;
+  int rows = (M + my - 1) / my;
+  rows = ((rows + 63) / 64) * 64;
+  if (rows < 256) rows = 256;
+  my = (M + rows - 1) / rows;
+  dim3 grid(jt, my);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* X = (const __nv_bfloat16*)x; const __nv_bfloat16* Y = (const __nv_bfloat16*)y;
+  if (I == 16) tn_reduce_kernel<1><<<grid, kRedThreads, 0, s>>>(X, ldx, Y, ldy, out, ldout, M, rows);
+  else if (I == 32) tn_reduce_kernel<2><<<grid, kRedThreads, 0, s>>>(X, ldx, Y, ldy, out, ldout, M, rows);
+  else tn_reduce_kernel<4><<<grid, kRedThreads, 0, s>>>(X, ldx, Y, ldy, out, ldout, M, rows);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}

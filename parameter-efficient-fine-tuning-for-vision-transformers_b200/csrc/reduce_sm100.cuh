@@ -1,0 +1,114 @@
+// Skinny "token-reduction" products for the adapter gradients:
+//     Out[I, J] += sum_m X[m, i] * Y[m, j]          I in {16, 32, 64},  J a multiple of 64,  m over all B*L tokens
+// e.g. dUp^T = p^T dC, dDn = dp^T x  (LoRA / Kronecker factors), Houlsby dW_up = z^T dy, dW_down = dz^T LN(h).
+// These are the only weight-gradient products the frozen-backbone step needs; they are HBM-bound (each token row of
+// Y is read once) so the math runs on warp-level mma.sync out of cp.async-staged shared memory and the partial sums of
+// the 4 warps of a CTA are combined in shared memory before one fp32 atomicAdd per output element per CTA.
+#pragma once
+#include "ptx_sm100.cuh"
+
+namespace peft {
+
+constexpr int kRedThreads = 128;
+constexpr int kRedRowsPerStage = 64;   // token rows per pipeline stage (16 per warp)
+
+__device__ __forceinline__ uint32_t sw_off_x(int row, int chunk, int chunks_per_row) {
+  // rows of 32/64/128 bytes: XOR the 16-byte chunk index so 8 consecutive rows hit 8 distinct bank groups
+  if (chunks_per_row == 8) return (uint32_t)(row * 128 + ((chunk ^ (row & 7)) << 4));
+  if (chunks_per_row == 4) return (uint32_t)(row * 64 + ((chunk ^ ((row >> 1) & 3)) << 4));
+  return (uint32_t)(row * 32 + ((chunk ^ ((row >> 2) & 1)) << 4));
+}
+
+template <int IT>  // I = 16 * IT
+__global__ void __launch_bounds__(kRedThreads)
+tn_reduce_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const __nv_bfloat16* __restrict__ Y, long long ldy,
+                 float* __restrict__ out, long long ldout, int M, int rows_per_cta) {
+  constexpr int I = 16 * IT;
+  constexpr int XCH = I / 8;                       // 16-byte chunks per X row
+  constexpr int kXBytes = kRedRowsPerStage * I * 2;
+  constexpr int kYBytes = kRedRowsPerStage * 128;
+  __shared__ __align__(128) uint8_t sX[2][kXBytes];
+  __shared__ __align__(128) uint8_t sY[2][kYBytes];
+  __shared__ float sRed[I * 64];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j0 = blockIdx.x * 64;
+  const long long m_begin = (long long)blockIdx.y * rows_per_cta;
+  long long m_end = m_begin + rows_per_cta;
+  if (m_end > M) m_end = M;
+  const int nstages = (int)((m_end - m_begin + kRedRowsPerStage - 1) / kRedRowsPerStage);
+
+  auto issue = [&](int st, int buf) {
+    const long long r0 = m_begin + (long long)st * kRedRowsPerStage;
+    for (int idx = threadIdx.x; idx < kRedRowsPerStage * XCH; idx += kRedThreads) {
+      const int r = idx / XCH, c = idx % XCH;
+      const bool ok = (r0 + r) < m_end;
+      ptx::cp_async_16(&sX[buf][sw_off_x(r, c, XCH)], X + (ok ? (r0 + r) : 0) * ldx + c * 8, ok);
+    }
+    for (int idx = threadIdx.x; idx < kRedRowsPerStage * 8; idx += kRedThreads) {
+      const int r = idx >> 3, c = idx & 7;
+      const bool ok = (r0 + r) < m_end;
+      ptx::cp_async_16(&sY[buf][sw_off_x(r, c, 8)], Y + (ok ? (r0 + r) : 0) * ldy + j0 + c * 8, ok);
+    }
+    ptx::cp_async_commit();
+  };
+
+  float acc[IT][8][4];
+#pragma unroll
+  for (int a = 0; a < IT; ++a)
+#pragma unroll
+    for (int n = 0; n < 8; ++n) acc[a][n][0] = acc[a][n][1] = acc[a][n][2] = acc[a][n][3] = 0.f;
+
+  if (nstages > 0) issue(0, 0);
+  for (int st = 0; st < nstages; ++st) {
+    const int buf = st & 1;
+    if (st + 1 < nstages) {
+      issue(st + 1, buf ^ 1);
+      ptx::cp_async_wait<1>();
+    } else {
+      ptx::cp_async_wait<0>();
+    }
+    __syncthreads();
+    const uint32_t uX = ptx::smem_u32(sX[buf]), uY = ptx::smem_u32(sY[buf]);
+    const int k0 = warp * 16;  // this warp's 16 token rows of the stage
+    const int mat = lane >> 3, r = lane & 7;
+    uint32_t bfr[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; nt += 2)
+      ptx::ldmatrix_x4_trans(bfr[nt >> 1], uY + sw_off_x(k0 + (mat & 1) * 8 + r, nt + (mat >> 1), 8));
+#pragma unroll
+    for (int a = 0; a < IT; ++a) {
+      uint32_t af[4];
+      // A[i][m] = X[m][i]: transposed 8x8 loads; matrices (i lo, m lo), (i hi, m lo), (i lo, m hi), (i hi, m hi)
+      ptx::ldmatrix_x4_trans(af, uX + sw_off_x(k0 + (mat >> 1) * 8 + r, a * 2 + (mat & 1), XCH));
+#pragma unroll
+      for (int nt = 0; nt < 8; nt += 2) {
+        const uint32_t b0[2] = {bfr[nt >> 1][0], bfr[nt >> 1][1]}, b1[2] = {bfr[nt >> 1][2], bfr[nt >> 1][3]};
+        ptx::mma_bf16_16816(acc[a][nt], af, b0);
+        ptx::mma_bf16_16816(acc[a][nt + 1], af, b1);
+      }
+    }
+    __syncthreads();
+  }
+
+  // combine the 4 warps' partial sums, then one atomic per element
+  for (int i = threadIdx.x; i < I * 64; i += kRedThreads) sRed[i] = 0.f;
+  __syncthreads();
+#pragma unroll
+  for (int a = 0; a < IT; ++a)
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      const int row = a * 16 + (lane >> 2), col = nt * 8 + (lane & 3) * 2;
+      atomicAdd(&sRed[row * 64 + col], acc[a][nt][0]);
+      atomicAdd(&sRed[row * 64 + col + 1], acc[a][nt][1]);
+      atomicAdd(&sRed[(row + 8) * 64 + col], acc[a][nt][2]);
+      atomicAdd(&sRed[(row + 8) * 64 + col + 1], acc[a][nt][3]);
+    }
+  __syncthreads();
+  for (int i = threadIdx.x; i < I * 64; i += kRedThreads) {
+    const int row = i >> 6, col = i & 63;
+    atomicAdd(out + (long long)row * ldout + j0 + col, sRed[i]);
+  }
+}
+
+}  // namespace peft

@@ -1,0 +1,292 @@
+"""Frozen-backbone ViT step engine: runs the whole visual tower forward and backward through the C-ABI kernels.
+
+One `VitEngine` owns
+  * the prepared frozen weights (bf16 W [N,K] for the forward products, bf16 W^T [K,N] for the dX products — the
+    backbone is frozen, so there is never a dW product; fp32 biases and LayerNorm parameters),
+  * a per-batch-size workspace holding the activations saved for backward and the scratch buffers,
+and exposes the tower as ONE autograd node (`backbone(images, Dn, UpT)`), so Python overhead per step is a few dozen
+ctypes calls and torch.autograd only sees the tiny adapter tensors.
+
+Adapter algebra (timm dialect): the q/v update is applied in low-rank form
+      qkv = [LN1(x) | p] @ [Wqkv | Up]^T + b,      p = LN1(x) @ Dn^T            (K-extension of the frozen GEMM)
+with   LoRA:        Dn = [W1_q ; W1_v],               Up = alpha/r * blockdiag(W2_q, 0, W2_v)
+       KAdaptation: Dn[(i,r,c),(a,k)] = A_i[a,c] u_i[k,r],   Up[(c,p),(i,r,c')] = delta(c,c') v_i[r,p]   (reshape trick)
+so the [D,D] update matrix is never formed.  The engine consumes Dn [depth, r, D] and UpT [depth, r, 3D] (fp32, built
+by tiny differentiable torch ops from the reference-named parameters, see modules.py) and returns their gradients,
+which are token reductions p^T dqkv and dp^T LN1(x) done by peft_tn_reduce.
+
+Reference lines replaced: FS/kadaptation.py:198-238,273-277,516-544; FS/lora.py (same lines); FS/model.py:1155-1158,
+1202-1219 (CLIP dialect: QuickGELU, ln_pre, ln_post, proj; eps 1e-5).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+from . import ops
+
+
+@dataclass
+class EngineCfg:
+    dialect: str          # "timm" | "clip"
+    img: int
+    patch: int
+    width: int
+    depth: int
+    heads: int
+    mlp: int
+    out_dim: int = 0      # clip: visual projection width (0 = no projection)
+    rank: int = 0         # low-rank q/v adapter columns r' (0 = no q/v adapter)
+
+    @property
+    def seq(self):
+        return (self.img // self.patch) ** 2 + 1
+
+    @property
+    def eps(self):
+        return 1e-6 if self.dialect == "timm" else 1e-5
+
+    @property
+    def rank_pad(self):
+        return ((self.rank + 15) // 16) * 16
+
+
+_TIMM_KEYS = dict(ln1_w="blocks.{i}.norm1.weight", ln1_b="blocks.{i}.norm1.bias", qkv_w="blocks.{i}.attn.qkv.weight",
+                  qkv_b="blocks.{i}.attn.qkv.bias", proj_w="blocks.{i}.attn.proj.weight", proj_b="blocks.{i}.attn.proj.bias",
+                  ln2_w="blocks.{i}.norm2.weight", ln2_b="blocks.{i}.norm2.bias", fc1_w="blocks.{i}.mlp.fc1.weight",
+                  fc1_b="blocks.{i}.mlp.fc1.bias", fc2_w="blocks.{i}.mlp.fc2.weight", fc2_b="blocks.{i}.mlp.fc2.bias")
+_CLIP_KEYS = dict(ln1_w="transformer.resblocks.{i}.ln_1.weight", ln1_b="transformer.resblocks.{i}.ln_1.bias",
+                  qkv_w="transformer.resblocks.{i}.attn.in_proj_weight", qkv_b="transformer.resblocks.{i}.attn.in_proj_bias",
+                  proj_w="transformer.resblocks.{i}.attn.out_proj.weight", proj_b="transformer.resblocks.{i}.attn.out_proj.bias",
+                  ln2_w="transformer.resblocks.{i}.ln_2.weight", ln2_b="transformer.resblocks.{i}.ln_2.bias",
+                  fc1_w="transformer.resblocks.{i}.mlp.c_fc.weight", fc1_b="transformer.resblocks.{i}.mlp.c_fc.bias",
+                  fc2_w="transformer.resblocks.{i}.mlp.c_proj.weight", fc2_b="transformer.resblocks.{i}.mlp.c_proj.bias")
+
+
+class _Workspace:
+    """Activations saved for backward + scratch, for one batch size."""
+
+    def __init__(self, cfg: EngineCfg, B: int, dev):
+        D, L, H, F, dep, rp = cfg.width, cfg.seq, cfg.heads, cfg.mlp, cfg.depth, cfg.rank_pad
+        M = B * L
+        bf, f32 = torch.bfloat16, torch.float32
+        e = lambda *s, dt=bf: torch.empty(*s, device=dev, dtype=dt)
+        self.B, self.M = B, M
+        P = L - 1
+        self.patches = e(B * P, 3 * cfg.patch * cfg.patch)
+        self.pe = e(B * P, D)
+        self.tokens = e(M, D, dt=f32) if cfg.dialect == "clip" else None
+        # per layer, saved for backward
+        self.x0 = [e(M, D, dt=f32) for _ in range(dep + 1)]      # block inputs; x0[dep] = tower output
+        self.x1 = [e(M, D, dt=f32) for _ in range(dep)]          # after the attention residual
+        self.mean1 = e(dep, M, dt=f32); self.rstd1 = e(dep, M, dt=f32)
+        self.mean2 = e(dep, M, dt=f32); self.rstd2 = e(dep, M, dt=f32)
+        self.xn1 = [torch.zeros(M, D + rp, device=dev, dtype=bf) for _ in range(dep)]   # [LN1(x) | p]
+        self.qkv = [e(M, 3 * D) for _ in range(dep)]
+        self.o = [e(M, D) for _ in range(dep)]
+        self.lse2 = e(dep, B * H * L, dt=f32)
+        self.h = [e(M, F) for _ in range(dep)]                   # MLP pre-activation
+        # scratch shared by all layers
+        self.xn2 = e(M, D)
+        self.act = e(M, F)
+        self.dh = e(M, F)
+        self.dxn = e(M, D)
+        self.d_o = e(M, D)
+        self.dqkv = torch.zeros(M, 3 * D + rp, device=dev, dtype=bf)   # [dq dk dv | dp]
+        self.delta = e(B * H * L, dt=f32)
+        self.g = e(M, D)                                         # residual-gradient stream (bf16)
+        # final LayerNorm on the cls rows
+        self.meanf = e(B, dt=f32); self.rstdf = e(B, dt=f32)
+        self.yf = e(B, D)                                        # clip: ln_post output (bf16 operand of the projection)
+        self.dyf = e(B, D)
+        self.generation = 0
+
+
+class VitEngine:
+    def __init__(self, cfg: EngineCfg, device="cuda"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("peft_b200.VitEngine needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.cfg = cfg
+        self.dev = torch.device(device)
+        self.ws = {}
+        self.frozen_loaded = False
+        self._fwd_generation = 0
+
+    # ------------------------------------------------------------------ frozen weights
+    def load_frozen(self, sd: dict):
+        """sd: reference-named fp32 state dict of the visual tower (any device)."""
+        cfg, dev = self.cfg, self.dev
+        D, F, dep, rp = cfg.width, cfg.mlp, cfg.depth, cfg.rank_pad
+        bf, f32 = torch.bfloat16, torch.float32
+        keys = _TIMM_KEYS if cfg.dialect == "timm" else _CLIP_KEYS
+        g = lambda k: sd[k].detach().to(dev, f32)
+        L = {k: [g(v.format(i=i)) for i in range(dep)] for k, v in keys.items()}
+        # forward operands: W [N, K]; the qkv weight carries rp extra K columns for scale*Up (refreshed every step)
+        self.wqkv = torch.zeros(dep, 3 * D, D + rp, device=dev, dtype=bf)
+        self.wqkvT = torch.zeros(dep, D, 3 * D + rp, device=dev, dtype=bf)   # [W^T | Dn^T] for dX
+        for i in range(dep):
+            self.wqkv[i, :, :D] = L["qkv_w"][i]
+            self.wqkvT[i, :, :3 * D] = L["qkv_w"][i].T
+        stack = lambda k, t=False: torch.stack([(w.T if t else w) for w in L[k]]).to(bf).contiguous()
+        self.wproj, self.wprojT = stack("proj_w"), stack("proj_w", True)
+        self.wfc1, self.wfc1T = stack("fc1_w"), stack("fc1_w", True)
+        self.wfc2, self.wfc2T = stack("fc2_w"), stack("fc2_w", True)
+        vec = lambda k: torch.stack(L[k]).contiguous()
+        self.bqkv, self.bproj, self.bfc1, self.bfc2 = vec("qkv_b"), vec("proj_b"), vec("fc1_b"), vec("fc2_b")
+        self.ln1_w, self.ln1_b, self.ln2_w, self.ln2_b = vec("ln1_w"), vec("ln1_b"), vec("ln2_w"), vec("ln2_b")
+        if cfg.dialect == "timm":
+            self.patch_w = g("patch_embed.proj.weight").reshape(D, -1).to(bf).contiguous()
+            self.patch_b = g("patch_embed.proj.bias").contiguous()
+            self.cls = g("cls_token").reshape(D).contiguous()
+            self.pos = g("pos_embed").reshape(cfg.seq, D).contiguous()
+            self.lnf_w, self.lnf_b = g("norm.weight").contiguous(), g("norm.bias").contiguous()
+            self.vproj = None
+        else:
+            self.patch_w = g("conv1.weight").reshape(D, -1).to(bf).contiguous()
+            self.patch_b = None
+            self.cls = g("class_embedding").reshape(D).contiguous()
+            self.pos = g("positional_embedding").reshape(cfg.seq, D).contiguous()
+            self.lnpre_w, self.lnpre_b = g("ln_pre.weight").contiguous(), g("ln_pre.bias").contiguous()
+            self.lnf_w, self.lnf_b = g("ln_post.weight").contiguous(), g("ln_post.bias").contiguous()
+            pr = sd.get("proj")
+            if pr is not None and cfg.out_dim > 0:
+                self.vproj = g("proj").to(bf).contiguous()            # [D, E]  == B operand [N=D, K=E] of the backward
+                self.vprojT = g("proj").T.to(bf).contiguous()         # [E, D]  == B operand [N=E, K=D] of the forward
+            else:
+                self.vproj = None
+        if rp > 0:
+            self.dn_bf = torch.zeros(dep, rp, D, device=dev, dtype=bf)
+            self.upT_bf = torch.zeros(dep, rp, 3 * D, device=dev, dtype=bf)
+        self.act_fwd = ops.EPI_GELU if cfg.dialect == "timm" else ops.EPI_QUICKGELU
+        self.act_bwd = ops.EPI_DGELU if cfg.dialect == "timm" else ops.EPI_DQUICKGELU
+        self.frozen_loaded = True
+
+    def _workspace(self, B):
+        w = self.ws.get(B)
+        if w is None:
+            w = self.ws[B] = _Workspace(self.cfg, B, self.dev)
+        return w
+
+    # ------------------------------------------------------------------ adapter operand refresh (per step)
+    def _refresh_adapter(self, Dn, UpT):
+        cfg = self.cfg
+        D, r = cfg.width, cfg.rank
+        if r == 0:
+            return
+        with torch.no_grad():
+            self.dn_bf[:, :r].copy_(Dn)
+            self.upT_bf[:, :r].copy_(UpT)
+            self.wqkv[:, :, D:D + r].copy_(UpT.transpose(1, 2))
+            self.wqkvT[:, :, 3 * D:3 * D + r].copy_(Dn.transpose(1, 2))
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, images, Dn=None, UpT=None):
+        cfg = self.cfg
+        if not self.frozen_loaded:
+            raise RuntimeError("VitEngine.forward before load_frozen()")
+        if images.device != self.dev and images.device.type != "cuda":
+            raise RuntimeError("VitEngine: images must be on the CUDA device")
+        D, L, H, dep, rp = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.rank_pad
+        B = images.shape[0]
+        w = self._workspace(B)
+        self._refresh_adapter(Dn, UpT)
+        images = images.contiguous().float()
+        # patch embedding: unfold -> GEMM (+bias) -> prepend cls, add positions
+        ops.im2col_patches(images, w.patches, cfg.patch)
+        ops.gemm(w.patches, self.patch_w, w.pe, bias=self.patch_b)
+        if cfg.dialect == "clip":
+            ops.assemble_tokens(w.pe, self.cls, self.pos, w.tokens, B, L, D)
+            ops.layernorm_fwd(w.tokens, self.lnpre_w, self.lnpre_b, w.x0[0], None, None, cfg.eps)
+        else:
+            ops.assemble_tokens(w.pe, self.cls, self.pos, w.x0[0], B, L, D)
+        scale = 64 ** -0.5
+        for i in range(dep):
+            xn1 = w.xn1[i]
+            ops.layernorm_fwd(w.x0[i], self.ln1_w[i], self.ln1_b[i], xn1[:, :D], w.mean1[i], w.rstd1[i], cfg.eps)
+            if rp:
+                ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                    # p = LN1(x) Dn^T
+                ops.gemm(xn1, self.wqkv[i], w.qkv[i], bias=self.bqkv[i])           # [x|p] [W|Up]^T + b
+            else:
+                ops.gemm(xn1[:, :D], self.wqkv[i][:, :D], w.qkv[i], bias=self.bqkv[i])
+            ops.attention_fwd(w.qkv[i], w.o[i], w.lse2[i], B, H, L, scale)
+            ops.gemm(w.o[i], self.wproj[i], w.x1[i], bias=self.bproj[i], epilogue=ops.EPI_RESID_F32, aux=w.x0[i])
+            ops.layernorm_fwd(w.x1[i], self.ln2_w[i], self.ln2_b[i], w.xn2, w.mean2[i], w.rstd2[i], cfg.eps)
+            ops.gemm(w.xn2, self.wfc1[i], w.h[i], bias=self.bfc1[i], epilogue=self.act_fwd, out2=w.act)
+            ops.gemm(w.act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i])
+        # final LayerNorm on the cls rows (+ CLIP projection)
+        xcls = w.x0[dep].view(B, L * D)[:, :D]
+        if self.vproj is None:
+            feat = torch.empty(B, D, device=self.dev, dtype=torch.float32)
+            ops.layernorm_fwd(xcls, self.lnf_w, self.lnf_b, feat, w.meanf, w.rstdf, cfg.eps)
+        else:
+            ops.layernorm_fwd(xcls, self.lnf_w, self.lnf_b, w.yf, w.meanf, w.rstdf, cfg.eps)
+            feat = torch.empty(B, cfg.out_dim, device=self.dev, dtype=torch.float32)
+            ops.gemm(w.yf, self.vprojT, feat, epilogue=ops.EPI_STORE_F32)
+        w.generation += 1
+        self._fwd_generation = (B, w.generation)
+        return feat
+
+    # ------------------------------------------------------------------ backward
+    def backward(self, dfeat):
+        cfg = self.cfg
+        D, L, H, dep, r, rp = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.rank, cfg.rank_pad
+        B = dfeat.shape[0]
+        w = self._workspace(B)
+        if self._fwd_generation != (B, w.generation):
+            raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
+        dfeat = dfeat.contiguous().float()
+        w.g.zero_()
+        xcls = w.x0[dep].view(B, L * D)[:, :D]
+        gcls = w.g.view(B, L * D)[:, :D]
+        if self.vproj is None:
+            ops.layernorm_bwd(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls)
+        else:
+            ops.gemm(dfeat.to(torch.bfloat16), self.vproj, w.dyf)                # dy = dfeat proj^T
+            ops.layernorm_bwd(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls)
+        dDn = dUpT = None
+        if r:
+            dDn = torch.zeros(dep, rp, D, device=self.dev, dtype=torch.float32)
+            dUpT = torch.zeros(dep, rp, 3 * D, device=self.dev, dtype=torch.float32)
+        scale = 64 ** -0.5
+        for i in reversed(range(dep)):
+            # MLP: dh = (g W2) * act'(h) ; dxn2 = dh W1 ; g += LN2'(dxn2)
+            ops.gemm(w.g, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
+            ops.gemm(w.dh, self.wfc1T[i], w.dxn)
+            ops.layernorm_bwd(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g)
+            # attention: d_o = g Wproj ; dqkv = attn'(d_o)
+            ops.gemm(w.g, self.wprojT[i], w.d_o)
+            ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
+            if rp:
+                dq = w.dqkv[:, :3 * D]
+                ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
+                for c in range(0, rp, 64):                                          # adapter-gradient token reductions
+                    cw = min(64, rp - c)
+                    ops.tn_reduce(w.xn1[i][:, D + c:D + c + cw], dq, dUpT[i, c:c + cw])            # dUp^T = p^T dqkv
+                    ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])  # dDn = dp^T x
+                ops.gemm(w.dqkv, self.wqkvT[i], w.dxn)                              # dxn1 = [dqkv|dp] [W^T|Dn^T]^T
+            else:
+                ops.gemm(w.dqkv[:, :3 * D], self.wqkvT[i][:, :3 * D], w.dxn)
+            ops.layernorm_bwd(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g)
+        # the patch embedding / ln_pre are frozen and the images need no gradient: stop here.
+        if r:
+            return dDn[:, :r], dUpT[:, :r]
+        return None, None
+
+
+class _BackboneFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, engine, images, Dn, UpT):
+        ctx.engine = engine
+        ctx.has_adapter = Dn is not None
+        return engine.forward(images, Dn, UpT)
+
+    @staticmethod
+    def backward(ctx, dfeat):
+        dDn, dUpT = ctx.engine.backward(dfeat)
+        return None, None, dDn, dUpT
+
+
+def backbone(engine: VitEngine, images, Dn=None, UpT=None):
+    """Differentiable (w.r.t. Dn / UpT) visual-tower feature extraction through the CUDA engine."""
+    return _BackboneFn.apply(engine, images, Dn, UpT)

@@ -1,0 +1,127 @@
+"""Tensor-level wrappers over the C ABI (include/peft_b200.h).  torch is used only for device memory and streams.
+
+Every function enqueues on the current torch CUDA stream and returns immediately.  Inputs must be CUDA tensors whose
+last dimension is contiguous; 2-D views with a row pitch (column slices of wider buffers) are accepted and passed as
+(pointer, ld).  Nothing here falls back to torch math.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+EPI_STORE, EPI_GELU, EPI_QUICKGELU, EPI_RESID_F32, EPI_DGELU, EPI_DQUICKGELU, EPI_STORE_F32, EPI_RELU, EPI_DRELU, \
+    EPI_GELU_TANH, EPI_DGELU_TANH, EPI_RESID_BF16 = range(12)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _mat(t: torch.Tensor, dtype=None, name="tensor"):
+    if not t.is_cuda:
+        raise RuntimeError(f"peft_b200: {name} must be a CUDA tensor (no CPU fallback)")
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"peft_b200: {name} must be 2-D with a contiguous last dim, got shape {tuple(t.shape)} strides {t.stride()}")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"peft_b200: {name} must be {dtype}, got {t.dtype}")
+    return t.data_ptr(), t.stride(0)
+
+
+def gemm(a, b, out, bias=None, epilogue=EPI_STORE, out2=None, aux=None):
+    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T (+ bias)); bf16 operands, see peft_gemm_bf16."""
+    pa, lda = _mat(a, torch.bfloat16, "a")
+    pb, ldb = _mat(b, torch.bfloat16, "b")
+    M, K = a.shape
+    N = b.shape[0]
+    if b.shape[1] != K:
+        raise ValueError(f"gemm: K mismatch {a.shape} x {b.shape}")
+    f32 = epilogue in (EPI_RESID_F32, EPI_STORE_F32)
+    po, ldo = _mat(out, torch.float32 if f32 else torch.bfloat16, "out")
+    if tuple(out.shape) != (M, N):
+        raise ValueError(f"gemm: out shape {tuple(out.shape)} != {(M, N)}")
+    po2 = ldo2 = 0
+    if out2 is not None:
+        po2, ldo2 = _mat(out2, torch.bfloat16, "out2")
+    pax = ldax = 0
+    if aux is not None:
+        pax, ldax = _mat(aux, torch.float32 if epilogue == EPI_RESID_F32 else torch.bfloat16, "aux")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != N or not bias.is_contiguous()):
+        raise ValueError("gemm: bias must be contiguous fp32 [N]")
+    _lib.check(_lib.load().peft_gemm_bf16(pa, lda, pb, ldb, M, N, K, _p(bias), po, ldo, po2, ldo2, pax, ldax, epilogue,
+                                          _stream()), "peft_gemm_bf16")
+    return out
+
+
+def layernorm_fwd(x, gamma, beta, y, mean=None, rstd=None, eps=1e-6):
+    px, ldx = _mat(x, None, "x")
+    py, ldy = _mat(y, None, "y")
+    M, D = x.shape
+    _lib.check(_lib.load().peft_layernorm_fwd(px, ldx, int(x.dtype == torch.bfloat16), _p(gamma), _p(beta), py, ldy,
+                                              int(y.dtype == torch.float32), _p(mean), _p(rstd), M, D, float(eps),
+                                              _stream()), "peft_layernorm_fwd")
+    return y
+
+
+def layernorm_bwd(dy, x, mean, rstd, gamma, g_in, g_out, dgamma=None, dbeta=None):
+    pdy, lddy = _mat(dy, None, "dy")
+    px, ldx = _mat(x, None, "x")
+    pgo, ldgo = _mat(g_out, torch.bfloat16, "g_out")
+    pgi = ldgi = 0
+    if g_in is not None:
+        pgi, ldgi = _mat(g_in, torch.bfloat16, "g_in")
+    M, D = x.shape
+    _lib.check(_lib.load().peft_layernorm_bwd(pdy, lddy, int(dy.dtype == torch.float32), px, ldx,
+                                              int(x.dtype == torch.bfloat16), _p(mean), _p(rstd), _p(gamma), pgi, ldgi,
+                                              pgo, ldgo, _p(dgamma), _p(dbeta), M, D, _stream()), "peft_layernorm_bwd")
+    return g_out
+
+
+def attention_fwd(qkv, o, lse2, B, H, L, scale):
+    pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
+    po, ldo = _mat(o, torch.bfloat16, "o")
+    _lib.check(_lib.load().peft_attention_fwd(pq, ldq, po, ldo, _p(lse2), B, H, L, float(scale), _stream()),
+               "peft_attention_fwd")
+    return o
+
+
+def attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, scale):
+    pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
+    po, ldo = _mat(o, torch.bfloat16, "o")
+    pg, ldg = _mat(d_o, torch.bfloat16, "d_o")
+    pd, ldd = _mat(dqkv, torch.bfloat16, "dqkv")
+    _lib.check(_lib.load().peft_attention_bwd(pq, ldq, po, ldo, pg, ldg, _p(lse2), _p(delta), pd, ldd, B, H, L,
+                                              float(scale), _stream()), "peft_attention_bwd")
+    return dqkv
+
+
+def im2col_patches(images, patches, patch):
+    B, C, Hh, Ww = images.shape
+    if C != 3 or Hh != Ww or images.dtype != torch.float32 or not images.is_contiguous() or not images.is_cuda:
+        raise ValueError("im2col_patches: images must be contiguous CUDA fp32 [B,3,S,S]")
+    _lib.check(_lib.load().peft_im2col_patches(images.data_ptr(), patches.data_ptr(), B, Hh, patch, _stream()),
+               "peft_im2col_patches")
+    return patches
+
+
+def assemble_tokens(patch_embed, cls, pos, x, B, L, D):
+    _lib.check(_lib.load().peft_assemble_tokens(patch_embed.data_ptr(), cls.data_ptr(), pos.data_ptr(), x.data_ptr(), B,
+                                                L, D, _stream()), "peft_assemble_tokens")
+    return x
+
+
+def tn_reduce(x, y, out):
+    """out[I,J] += x[M,I]^T @ y[M,J]  (fp32 out, bf16 x / y)."""
+    px, ldx = _mat(x, torch.bfloat16, "x")
+    py, ldy = _mat(y, torch.bfloat16, "y")
+    po, ldo = _mat(out, torch.float32, "out")
+    M, I = x.shape
+    J = y.shape[1]
+    if tuple(out.shape) != (I, J) or y.shape[0] != M:
+        raise ValueError("tn_reduce: shape mismatch")
+    _lib.check(_lib.load().peft_tn_reduce(px, ldx, I, py, ldy, J, po, ldo, M, _stream()), "peft_tn_reduce")
+    return out

@@ -1,0 +1,198 @@
+"""Op-level parity of every C-ABI kernel against a plain PyTorch fp32 reference of the same op (GPU only).
+
+Tolerances: bf16 outputs are compared with a relative Frobenius error <= 1e-2 (one bf16 rounding is 2^-9 = 2e-3 per
+element; products accumulate in fp32); fp32 outputs <= 1e-4.
+"""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a = a.float()
+    b = b.float()
+    return float((a - b).norm() / (b.norm() + 1e-20))
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from peft_b200 import ops as _ops
+    return _ops
+
+
+def _r(*shape, scale=1.0, dtype=torch.float32, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(*shape, generator=g, device="cuda") * scale).to(dtype)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 768, 768), (1576, 2304, 800), (1576, 32, 768), (1576, 16, 768),
+                                   (777, 200, 72), (50, 768, 3072), (6304, 768, 2336)])
+def test_gemm_store(ops, M, N, K):
+    a = _r(M, K, dtype=torch.bfloat16, seed=1)
+    b = _r(N, K, scale=0.05, dtype=torch.bfloat16, seed=2)
+    bias = _r(N, seed=3)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a, b, out, bias=bias)
+    ref = a.float() @ b.float().T + bias
+    assert rel(out, ref) < 1e-2
+
+
+def test_gemm_strided_views(ops):
+    """K-extended operands: A and out are column slices of wider buffers (the [x | p] layout)."""
+    M, D, r = 500, 768, 32
+    buf = _r(M, D + r, dtype=torch.bfloat16, seed=4)
+    dn = _r(r, D, scale=0.05, dtype=torch.bfloat16, seed=5)
+    ref_p = buf[:, :D].float() @ dn.float().T
+    ops.gemm(buf[:, :D], dn, buf[:, D:])
+    assert rel(buf[:, D:], ref_p) < 1e-2
+    w = _r(2304, D + r, scale=0.05, dtype=torch.bfloat16, seed=6)
+    out = torch.empty(M, 2304, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(buf, w, out)
+    assert rel(out, buf.float() @ w.float().T) < 1e-2
+
+
+@pytest.mark.parametrize("epi", ["gelu", "quickgelu", "gelu_tanh", "relu"])
+def test_gemm_activation_epilogues(ops, epi):
+    M, N, K = 700, 3072, 768
+    a = _r(M, K, dtype=torch.bfloat16, seed=1)
+    b = _r(N, K, scale=0.05, dtype=torch.bfloat16, seed=2)
+    bias = _r(N, scale=0.5, seed=3)
+    h = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    act = torch.empty_like(h)
+    ref_h = a.float() @ b.float().T + bias
+    if epi == "relu":
+        ops.gemm(a, b, h, bias=bias, epilogue=ops.EPI_RELU)
+        assert rel(h, F.relu(ref_h)) < 1e-2
+        return
+    code = {"gelu": ops.EPI_GELU, "quickgelu": ops.EPI_QUICKGELU, "gelu_tanh": ops.EPI_GELU_TANH}[epi]
+    ops.gemm(a, b, h, bias=bias, epilogue=code, out2=act)
+    fn = {"gelu": F.gelu, "quickgelu": lambda x: x * torch.sigmoid(1.702 * x),
+          "gelu_tanh": lambda x: F.gelu(x, approximate="tanh")}[epi]
+    assert rel(h, ref_h) < 1e-2
+    assert rel(act, fn(ref_h)) < 1e-2
+    # derivative epilogues: out = acc * act'(aux)
+    dcode = {"gelu": ops.EPI_DGELU, "quickgelu": ops.EPI_DQUICKGELU, "gelu_tanh": ops.EPI_DGELU_TANH}[epi]
+    g = _r(M, K, dtype=torch.bfloat16, seed=7)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(g, b, out, epilogue=dcode, aux=h)
+    hh = h.float().requires_grad_(True)
+    fn(hh).backward(g.float() @ b.float().T)
+    assert rel(out, hh.grad) < 1e-2
+
+
+def test_gemm_residual_f32(ops):
+    M, N, K = 900, 768, 3072
+    a = _r(M, K, dtype=torch.bfloat16, seed=1)
+    b = _r(N, K, scale=0.05, dtype=torch.bfloat16, seed=2)
+    bias = _r(N, seed=3)
+    res = _r(M, N, seed=4)
+    out = torch.empty(M, N, device="cuda", dtype=torch.float32)
+    ops.gemm(a, b, out, bias=bias, epilogue=ops.EPI_RESID_F32, aux=res)
+    assert rel(out, a.float() @ b.float().T + bias + res) < 1e-4
+
+
+def test_gemm_rejects_bad_input(ops):
+    a = torch.zeros(16, 7, device="cuda", dtype=torch.bfloat16)
+    b = torch.zeros(16, 7, device="cuda", dtype=torch.bfloat16)
+    out = torch.zeros(16, 16, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError):
+        ops.gemm(a, b, out)          # K % 8 != 0 -> status code -> RuntimeError, not a silent fallback
+    with pytest.raises(RuntimeError):
+        ops.gemm(a.cpu(), b, out)
+
+
+@pytest.mark.parametrize("M,D", [(1000, 768), (333, 1024), (64, 128)])
+def test_layernorm_fwd_bwd(ops, M, D):
+    x = _r(M, D, scale=2.0, seed=1) + 0.5
+    gamma = 1.0 + _r(D, scale=0.1, seed=2)
+    beta = _r(D, scale=0.1, seed=3)
+    y = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+    yf = torch.empty(M, D, device="cuda", dtype=torch.float32)
+    mean = torch.empty(M, device="cuda")
+    rstd = torch.empty(M, device="cuda")
+    ops.layernorm_fwd(x, gamma, beta, y, mean, rstd, eps=1e-6)
+    ops.layernorm_fwd(x, gamma, beta, yf, None, None, eps=1e-6)
+    xr = x.clone().requires_grad_(True)
+    gr = gamma.clone().requires_grad_(True)
+    br = beta.clone().requires_grad_(True)
+    ref = F.layer_norm(xr, (D,), gr, br, 1e-6)
+    assert rel(yf, ref) < 1e-5
+    assert rel(y, ref) < 5e-3
+    dy = _r(M, D, dtype=torch.bfloat16, seed=4)
+    gin = _r(M, D, dtype=torch.bfloat16, seed=5)
+    gout = torch.empty_like(gin)
+    dgamma = torch.zeros(D, device="cuda")
+    dbeta = torch.zeros(D, device="cuda")
+    ops.layernorm_bwd(dy, x, mean, rstd, gamma, gin, gout, dgamma, dbeta)
+    ref.backward(dy.float())
+    assert rel(gout, gin.float() + xr.grad) < 5e-3
+    assert rel(dgamma, gr.grad) < 1e-4
+    assert rel(dbeta, br.grad) < 1e-4
+    # no residual input, fp32 dy, strided rows (the final-LN-on-cls-rows use)
+    gout2 = torch.zeros(M, 2 * D, device="cuda", dtype=torch.bfloat16)
+    ops.layernorm_bwd(dy.float(), x, mean, rstd, gamma, None, gout2[:, :D])
+    assert rel(gout2[:, :D], xr.grad) < 5e-3
+
+
+@pytest.mark.parametrize("B,H,L", [(2, 12, 50), (3, 12, 197), (2, 16, 257), (1, 2, 64), (2, 3, 5)])
+def test_attention_fwd_bwd(ops, B, H, L):
+    D = H * 64
+    qkv = _r(B * L, 3 * D, scale=1.0, dtype=torch.bfloat16, seed=1)
+    o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * L, device="cuda")
+    scale = 64 ** -0.5
+    ops.attention_fwd(qkv, o, lse2, B, H, L, scale)
+    t = qkv.float().reshape(B, L, 3, H, 64).permute(2, 0, 3, 1, 4).clone().requires_grad_(True)
+    q, k, v = t[0], t[1], t[2]
+    s = (q @ k.transpose(-2, -1)) * scale
+    ref = (F.softmax(s, dim=-1) @ v).transpose(1, 2).reshape(B * L, D)
+    assert rel(o, ref) < 1e-2
+    ref_lse2 = (torch.logsumexp(s, dim=-1) * math.log2(math.e)).reshape(-1)
+    assert float((lse2 - ref_lse2).abs().max()) < 2e-2
+    d_o = _r(B * L, D, dtype=torch.bfloat16, seed=2)
+    dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+    delta = torch.empty(B * H * L, device="cuda")
+    ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, scale)
+    ref.backward(d_o.float())
+    ref_d = t.grad.permute(1, 3, 0, 2, 4).reshape(B * L, 3 * D)
+    for i, nm in enumerate("qkv"):
+        assert rel(dqkv[:, i * D:(i + 1) * D], ref_d[:, i * D:(i + 1) * D]) < 2e-2, nm
+
+
+@pytest.mark.parametrize("M,I,J", [(1000, 32, 768), (5000, 16, 2304), (333, 64, 768), (64, 32, 64), (50432, 32, 768)])
+def test_tn_reduce(ops, M, I, J):
+    wide = _r(M, 800 if I <= 32 else 832, dtype=torch.bfloat16, seed=1)
+    x = wide[:, 768:768 + I]
+    y = _r(M, J, dtype=torch.bfloat16, seed=2)
+    out = torch.zeros(I, J, device="cuda")
+    ops.tn_reduce(x, y, out)
+    ref = x.float().T @ y.float()
+    assert rel(out, ref) < 1e-4
+    ops.tn_reduce(x, y, out)      # accumulates
+    assert rel(out, 2 * ref) < 1e-4
+
+
+def test_patch_embed_pieces(ops):
+    B, S, p, D = 3, 64, 16, 768
+    img = _r(B, 3, S, S, seed=1)
+    w = _r(D, 3, p, p, scale=0.02, seed=2)
+    bias = _r(D, scale=0.02, seed=3)
+    P = (S // p) ** 2
+    patches = torch.empty(B * P, 3 * p * p, device="cuda", dtype=torch.bfloat16)
+    ops.im2col_patches(img, patches, p)
+    ref_patches = F.unfold(img, kernel_size=p, stride=p).transpose(1, 2).reshape(B * P, -1)
+    assert rel(patches, ref_patches) < 4e-3
+    pe = torch.empty(B * P, D, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(patches, w.reshape(D, -1).to(torch.bfloat16), pe, bias=bias)
+    ref_pe = F.conv2d(img, w, bias, stride=p).flatten(2).transpose(1, 2)
+    assert rel(pe.reshape(B, P, D), ref_pe) < 1e-2
+    cls = _r(D, seed=4)
+    pos = _r(P + 1, D, seed=5)
+    x = torch.empty(B, P + 1, D, device="cuda")
+    ops.assemble_tokens(pe, cls, pos, x, B, P + 1, D)
+    ref_x = torch.cat([cls.expand(B, 1, D), pe.float().reshape(B, P, D)], 1) + pos
+    assert rel(x, ref_x) < 1e-6
