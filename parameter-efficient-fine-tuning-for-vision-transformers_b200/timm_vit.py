@@ -1,0 +1,257 @@
+"""timm-dialect ViT with PEFT adapters — drop-in for the reference classes of
+few_shot/vision_benchmark/evaluation/{kadaptation,lora,adapter}.py (= full_shot/main/lib/models/cls_vit_*.py).
+
+Same class names, constructor arguments, parameter names and shapes (so `state_dict()` / `load_state_dict()` and the
+trainers' name filters — `'W' in name`, `'adapter' in name` — work unchanged), but `VisionTransformer.forward` runs the
+whole tower through the CUDA engine (engine.py) instead of ATen.  The sub-modules only hold parameters; they have no
+eager forward — calling one raises, there is no fallback path.
+
+Adapter hyper-parameters are constructor kwargs with the reference's values as defaults where the reference is
+usable: LoRA r=4, alpha=128 (FS/lora.py); KAdaptation phm_rank=1, init 0.01, and phm_dim=4 instead of the committed
+768 (north_star formula / headline config; the reference leaves phm_rule uninitialised — here it is
+N(0, 0.01^2)); Houlsby bottleneck 64 with ReLU (FS/adapter.py).
+"""
+from __future__ import annotations
+
+from functools import partial
+
+import torch
+import torch.nn as nn
+
+from .engine import EngineCfg, VitEngine, backbone
+
+
+def _no_eager(self, *a, **k):
+    raise RuntimeError(f"{type(self).__name__} has no eager forward in peft_b200: run the enclosing VisionTransformer "
+                       "(CUDA engine); there is no PyTorch fallback path")
+
+
+class Mlp(nn.Module):
+    """FS/kadaptation.py:57-78."""
+
+    def __init__(self, in_features, hidden_features=None, out_features=None, act_layer=nn.GELU, drop=0.):
+        super().__init__()
+        out_features = out_features or in_features
+        hidden_features = hidden_features or in_features
+        if drop != 0.:
+            raise NotImplementedError("dropout > 0 is not supported (reference configs use 0)")
+        self.fc1 = nn.Linear(in_features, hidden_features)
+        self.act = act_layer()
+        self.fc2 = nn.Linear(hidden_features, out_features)
+
+    forward = _no_eager
+
+
+class Attention(nn.Module):
+    """FS/kadaptation.py:117-238 (adapter='kron'), FS/lora.py Attention (adapter='lora'), plain (adapter='none')."""
+
+    def __init__(self, dim, num_heads=8, qkv_bias=False, qk_scale=None, attn_drop=0., proj_drop=0., res_score=False,
+                 adapter="kron", phm_dim=4, phm_rank=1, phm_init_range=0.01, lora_attn_dim=4, lora_attn_alpha=128):
+        super().__init__()
+        if attn_drop != 0. or proj_drop != 0. or res_score or qk_scale is not None:
+            raise NotImplementedError("attn/proj dropout, res_score and qk_scale overrides are not supported")
+        if dim // num_heads != 64:
+            raise NotImplementedError("the attention kernels are specialised for head_dim 64")
+        self.num_heads = num_heads
+        self.scale = (dim // num_heads) ** -0.5
+        self.adapter_kind = adapter
+        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+        self.proj = nn.Linear(dim, dim)
+        if adapter == "kron":
+            assert dim % phm_dim == 0
+            self.phm_rank = phm_rank
+            self.phm_init_range = phm_init_range
+            n, k = phm_dim, dim // phm_dim
+            self.phm_rule = nn.Parameter(torch.empty(n, n, n).normal_(0, phm_init_range))
+            self.W_left1 = nn.Parameter(torch.empty(n, k, phm_rank).normal_(0, phm_init_range))
+            self.W_right1 = nn.Parameter(torch.empty(n, phm_rank, k).normal_(0, phm_init_range))
+            self.W_left2 = nn.Parameter(torch.empty(n, k, phm_rank).normal_(0, phm_init_range))
+            self.W_right2 = nn.Parameter(torch.empty(n, phm_rank, k).normal_(0, phm_init_range))
+            self.phmb = nn.Parameter(torch.zeros(dim))      # allocated but unused by the reference forward (:100-101)
+        elif adapter == "lora":
+            self.lora_attn_dim = lora_attn_dim
+            self.lora_attn_alpha = lora_attn_alpha
+            self.q_proj_adapter1 = nn.Linear(dim, lora_attn_dim, bias=False)
+            nn.init.normal_(self.q_proj_adapter1.weight, std=0.02)
+            self.q_proj_adapter2 = nn.Linear(lora_attn_dim, dim, bias=False)
+            self.q_proj_adapter2.weight.data.zero_()
+            self.v_proj_adapter1 = nn.Linear(dim, lora_attn_dim, bias=False)
+            nn.init.normal_(self.v_proj_adapter1.weight, std=0.02)
+            self.v_proj_adapter2 = nn.Linear(lora_attn_dim, dim, bias=False)
+            self.v_proj_adapter2.weight.data.zero_()
+        elif adapter not in ("none", "houlsby"):
+            raise ValueError(adapter)
+
+    forward = _no_eager
+
+
+class Block(nn.Module):
+    """FS/kadaptation.py:241-283 (pre-norm only)."""
+
+    def __init__(self, dim, num_heads, mlp_ratio=4., qkv_bias=False, qk_scale=None, drop=0., attn_drop=0., drop_path=0.,
+                 act_layer=nn.GELU, norm_layer=nn.LayerNorm, pre_norm=True, res_score=False, **adapter_kw):
+        super().__init__()
+        if not pre_norm:
+            raise NotImplementedError("post-norm blocks are not supported")
+        if drop_path != 0.:
+            raise NotImplementedError("stochastic depth > 0 is not supported")
+        self.norm1 = norm_layer(dim)
+        self.attn = Attention(dim, num_heads=num_heads, qkv_bias=qkv_bias, qk_scale=qk_scale, attn_drop=attn_drop,
+                              proj_drop=drop, res_score=res_score, **adapter_kw)
+        self.norm2 = norm_layer(dim)
+        self.mlp = Mlp(in_features=dim, hidden_features=int(dim * mlp_ratio), act_layer=act_layer, drop=drop)
+
+    forward = _no_eager
+
+
+class PatchEmbed(nn.Module):
+    """FS/kadaptation.py:286-308."""
+
+    def __init__(self, img_size=224, patch_size=16, in_chans=3, embed_dim=768):
+        super().__init__()
+        self.img_size = (img_size, img_size)
+        self.patch_size = (patch_size, patch_size)
+        self.num_patches = (img_size // patch_size) ** 2
+        self.proj = nn.Conv2d(in_chans, embed_dim, kernel_size=patch_size, stride=patch_size)
+
+    forward = _no_eager
+
+
+def lowrank_factors_kron(rule, w_left, w_right):
+    """[dep,n,n,n], [dep,n,K,r], [dep,n,r,P] -> Dn [dep, n*r*n, n*K], UpT [dep, n*r*n, n*P]  (reshape trick).
+
+    H[(a,k),(c,p)] = sum_{i,r} A_i[a,c] u_i[k,r] v_i[r,p] = (Dn^T UpT)[(a,k),(c,p)]  (FS/kadaptation.py:81-115).
+    """
+    dep, n, K, r = w_left.shape
+    P = w_right.shape[3]
+    Dn = torch.einsum("liac,likr->lircak", rule, w_left).reshape(dep, n * r * n, n * K)
+    eye = torch.eye(n, device=rule.device, dtype=rule.dtype)
+    UpT = torch.einsum("dc,lirp->lirdcp", eye, w_right).reshape(dep, n * r * n, n * P)
+    return Dn, UpT
+
+
+class VisionTransformer(nn.Module):
+    """FS/kadaptation.py:352-551.  forward(x) returns the final-LayerNorm cls feature (the head is applied by the
+    trainer's Classifier, as in the reference: `# x = self.head(x)`)."""
+
+    def __init__(self, img_size=224, patch_size=16, in_chans=3, num_classes=1000, embed_dim=768, depth=12, num_heads=12,
+                 mlp_ratio=4., qkv_bias=False, qk_scale=None, drop_rate=0., attn_drop_rate=0., drop_path_rate=0.,
+                 hybrid_backbone=None, norm_layer=None, use_cls_tocken=True, norm_embed=False, pre_norm=True,
+                 res_score=False, init='trunc_norm', adapter="kron", **adapter_kw):
+        super().__init__()
+        if hybrid_backbone is not None or norm_embed or not use_cls_tocken or in_chans != 3:
+            raise NotImplementedError("hybrid backbone / norm_embed / no-cls-token / in_chans != 3 are not supported")
+        if drop_rate != 0. or drop_path_rate != 0.:
+            raise NotImplementedError("dropout / stochastic depth > 0 are not supported")
+        norm_layer = norm_layer or partial(nn.LayerNorm, eps=1e-6)
+        self.num_classes = num_classes
+        self.num_features = self.embed_dim = embed_dim
+        self.adapter_kind = adapter
+        self.patch_embed = PatchEmbed(img_size=img_size, patch_size=patch_size, in_chans=in_chans, embed_dim=embed_dim)
+        num_patches = self.patch_embed.num_patches
+        self.cls_token = nn.Parameter(torch.zeros(1, 1, embed_dim))
+        self.pos_embed = nn.Parameter(torch.zeros(1, num_patches + 1, embed_dim))
+        self.blocks = nn.ModuleList([
+            Block(dim=embed_dim, num_heads=num_heads, mlp_ratio=mlp_ratio, qkv_bias=qkv_bias, qk_scale=qk_scale,
+                  drop=drop_rate, attn_drop=attn_drop_rate, drop_path=0., norm_layer=norm_layer, pre_norm=pre_norm,
+                  res_score=res_score, adapter=adapter, **adapter_kw)
+            for _ in range(depth)])
+        self.norm = norm_layer(embed_dim)
+        self.head = nn.Linear(embed_dim, num_classes) if num_classes > 0 else nn.Identity()
+        nn.init.trunc_normal_(self.cls_token, std=.02)
+        nn.init.trunc_normal_(self.pos_embed, std=.02)
+        self.apply(self._init_weights_xavier if init == 'xavier' else self._init_weights_trunc_normal)
+        eps = self.norm.eps
+        if abs(eps - 1e-6) > 1e-12:
+            raise NotImplementedError("timm dialect uses LayerNorm eps 1e-6")
+        self._cfg = dict(img=img_size, patch=patch_size, width=embed_dim, depth=depth, heads=num_heads,
+                         mlp=int(embed_dim * mlp_ratio))
+        self._engine = None
+        self._frozen_sig = None
+
+    @staticmethod
+    def _init_weights_trunc_normal(m):
+        if isinstance(m, nn.Linear):
+            nn.init.trunc_normal_(m.weight, std=0.02)
+            if m.bias is not None:
+                nn.init.constant_(m.bias, 0)
+        elif isinstance(m, nn.LayerNorm):
+            nn.init.constant_(m.bias, 0)
+            nn.init.constant_(m.weight, 1.0)
+
+    @staticmethod
+    def _init_weights_xavier(m):
+        if isinstance(m, nn.Linear):
+            nn.init.xavier_uniform_(m.weight)
+            if m.bias is not None:
+                nn.init.constant_(m.bias, 0)
+        elif isinstance(m, nn.LayerNorm):
+            nn.init.constant_(m.bias, 0)
+            nn.init.constant_(m.weight, 1.0)
+
+    @torch.jit.ignore
+    def no_weight_decay(self):
+        return {'pos_embed', 'cls_token'}
+
+    # ---------------------------------------------------------------- adapter -> low-rank operands
+    _ADAPTER_KEYS = ("phm_rule", "W_left", "W_right", "phmb", "_proj_adapter")
+
+    def _rank(self):
+        a0 = self.blocks[0].attn
+        if self.adapter_kind == "kron":
+            n = a0.phm_rule.shape[0]
+            return 2 * n * a0.phm_rank * n
+        if self.adapter_kind == "lora":
+            return 2 * a0.lora_attn_dim
+        return 0
+
+    def lowrank_operands(self):
+        """Dn [depth, r', D], UpT [depth, r', 3D] built differentiably from the reference-named parameters."""
+        D = self.embed_dim
+        attns = [b.attn for b in self.blocks]
+        if self.adapter_kind == "kron":
+            rule = torch.stack([a.phm_rule for a in attns])
+            dq, uq = lowrank_factors_kron(rule, torch.stack([a.W_left1 for a in attns]), torch.stack([a.W_right1 for a in attns]))
+            dv, uv = lowrank_factors_kron(rule, torch.stack([a.W_left2 for a in attns]), torch.stack([a.W_right2 for a in attns]))
+        elif self.adapter_kind == "lora":
+            s = attns[0].lora_attn_alpha / attns[0].lora_attn_dim
+            dq = torch.stack([a.q_proj_adapter1.weight for a in attns])
+            dv = torch.stack([a.v_proj_adapter1.weight for a in attns])
+            uq = torch.stack([a.q_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
+            uv = torch.stack([a.v_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
+        else:
+            return None, None
+        z = torch.zeros_like(uq)
+        Dn = torch.cat([dq, dv], dim=1)
+        UpT = torch.cat([torch.cat([uq, z, z], dim=2), torch.cat([z, z, uv], dim=2)], dim=1)
+        return Dn, UpT
+
+    # ---------------------------------------------------------------- engine plumbing
+    def _frozen_items(self):
+        return [(k, v) for k, v in self.state_dict(keep_vars=True).items()
+                if not any(t in k for t in self._ADAPTER_KEYS) and not k.startswith("head.")]
+
+    def _ensure_engine(self, device):
+        items = self._frozen_items()
+        sig = tuple((k, v.data_ptr(), v._version) for k, v in items)
+        if self._engine is None or self._engine.dev != device:
+            self._engine = VitEngine(EngineCfg(dialect="timm", rank=self._rank(), **self._cfg), device)
+            self._frozen_sig = None
+        if sig != self._frozen_sig:
+            sd = dict(items)
+            if self.blocks[0].attn.qkv.bias is None:
+                for i in range(len(self.blocks)):
+                    sd[f"blocks.{i}.attn.qkv.bias"] = torch.zeros(3 * self.embed_dim)
+            self._engine.load_frozen(sd)
+            self._frozen_sig = sig
+        return self._engine
+
+    def forward_features(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
+        eng = self._ensure_engine(x.device)
+        Dn, UpT = self.lowrank_operands()
+        return backbone(eng, x, Dn, UpT)
+
+    def forward(self, x):
+        return self.forward_features(x)

@@ -1,0 +1,59 @@
+"""world_size-2 gloo test (CPU) of the flat gradient bucket: N-rank averaged gradients == gradients of the mean loss
+over the concatenated batch."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from peft_b200.dist import GradBucket
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(8, 3)
+    frozen = torch.nn.Linear(8, 8)
+    for p in frozen.parameters():
+        p.requires_grad_(False)
+    bucket = GradBucket(list(lin.parameters()) + list(frozen.parameters()))
+    assert bucket.numel == 8 * 3 + 3
+    x = torch.randn(6, 8, generator=torch.Generator().manual_seed(1))
+    y = torch.randn(6, 3, generator=torch.Generator().manual_seed(2))
+    xs, ys = x[rank * 3:(rank + 1) * 3], y[rank * 3:(rank + 1) * 3]
+    for _ in range(2):  # second iteration checks zero() keeps the views attached
+        bucket.zero()
+        loss = ((lin(frozen(xs)) - ys) ** 2).mean()
+        loss.backward()
+        bucket.check_attached()
+        bucket.all_reduce_mean()
+    got = [p.grad.clone() for p in lin.parameters()]
+    lin2 = torch.nn.Linear(8, 3)
+    lin2.load_state_dict(lin.state_dict())
+    ((lin2(frozen(x)) - y) ** 2).mean().backward()
+    ok = all(torch.allclose(a, b.grad, atol=1e-6) for a, b in zip(got, lin2.parameters()))
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_bucket_allreduce_two_ranks():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok in res), res
