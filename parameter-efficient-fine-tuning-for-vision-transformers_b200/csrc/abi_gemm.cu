@@ -1,6 +1,7 @@
 // C-ABI: peft_gemm_bf16 — host launcher of the tcgen05/TMA GEMM (gemm_sm100.cuh).
 #include "common.cuh"
 #include "gemm_sm100.cuh"
+#include "gemm2_sm100.cuh"
 
 namespace peft {
 
@@ -37,6 +38,70 @@ static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, c
     case EPI_RESID_BF16: return launch_gemm<BN, EPI_RESID_BF16>(ta, tb, p, s);
     default: return fail(PEFT_ERR_INVALID, "unknown epilogue %d", epi);
   }
+}
+
+// ---------------------------------------------------------------- 2-CTA kernel (gemm2_sm100.cuh)
+static std::atomic<int>& gemm_algo() {
+  static std::atomic<int> a{0};   // 0 = auto, 1 = force 1-CTA kernel, 2 = force 2-CTA kernel
+  return a;
+}
+
+template <int EPI>
+static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& to2,
+                        const CUtensorMap& tx, const GemmParams& p, cudaStream_t stream) {
+  auto kern = gemm2_bf16_tcgen05_kernel<EPI>;
+  static bool configured = false;
+  if (!configured) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2SmemBytes));
+    configured = true;
+  }
+  const int num_tiles = ((p.M + 2 * kBM - 1) / (2 * kBM)) * ((p.N + kG2BN - 1) / kG2BN);
+  const int max_clusters = sm_count() / 2;
+  const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters, 1, 1);
+  cfg.blockDim = dim3(kG2Threads, 1, 1);
+  cfg.dynamicSmemBytes = kG2SmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  PEFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, to, to2, tx, p));
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+static int dispatch_gemm2(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                          const CUtensorMap& to2, const CUtensorMap& tx, const GemmParams& p, cudaStream_t s) {
+  switch (epi) {
+    case EPI_STORE: return launch_gemm2<EPI_STORE>(ta, tb, to, to2, tx, p, s);
+    case EPI_GELU: return launch_gemm2<EPI_GELU>(ta, tb, to, to2, tx, p, s);
+    case EPI_QUICKGELU: return launch_gemm2<EPI_QUICKGELU>(ta, tb, to, to2, tx, p, s);
+    case EPI_RESID_F32: return launch_gemm2<EPI_RESID_F32>(ta, tb, to, to2, tx, p, s);
+    case EPI_DGELU: return launch_gemm2<EPI_DGELU>(ta, tb, to, to2, tx, p, s);
+    case EPI_DQUICKGELU: return launch_gemm2<EPI_DQUICKGELU>(ta, tb, to, to2, tx, p, s);
+    case EPI_STORE_F32: return launch_gemm2<EPI_STORE_F32>(ta, tb, to, to2, tx, p, s);
+    case EPI_RELU: return launch_gemm2<EPI_RELU>(ta, tb, to, to2, tx, p, s);
+    case EPI_DRELU: return launch_gemm2<EPI_DRELU>(ta, tb, to, to2, tx, p, s);
+    case EPI_GELU_TANH: return launch_gemm2<EPI_GELU_TANH>(ta, tb, to, to2, tx, p, s);
+    case EPI_DGELU_TANH: return launch_gemm2<EPI_DGELU_TANH>(ta, tb, to, to2, tx, p, s);
+    case EPI_RESID_BF16: return launch_gemm2<EPI_RESID_BF16>(ta, tb, to, to2, tx, p, s);
+    default: return fail(PEFT_ERR_INVALID, "unknown epilogue %d", epi);
+  }
+}
+
+// The 2-CTA kernel needs enough 256 x 256 tiles to fill the 74 SM pairs; small / narrow problems stay on the 1-CTA kernel.
+static bool use_gemm2(int M, int N) {
+  const int a = gemm_algo().load(std::memory_order_relaxed);
+  if (a == 1) return false;
+  if (a == 2) return true;
+  if (N < 256) return false;
+  const long long tiles = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  return tiles >= sm_count() / 2;
 }
 
 // Tile-width heuristic: widest tile that still gives >= ~2 waves over the SMs; narrow outputs get BN=32.
@@ -76,19 +141,45 @@ extern "C" int peft_gemm_bf16(const void* a, long long lda, const void* b, long 
   }
   if (bias) PEFT_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "peft_gemm_bf16: bias must be 16-byte aligned");
 
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
+  p.aux = aux; p.ldaux = ldaux;
+  if (use_gemm2(M, N)) {
+    CUtensorMap ta, tb, to, to2, tx;
+    int rc = make_tmap_2d(&ta, a, false, (unsigned long long)M, (unsigned long long)K, (unsigned long long)lda, kBM, 64);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tb, b, false, (unsigned long long)N, (unsigned long long)K, (unsigned long long)ldb, kG2BN / 2, 64);
+    if (rc) return rc;
+    rc = make_tmap_2d(&to, out, f32out, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldo, 32, f32out ? 32 : 64);
+    if (rc) return rc;
+    to2 = to; tx = to;
+    if (needs_out2) {
+      rc = make_tmap_2d(&to2, out2, false, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldo2, 32, 64);
+      if (rc) return rc;
+    }
+    if (needs_aux) {
+      const bool af32 = (epilogue == EPI_RESID_F32);
+      rc = make_tmap_2d(&tx, aux, af32, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldaux, 32, af32 ? 32 : 64);
+      if (rc) return rc;
+    }
+    return dispatch_gemm2(epilogue, ta, tb, to, to2, tx, p, s);
+  }
   const int bn = pick_bn(M, N);
   CUtensorMap ta, tb;
   int rc = make_tmap_bf16_2d(&ta, a, (unsigned long long)M, (unsigned long long)K, (unsigned long long)lda, kBM);
   if (rc) return rc;
   rc = make_tmap_bf16_2d(&tb, b, (unsigned long long)N, (unsigned long long)K, (unsigned long long)ldb, (unsigned)bn);
   if (rc) return rc;
-  GemmParams p;
-  p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
-  p.aux = aux; p.ldaux = ldaux;
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return dispatch_epi<256>(epilogue, ta, tb, p, s);
     case 128: return dispatch_epi<128>(epilogue, ta, tb, p, s);
     default: return dispatch_epi<32>(epilogue, ta, tb, p, s);
   }
+}
+
+extern "C" int peft_set_gemm_algo(int algo) {
+  PEFT_REQUIRE(algo >= 0 && algo <= 2, "peft_set_gemm_algo: algo must be 0 (auto), 1 (1-CTA) or 2 (2-CTA)");
+  gemm_algo().store(algo);
+  return 0;
 }

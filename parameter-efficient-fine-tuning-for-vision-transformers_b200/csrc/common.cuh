@@ -8,6 +8,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <unordered_map>
 #include "../../include/peft_b200.h"
 
 namespace peft {
@@ -73,23 +75,57 @@ inline EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// 2-D bf16 row-major [rows, cols] with row pitch ld (elements); box = box_rows x 64 columns, 128-byte swizzle.
-// Coordinates outside [rows, cols] are zero-filled by the hardware, which is what handles every M/N/K tail.
-inline int make_tmap_bf16_2d(CUtensorMap* tm, const void* ptr, unsigned long long rows, unsigned long long cols,
-                             unsigned long long ld, unsigned box_rows) {
+// 2-D row-major [rows, cols] tensor (bf16 or fp32) with row pitch ld (elements); box = box_rows x box_cols with
+// box_cols * elt == 128 bytes, 128-byte swizzle.  Loads outside [rows, cols] are zero-filled and stores are clipped by
+// the hardware, which is what handles every M/N/K tail.  Encoded maps are cached (the workspaces of the engine are
+// persistent, so a step re-uses the same few hundred maps): the key holds every encoded field, so a hit is always valid.
+struct TmapKey {
+  const void* ptr; unsigned long long rows, cols, ld; unsigned box_rows, box_cols; int f32;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows && box_cols == o.box_cols && f32 == o.f32;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows * 0x100000001B3ull) ^ (k.cols << 17) ^ (k.ld << 29) ^ ((size_t)k.box_rows << 7) ^ ((size_t)k.box_cols << 3) ^ (size_t)k.f32;
+    return h;
+  }
+};
+inline int make_tmap_2d(CUtensorMap* tm, const void* ptr, bool f32, unsigned long long rows, unsigned long long cols,
+                        unsigned long long ld, unsigned box_rows, unsigned box_cols) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+  const TmapKey key{ptr, rows, cols, ld, box_rows, box_cols, f32 ? 1 : 0};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *tm = it->second; return 0; }
+  }
   EncodeTiledFn fn = encode_tiled_fn();
+  const unsigned elt = f32 ? 4 : 2;
   if (fn == nullptr) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail(PEFT_ERR_INVALID, "TMA base pointer must be 16-byte aligned");
-  if ((ld * 2) % 16 != 0) return fail(PEFT_ERR_INVALID, "TMA row pitch must be a multiple of 16 bytes (ld=%llu)", ld);
+  if ((ld * elt) % 16 != 0) return fail(PEFT_ERR_INVALID, "TMA row pitch must be a multiple of 16 bytes (ld=%llu)", ld);
+  if (box_cols * elt != 128 || box_rows == 0 || box_rows > 256) return fail(PEFT_ERR_INVALID, "TMA box must be 128 bytes wide and <= 256 rows");
   cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {ld * 2};
-  cuuint32_t box[2] = {64, box_rows};
+  cuuint64_t strides[1] = {ld * elt};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  {
+    std::lock_guard<std::mutex> g(mu);
+    if (cache.size() > 16384) cache.clear();
+    cache.emplace(key, *tm);
+  }
   return 0;
+}
+inline int make_tmap_bf16_2d(CUtensorMap* tm, const void* ptr, unsigned long long rows, unsigned long long cols,
+                             unsigned long long ld, unsigned box_rows) {
+  return make_tmap_2d(tm, ptr, false, rows, cols, ld, box_rows, 64);
 }
 
 }  // namespace peft

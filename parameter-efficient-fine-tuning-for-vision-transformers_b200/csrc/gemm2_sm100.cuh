@@ -1,0 +1,458 @@
+// 2-CTA (cta_group::2) persistent bf16 GEMM for sm_100a:  C[M,N] = A[M,K] * B[N,K]^T  (+ fused epilogue)
+//
+// The main tensor-core kernel of the hot path (SURVEY.md §8a R3, R7, R8 and their dX products).  Compared with the
+// 1-CTA kernel of gemm_sm100.cuh it
+//   * pairs two SMs on one 256 x 256 output tile (tcgen05.mma.cta_group::2, M = 256): each CTA stages only its own
+//     128 rows of A and 128 of the 256 B rows per k-block (32 KB instead of 48 KB), i.e. 1.5x less L2->SM operand
+//     traffic per FLOP — the 1-CTA kernel measured at ~47 % of the MMA pace is bound by exactly that traffic;
+//   * moves ALL epilogue HBM traffic onto TMA: accumulators go TMEM -> registers -> 128B-swizzled shared-memory slots
+//     -> cp.async.bulk.tensor stores, and the epilogue's auxiliary operand (residual stream / saved pre-activation) is
+//     prefetched by TMA into the same slots before the accumulator is ready.  Row-per-lane global accesses (32 sectors
+//     per warp instruction) are gone; M/N tails are clipped (stores) or zero-filled (loads) by the TMA unit;
+//   * evaluates the activations with MUFU-based forms (ex2 / rcp / tanh) so that the per-tile epilogue stays under
+//     the per-tile MMA time at K = 768.
+//
+// Roles (384 threads): warp 0 = TMA producer (both CTAs), warp 1 = MMA issuer (leader CTA only), warp 2 = TMEM
+// allocator, warps 4..11 = epilogue (TMEM lane quarter = warp % 4, column half = (warp - 4) / 4).
+// Barriers: full/empty per smem stage (full lives in the LEADER: both CTAs' TMA loads complete on it), tmem_full /
+// tmem_empty per accumulator buffer (tmem_empty in the leader collects 16 warp arrivals from both CTAs), one aux
+// barrier per epilogue slot.
+#pragma once
+#include "gemm_sm100.cuh"
+
+namespace peft {
+
+constexpr int kG2Stages = 5;
+constexpr int kG2BN = 256;                       // tile columns; the CTA pair computes 256 (M) x 256 (N)
+constexpr int kG2StageBytes = 2 * kBM * kBK * 2; // A [128 x 64] + B half [128 x 64] bf16 = 32 KB
+constexpr int kG2Threads = 128 + kEpiWarps * 32;
+constexpr int kG2SlotBytes = 32 * 128;           // 32 rows x 128 B
+constexpr int kG2EpiBytes = kEpiWarps * 2 * kG2SlotBytes;
+constexpr int kG2BarBytes = 512;
+constexpr int kG2SmemBytes = kG2Stages * kG2StageBytes + kG2EpiBytes + kG2BarBytes + 1024 /*align slack*/;
+
+namespace ptx {
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP_C:\n"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE_C;\n"
+      "bra WAIT_LOOP_C;\n"
+      "WAIT_DONE_C:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// TMA load issued by either CTA of the pair; completion (bytes) is signalled on `bar_cluster_addr`, which may live in
+// the peer (leader) CTA.
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* tm, uint32_t bar_cluster_addr, int c0,
+                                                int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_slot) {  // one whole warp in EACH CTA of the pair
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrive on the mbarrier at this shared-memory offset in every CTA of `mask` once all prior MMAs have completed.
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+}  // namespace ptx
+
+// ---- MUFU-based activations.  Phi(x) = sigmoid(2 x q(x^2)) with q fitted to atanh(erf(x / sqrt 2)) / x:
+// max |x Phi_fit(x) - gelu_erf(x)| = 2.6e-5 over the reals (a bf16 ulp at |gelu| ~ 1 is 3.9e-3).
+__device__ __forceinline__ float phi_u(float x) {  // returns u = x q(x^2); Phi = sigmoid(2u) = 0.5 + 0.5 tanh(u)
+  const float s = fminf(x * x, 50.0f);   // q peaks at s = 52; beyond |x| = 7 the sigmoid is saturated anyway
+  return x * fmaf(s, fmaf(s, -3.53110710e-4f, 3.70155061e-2f), 7.97496957e-1f);
+}
+__device__ __forceinline__ float fast_gelu_erf(float x) {
+  const float e = ptx::ex2_approx(-2.8853900817779268f * phi_u(x));   // exp(-2u)
+  return x * ptx::rcp_approx(1.0f + e);
+}
+__device__ __forceinline__ float fast_dgelu_erf(float x) {
+  const float cdf = fmaf(0.5f, ptx::tanh_approx(phi_u(x)), 0.5f);
+  const float pdf = 0.3989422804014327f * ptx::ex2_approx(-0.72134752044448170f * x * x);
+  return fmaf(x, pdf, cdf);
+}
+__device__ __forceinline__ float fast_quickgelu(float x) {
+  return x * ptx::rcp_approx(1.0f + ptx::ex2_approx(-2.4554669595930156f * x));   // 1.702 * log2(e)
+}
+__device__ __forceinline__ float fast_dquickgelu(float x) {
+  const float s = ptx::rcp_approx(1.0f + ptx::ex2_approx(-2.4554669595930156f * x));
+  return s * fmaf(1.702f * x, 1.0f - s, 1.0f);
+}
+__device__ __forceinline__ float fast_gelu_tanh(float x) {
+  const float u = 0.7978845608028654f * fmaf(0.044715f * x * x, x, x);
+  return x * ptx::rcp_approx(1.0f + ptx::ex2_approx(-2.8853900817779268f * u));
+}
+__device__ __forceinline__ float fast_dgelu_tanh(float x) {
+  const float x2 = x * x;
+  const float u = 0.7978845608028654f * fmaf(0.044715f * x2, x, x);
+  const float t = ptx::tanh_approx(u);
+  const float du = 0.7978845608028654f * fmaf(0.134145f, x2, 1.0f);
+  return fmaf(0.5f * x * (1.0f - t * t), du, fmaf(0.5f, t, 0.5f));
+}
+
+template <int EPI>
+struct EpiTraits {
+  static constexpr bool kF32Out = (EPI == EPI_RESID_F32 || EPI == EPI_STORE_F32);
+  static constexpr bool kAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_DQUICKGELU || EPI == EPI_DRELU ||
+                                EPI == EPI_DGELU_TANH || EPI == EPI_RESID_BF16);
+  static constexpr bool kDual = (EPI == EPI_GELU || EPI == EPI_QUICKGELU || EPI == EPI_GELU_TANH);
+  static constexpr int kUnitCols = kF32Out ? 32 : 64;    // columns per 128-byte slot row
+  static constexpr int kUnits = 128 / kUnitCols;         // units per warp per tile (the warp owns 128 columns)
+};
+
+// 16-byte chunk j of row `lane` inside a 128B-swizzled [32 x 128 B] slot (the layout TMA expects for SWIZZLE_128B).
+__device__ __forceinline__ uint32_t slot_off(int lane, int j) { return (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4)); }
+
+template <int EPI>
+__global__ void __launch_bounds__(kG2Threads, 1)
+gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                          const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
+                          const __grid_constant__ CUtensorMap tmap_aux, const GemmParams p) {
+  using T = EpiTraits<EPI>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* tiles = smem;
+  uint8_t* epi_smem = smem + kG2Stages * kG2StageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_smem + kG2EpiBytes);
+  uint64_t* empty_bar = full_bar + kG2Stages;
+  uint64_t* tmem_full_bar = empty_bar + kG2Stages;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;      // [2]
+  uint64_t* aux_bar = tmem_empty_bar + 2;            // [kEpiWarps][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 2 * kEpiWarps);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = ptx::cluster_ctarank();
+  const bool leader = cta_rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    ptx::prefetch_tmap(&tmap_out);
+    if constexpr (T::kDual) ptx::prefetch_tmap(&tmap_out2);
+    if constexpr (T::kAux) ptx::prefetch_tmap(&tmap_aux);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kG2Stages; ++i) {
+      ptx::mbar_init(&full_bar[i], 1);    // leader producer's arrive.expect_tx (used in the leader only)
+      ptx::mbar_init(&empty_bar[i], 1);   // one multicast tcgen05.commit
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tmem_full_bar[i], 1);
+      ptx::mbar_init(&tmem_empty_bar[i], 2 * kEpiWarps);   // every epilogue warp of both CTAs (leader's copy is used)
+    }
+    for (int i = 0; i < 2 * kEpiWarps; ++i) ptx::mbar_init(&aux_bar[i], 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_2sm<512>(tmem_slot);
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();               // peer barriers initialised + peer TMEM allocated before any cross-CTA traffic
+  ptx::tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_mp = (p.M + 2 * kBM - 1) / (2 * kBM);     // 256-row pair tiles
+  const int num_n = (p.N + kG2BN - 1) / kG2BN;
+  const int num_tiles = num_mp * num_n;
+  const int num_kb = (p.K + kBK - 1) / kBK;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  if (warp == 0) {
+    // ===================== TMA producer (one lane, both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int mp = tile / num_n, n_blk = tile % num_n;
+        const int row_a = mp * 2 * kBM + (int)cta_rank * kBM;
+        const int row_b = n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = tiles + stage * kG2StageBytes;
+          uint8_t* sb = sa + kBM * kBK * 2;
+          const uint32_t bar = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+          if (leader) ptx::mbar_expect_tx(&full_bar[stage], 2 * kG2StageBytes);
+          ptx::tma_load_2d_2sm(sa, &tmap_a, bar, kb * kBK, row_a);
+          ptx::tma_load_2d_2sm(sb, &tmap_b, bar, kb * kBK, row_b);
+          if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one lane of the leader CTA) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kG2BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
+        ptx::tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kG2BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait_cluster(&full_bar[stage], phase);
+          ptx::tcgen05_fence_after();
+          const uint32_t sa = ptx::smem_u32(tiles + stage * kG2StageBytes);
+          const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
+          const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + kBM * kBK * 2);
+          const int krem = p.K - kb * kBK;
+          const int ksteps = krem >= kBK ? (kBK / 16) : ((krem + 15) / 16);
+          for (int k = 0; k < ksteps; ++k)
+            ptx::umma_bf16_2sm(tmem_d, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k), idesc,
+                               (kb | k) != 0 ? 1u : 0u);
+          ptx::umma_commit_2sm(&empty_bar[stage], 3);       // frees this smem slot in both CTAs
+          if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
+        }
+        ptx::umma_commit_2sm(&tmem_full_bar[acc], 3);       // accumulator complete -> both CTAs' epilogues
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue warps =====================
+    const int ew = warp - 4;
+    const int quarter = warp & 3;
+    const int half = ew >> 2;
+    uint8_t* const slot_base = epi_smem + ew * 2 * kG2SlotBytes;
+    auto slot_ptr = [&](int s) { return slot_base + s * kG2SlotBytes; };
+    uint64_t* abar = aux_bar + 2 * ew;
+    uint32_t aux_phase = 0;   // bit s = parity of slot s
+    const uint32_t tmem_empty_remote0 = ptx::mapa(ptx::smem_u32(&tmem_empty_bar[0]), 0);
+    const uint32_t tmem_empty_remote1 = ptx::mapa(ptx::smem_u32(&tmem_empty_bar[1]), 0);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int mp = tile / num_n, n_blk = tile % num_n;
+      const int row0 = mp * 2 * kBM + (int)cta_rank * kBM + quarter * 32;   // first row of this warp's 32-row slab
+      const int col0 = n_blk * kG2BN + half * 128;                          // first of this warp's 128 columns
+      if constexpr (T::kAux) {
+        // prefetch the auxiliary operand of units 0 and 1 (independent of the accumulator)
+        if (lane == 0) {
+          ptx::bulk_wait_read<0>();                   // previous tile's stores have released both slots
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            ptx::mbar_expect_tx(&abar[s], kG2SlotBytes);
+            ptx::tma_load_2d(slot_ptr(s), &tmap_aux, &abar[s], col0 + s * T::kUnitCols, row0);
+          }
+        }
+      }
+      ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+      ptx::tcgen05_fence_after();
+      const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                              static_cast<uint32_t>(acc * kG2BN + half * 128);
+#pragma unroll 1
+      for (int u = 0; u < T::kUnits; ++u) {
+        const int s = u & 1;
+        const int colu = col0 + u * T::kUnitCols;
+        float v[T::kUnitCols];
+        {
+          uint32_t r[32];
+          ptx::tmem_ld_32x32b_x32(taddr0 + u * T::kUnitCols, r);
+          if constexpr (T::kUnitCols == 64) {
+            uint32_t r2[32];
+            ptx::tmem_ld_32x32b_x32(taddr0 + u * T::kUnitCols + 32, r2);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r[j]); v[32 + j] = __uint_as_float(r2[j]); }
+          } else {
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          }
+        }
+        if (u == T::kUnits - 1) {
+          // all of this warp's accumulator reads are done: hand the TMEM buffer back to the MMA issuer
+          ptx::tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive_cluster(acc ? tmem_empty_remote1 : tmem_empty_remote0);
+        }
+        if (p.bias != nullptr) {
+          if (colu + T::kUnitCols <= p.N) {
+#pragma unroll
+            for (int j = 0; j < T::kUnitCols; j += 4) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + colu + j));
+              v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < T::kUnitCols; ++j)
+              if (colu + j < p.N) v[j] += __ldg(p.bias + colu + j);
+          }
+        }
+        // ---- slot availability / auxiliary operand
+        if constexpr (T::kAux) {
+          ptx::mbar_wait(&abar[s], (aux_phase >> s) & 1u);
+          aux_phase ^= (1u << s);
+          if constexpr (EPI == EPI_RESID_F32) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 a = *reinterpret_cast<const float4*>(slot_ptr(s) + slot_off(lane, j));
+              v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint4 a = *reinterpret_cast<const uint4*>(slot_ptr(s) + slot_off(lane, j));
+              const uint32_t au[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float2 h = ptx::unpack_bf16x2(au[q]);
+                float& v0 = v[8 * j + 2 * q];
+                float& v1 = v[8 * j + 2 * q + 1];
+                if constexpr (EPI == EPI_DGELU) { v0 *= fast_dgelu_erf(h.x); v1 *= fast_dgelu_erf(h.y); }
+                if constexpr (EPI == EPI_DQUICKGELU) { v0 *= fast_dquickgelu(h.x); v1 *= fast_dquickgelu(h.y); }
+                if constexpr (EPI == EPI_DGELU_TANH) { v0 *= fast_dgelu_tanh(h.x); v1 *= fast_dgelu_tanh(h.y); }
+                if constexpr (EPI == EPI_DRELU) { v0 = h.x > 0.f ? v0 : 0.f; v1 = h.y > 0.f ? v1 : 0.f; }
+                if constexpr (EPI == EPI_RESID_BF16) { v0 += h.x; v1 += h.y; }
+              }
+            }
+          }
+          __syncwarp();   // every lane has read its aux row before anyone overwrites the slot
+        } else if constexpr (T::kDual) {
+          if (lane == 0) ptx::bulk_wait_read<0>();   // both slots are rewritten by this unit
+          __syncwarp();
+        } else {
+          if (lane == 0) ptx::bulk_wait_read<1>();   // the store issued two units ago (same slot) has been read
+          __syncwarp();
+        }
+        if constexpr (EPI == EPI_RELU) {
+#pragma unroll
+          for (int j = 0; j < T::kUnitCols; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        // ---- registers -> swizzled slot
+        if constexpr (T::kF32Out) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(slot_ptr(s) + slot_off(lane, j)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        } else {
+          uint8_t* dst = T::kDual ? slot_ptr(0) : slot_ptr(s);
+          uint32_t pk[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) pk[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(dst + slot_off(lane, j)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          if constexpr (T::kDual) {
+            // activation of the bf16-ROUNDED pre-activation: backward differentiates exactly what forward evaluated
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float2 h = ptx::unpack_bf16x2(pk[j]);
+              float a0, a1;
+              if constexpr (EPI == EPI_GELU) { a0 = fast_gelu_erf(h.x); a1 = fast_gelu_erf(h.y); }
+              else if constexpr (EPI == EPI_QUICKGELU) { a0 = fast_quickgelu(h.x); a1 = fast_quickgelu(h.y); }
+              else { a0 = fast_gelu_tanh(h.x); a1 = fast_gelu_tanh(h.y); }
+              pk[j] = ptx::pack_bf16x2(a0, a1);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *reinterpret_cast<uint4*>(slot_ptr(1) + slot_off(lane, j)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          }
+        }
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (T::kDual) {
+            ptx::tma_store_2d(&tmap_out, slot_ptr(0), colu, row0);
+            ptx::tma_store_2d(&tmap_out2, slot_ptr(1), colu, row0);
+          } else {
+            ptx::tma_store_2d(&tmap_out, slot_ptr(s), colu, row0);
+          }
+          ptx::bulk_commit();
+          if constexpr (T::kAux) {
+            if (u + 2 < T::kUnits) {
+              ptx::bulk_wait_read<0>();               // the store just issued has drained the slot
+              ptx::mbar_expect_tx(&abar[s], kG2SlotBytes);
+              ptx::tma_load_2d(slot_ptr(s), &tmap_aux, &abar[s], col0 + (u + 2) * T::kUnitCols, row0);
+            }
+          }
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+    if (lane == 0) ptx::bulk_wait<0>();   // all global writes of this warp are complete before the CTA exits
+  }
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();                    // the peer may still be multicasting into / reading from this CTA
+  if (warp == 2) ptx::tmem_dealloc_2sm<512>(tmem_base);
+}
+
+}  // namespace peft

@@ -10,6 +10,10 @@
 
 static float bf16r(float x) { return __bfloat162float(__float2bfloat16(x)); }
 static double gelu(double x) { return 0.5 * x * (1.0 + erf(x / sqrt(2.0))); }
+static double qgelu(double x) { return x / (1.0 + exp(-1.702 * x)); }
+static double dqgelu(double x) { double s = 1.0 / (1.0 + exp(-1.702 * x)); return s * (1.0 + 1.702 * x * (1.0 - s)); }
+static double tgelu(double x) { return 0.5 * x * (1.0 + tanh(sqrt(2.0 / M_PI) * (x + 0.044715 * x * x * x))); }
+static double dtgelu(double x) { double u = sqrt(2.0 / M_PI) * (x + 0.044715 * x * x * x), t = tanh(u); return 0.5 * (1 + t) + 0.5 * x * (1 - t * t) * sqrt(2.0 / M_PI) * (1 + 3 * 0.044715 * x * x); }
 static double dgelu(double x) { return 0.5 * (1.0 + erf(x / sqrt(2.0))) + x * exp(-0.5 * x * x) / sqrt(2.0 * M_PI); }
 
 struct Case { int M, N, K, epi; int lda_pad; };
@@ -65,6 +69,12 @@ int run_case(const Case& c, bool timeit) {
       case PEFT_EPI_STORE_F32: got = hOf[(size_t)i * N + j]; break;
       case PEFT_EPI_DGELU: ref = acc * dgelu(h); got = __bfloat162float(hO[(size_t)i * N + j]); break;
       case PEFT_EPI_RESID_BF16: ref = acc + h; got = __bfloat162float(hO[(size_t)i * N + j]); break;
+      case PEFT_EPI_QUICKGELU: got = __bfloat162float(hO[(size_t)i * N + j]); two = true; ref2 = qgelu(bf16r((float)acc)); got2 = __bfloat162float(hO2[(size_t)i * N + j]); break;
+      case PEFT_EPI_GELU_TANH: got = __bfloat162float(hO[(size_t)i * N + j]); two = true; ref2 = tgelu(bf16r((float)acc)); got2 = __bfloat162float(hO2[(size_t)i * N + j]); break;
+      case PEFT_EPI_DQUICKGELU: ref = acc * dqgelu(h); got = __bfloat162float(hO[(size_t)i * N + j]); break;
+      case PEFT_EPI_DGELU_TANH: ref = acc * dtgelu(h); got = __bfloat162float(hO[(size_t)i * N + j]); break;
+      case PEFT_EPI_RELU: ref = acc > 0 ? acc : 0; got = __bfloat162float(hO[(size_t)i * N + j]); break;
+      case PEFT_EPI_DRELU: ref = h > 0 ? acc : 0; got = __bfloat162float(hO[(size_t)i * N + j]); break;
       default: got = ref;
     }
     const double tol = f32 ? 2e-3 : 2e-2;
@@ -90,14 +100,22 @@ int run_case(const Case& c, bool timeit) {
 
 int main(int argc, char** argv) {
   const bool timeit = argc > 1;
+  const int algo = argc > 2 ? atoi(argv[2]) : 0;
+  if (peft_set_gemm_algo(algo)) { printf("bad algo\n"); return 2; }
+  printf("== gemm self-test, algo=%d (0 auto, 1 = 1-CTA, 2 = 2-CTA)\n", algo);
   std::vector<Case> cases = {
       {128, 128, 64, PEFT_EPI_STORE, 0},   {128, 256, 128, PEFT_EPI_STORE, 0}, {256, 128, 768, PEFT_EPI_STORE, 0},
       {1000, 768, 768, PEFT_EPI_STORE, 0}, {1576, 2304, 800, PEFT_EPI_STORE, 32}, {1576, 32, 768, PEFT_EPI_STORE, 0},
       {1576, 16, 768, PEFT_EPI_STORE, 0},  {777, 200, 72, PEFT_EPI_STORE, 8},
       {1576, 3072, 768, PEFT_EPI_GELU, 0}, {1576, 768, 3072, PEFT_EPI_RESID_F32, 0}, {1576, 3072, 768, PEFT_EPI_DGELU, 0},
       {1576, 768, 768, PEFT_EPI_STORE_F32, 0}, {1576, 768, 768, PEFT_EPI_RESID_BF16, 0},
+      {1576, 3072, 768, PEFT_EPI_QUICKGELU, 0}, {1576, 3072, 768, PEFT_EPI_DQUICKGELU, 0}, {1576, 3072, 768, PEFT_EPI_GELU_TANH, 0},
+      {1576, 3072, 768, PEFT_EPI_DGELU_TANH, 0}, {1576, 1024, 768, PEFT_EPI_RELU, 0}, {1576, 1024, 768, PEFT_EPI_DRELU, 0},
+      {6304, 768, 768, PEFT_EPI_RESID_F32, 0}, {300, 520, 264, PEFT_EPI_STORE, 0},
       {50432, 2304, 800, PEFT_EPI_STORE, 0}, {50432, 3072, 768, PEFT_EPI_GELU, 0}, {50432, 768, 3072, PEFT_EPI_RESID_F32, 0},
       {50432, 768, 768, PEFT_EPI_STORE, 0}, {50432, 768, 2336, PEFT_EPI_STORE, 0}, {50432, 3072, 768, PEFT_EPI_DGELU, 0},
+      {50432, 768, 768, PEFT_EPI_RESID_F32, 0}, {50432, 768, 3072, PEFT_EPI_STORE, 0}, {32896, 4096, 1024, PEFT_EPI_QUICKGELU, 0},
+      {8192, 8192, 8192, PEFT_EPI_STORE, 0},
   };
   int fails = 0;
   for (auto& c : cases) fails += run_case(c, timeit);
