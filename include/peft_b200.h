@@ -43,6 +43,8 @@ unsigned long long peft_launch_count(void);
 /* tuning / test knob: which tensor-core GEMM kernel peft_gemm_bf16 uses — 0 = automatic (2-CTA cta_group::2 kernel when
  * the problem fills the 74 SM pairs, else the 1-CTA kernel), 1 = always 1-CTA, 2 = always 2-CTA. */
 int peft_set_gemm_algo(int algo);
+/* same for the attention kernels: 0 = automatic (tcgen05/TMEM kernels for L <= 272), 1 = mma.sync kernels, 2 = tcgen05 */
+int peft_set_attention_algo(int algo);
 
 /* C[M,N] = A[M,K] * B[N,K]^T with fused epilogue, bf16 operands, fp32 accumulate in TMEM (tcgen05 + TMA).
  * replaces: F.linear / nn.Linear on the hot path —

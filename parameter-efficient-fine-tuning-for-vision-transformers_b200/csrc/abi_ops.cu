@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "ln_sm100.cuh"
 #include "attention_sm100.cuh"
+#include "attention2_sm100.cuh"
 #include "reduce_sm100.cuh"
 
 using namespace peft;
@@ -88,6 +89,41 @@ static int attn_check(const AttnParams& p) {
   return 0;
 }
 
+static std::atomic<int>& attn_algo() {
+  static std::atomic<int> a{0};   // 0 = auto (tcgen05 kernels), 1 = mma.sync v1 kernels, 2 = tcgen05 kernels
+  return a;
+}
+extern "C" int peft_set_attention_algo(int algo) {
+  PEFT_REQUIRE(algo >= 0 && algo <= 2, "peft_set_attention_algo: algo must be 0 (auto), 1 (mma.sync) or 2 (tcgen05)");
+  attn_algo().store(algo);
+  return 0;
+}
+
+template <int NK>
+static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long ldo, float* lse2, int B, int H, int L,
+                            float scale, cudaStream_t s) {
+  using C = Attn2Cfg<NK>;
+  CUtensorMap tq, tkv, to;
+  int rc = make_tmap_bf16_3d(&tq, qkv, B, L, 3ull * H * 64, ldqkv, 128);
+  if (rc) return rc;
+  rc = make_tmap_bf16_3d(&tkv, qkv, B, L, 3ull * H * 64, ldqkv, C::kKVBox);
+  if (rc) return rc;
+  rc = make_tmap_bf16_3d(&to, o, B, L, 1ull * H * 64, ldo, 128);
+  if (rc) return rc;
+  auto kern = attn2_fwd_kernel<NK>;
+  static bool configured = false;
+  if (!configured) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    configured = true;
+  }
+  Attn2Params p{};
+  p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
+  const int grid = B * H < sm_count() ? B * H : sm_count();
+  kern<<<grid, kA2Threads, C::kSmemBytes, s>>>(tq, tkv, to, p);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, long long ldo, float* lse2, int B, int H,
                                   int L, float scale, void* stream) {
   AttnParams p{};
@@ -96,6 +132,12 @@ extern "C" int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, lon
   int rc = attn_check(p);
   if (rc) return rc;
   PEFT_REQUIRE(o && lse2 && ldo % 8 == 0 && aligned16(o), "peft_attention_fwd: bad output");
+  if (attn_algo().load() != 1 && L <= 272) {
+    cudaStream_t s2 = reinterpret_cast<cudaStream_t>(stream);
+    if (L <= 64) return launch_attn2_fwd<64>(qkv, ldqkv, o, ldo, lse2, B, H, L, scale, s2);
+    if (L <= 208) return launch_attn2_fwd<208>(qkv, ldqkv, o, ldo, lse2, B, H, L, scale, s2);
+    return launch_attn2_fwd<272>(qkv, ldqkv, o, ldo, lse2, B, H, L, scale, s2);
+  }
   const int Lp = attn_lp(L);
   const int smem = (64 + 2 * Lp) * 128;
   static int configured = 0;

@@ -123,6 +123,39 @@ inline int make_tmap_2d(CUtensorMap* tm, const void* ptr, bool f32, unsigned lon
   }
   return 0;
 }
+// 3-D bf16 view [batch, rows, cols] of a row-major [batch*rows, ld] buffer (batch stride = rows * ld): box =
+// 1 x box_rows x 64 columns.  Used by the attention kernels: a (batch, head) tile never crosses into the next batch
+// element because rows >= `rows` are out of bounds in dimension 1 (zero-filled on load, clipped on store).
+inline int make_tmap_bf16_3d(CUtensorMap* tm, const void* ptr, unsigned long long batch, unsigned long long rows,
+                             unsigned long long cols, unsigned long long ld, unsigned box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+  const TmapKey key{ptr, rows, cols, ld, box_rows, (unsigned)batch, 3};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *tm = it->second; return 0; }
+  }
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail(PEFT_ERR_INVALID, "TMA base pointer must be 16-byte aligned");
+  if ((ld * 2) % 16 != 0) return fail(PEFT_ERR_INVALID, "TMA row pitch must be a multiple of 16 bytes (ld=%llu)", ld);
+  if (box_rows == 0 || box_rows > 256) return fail(PEFT_ERR_INVALID, "TMA box rows must be in [1, 256]");
+  cuuint64_t dims[3] = {cols, rows, batch};
+  cuuint64_t strides[2] = {ld * 2, rows * ld * 2};
+  cuuint32_t box[3] = {64, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed with CUresult %d", (int)r);
+  {
+    std::lock_guard<std::mutex> g(mu);
+    if (cache.size() > 16384) cache.clear();
+    cache.emplace(key, *tm);
+  }
+  return 0;
+}
 inline int make_tmap_bf16_2d(CUtensorMap* tm, const void* ptr, unsigned long long rows, unsigned long long cols,
                              unsigned long long ld, unsigned box_rows) {
   return make_tmap_2d(tm, ptr, false, rows, cols, ld, box_rows, 64);

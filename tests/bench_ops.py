@@ -1,0 +1,84 @@
+"""Micro-benchmarks (not a test): CUDA-event timing of individual C-ABI ops at the headline shapes.
+
+    python tests/bench_ops.py attn|ln|reduce|all
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from peft_b200 import _lib, ops
+
+
+def timeit(fn, iters=20, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3  # us
+
+
+def bench_attn(B=256, H=12, L=197):
+    D = H * 64
+    g = torch.Generator(device="cuda").manual_seed(0)
+    qkv = torch.randn(B * L, 3 * D, device="cuda", generator=g).to(torch.bfloat16)
+    o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+    d_o = torch.randn(B * L, D, device="cuda", generator=g).to(torch.bfloat16)
+    dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * L, device="cuda")
+    delta = torch.empty(B * H * L, device="cuda")
+    scale = 64 ** -0.5
+    flops_f = 4.0 * B * H * L * L * 64
+    for algo in (1, 2):
+        _lib.check(_lib.load().peft_set_attention_algo(algo))
+        tf = timeit(lambda: ops.attention_fwd(qkv, o, lse2, B, H, L, scale))
+        tb = timeit(lambda: ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, scale))
+        print(f"attention B={B} H={H} L={L} algo={algo}: fwd {tf:8.1f} us ({flops_f / tf / 1e6:6.1f} TFLOP/s)  "
+              f"bwd {tb:8.1f} us ({2.5 * flops_f / tb / 1e6:6.1f} TFLOP/s)", flush=True)
+    _lib.load().peft_set_attention_algo(0)
+
+
+def bench_ln(M=50432, D=768):
+    x = torch.randn(M, D, device="cuda")
+    gamma = torch.ones(D, device="cuda")
+    beta = torch.zeros(D, device="cuda")
+    y = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+    mean = torch.empty(M, device="cuda")
+    rstd = torch.empty(M, device="cuda")
+    t = timeit(lambda: ops.layernorm_fwd(x, gamma, beta, y, mean, rstd, 1e-6))
+    print(f"ln_fwd  M={M} D={D}: {t:7.1f} us  {(M * D * 6) / t / 1e3:7.1f} GB/s")
+    dy = torch.randn(M, D, device="cuda").to(torch.bfloat16)
+    gi = torch.randn(M, D, device="cuda").to(torch.bfloat16)
+    go = torch.empty_like(gi)
+    t = timeit(lambda: ops.layernorm_bwd(dy, x, mean, rstd, gamma, gi, go))
+    print(f"ln_bwd  M={M} D={D}: {t:7.1f} us  {(M * D * 10) / t / 1e3:7.1f} GB/s")
+
+
+def bench_reduce(M=50432):
+    wide = torch.randn(M, 800, device="cuda").to(torch.bfloat16)
+    y = torch.randn(M, 2304, device="cuda").to(torch.bfloat16)
+    out = torch.zeros(32, 2304, device="cuda")
+    t = timeit(lambda: ops.tn_reduce(wide[:, 768:800], y, out))
+    print(f"tn_reduce I=32 J=2304 M={M}: {t:7.1f} us  {(M * (2304 + 32) * 2) / t / 1e3:7.1f} GB/s")
+    out2 = torch.zeros(32, 768, device="cuda")
+    t = timeit(lambda: ops.tn_reduce(y[:, :32], wide[:, :768], out2))
+    print(f"tn_reduce I=32 J=768  M={M}: {t:7.1f} us  {(M * (768 + 32) * 2) / t / 1e3:7.1f} GB/s")
+
+
+if __name__ == "__main__":
+    what = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if what in ("attn", "all"):
+        bench_attn()
+        bench_attn(128, 16, 257)
+        bench_attn(256, 12, 50)
+    if what in ("ln", "all"):
+        bench_ln()
+    if what in ("reduce", "all"):
+        bench_reduce()
