@@ -3,6 +3,7 @@
 #include "ln_sm100.cuh"
 #include "attention_sm100.cuh"
 #include "attention2_sm100.cuh"
+#include "attention2_bwd_sm100.cuh"
 #include "reduce_sm100.cuh"
 
 using namespace peft;
@@ -151,6 +152,38 @@ extern "C" int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, lon
   return 0;
 }
 
+template <int NKC, int NCH>
+static int launch_attn2_bwd(const void* qkv, long long ldqkv, const void* o, long long ldo, const void* d_o, long long lddo,
+                            const float* lse2, float* delta, void* dqkv, long long lddqkv, int B, int H, int L, float scale,
+                            cudaStream_t s) {
+  using C = Attn2BwdCfg<NKC, NCH>;
+  const unsigned long long D = 64ull * H;
+  CUtensorMap t128, tchunk, tdo128, tdochunk, to128, tout;
+  int rc;
+  if ((rc = make_tmap_bf16_3d(&t128, qkv, B, L, 3 * D, ldqkv, 128))) return rc;
+  if ((rc = make_tmap_bf16_3d(&tchunk, qkv, B, L, 3 * D, ldqkv, NKC))) return rc;
+  if ((rc = make_tmap_bf16_3d(&tdo128, d_o, B, L, D, lddo, 128))) return rc;
+  if ((rc = make_tmap_bf16_3d(&tdochunk, d_o, B, L, D, lddo, NKC))) return rc;
+  if ((rc = make_tmap_bf16_3d(&to128, o, B, L, D, ldo, 128))) return rc;
+  if ((rc = make_tmap_bf16_3d(&tout, dqkv, B, L, 3 * D, lddqkv, 128))) return rc;
+  auto kdq = attn2_bwd_dq_kernel<NKC, NCH>;
+  auto kdkv = attn2_bwd_dkv_kernel<NKC, NCH>;
+  static bool configured = false;
+  if (!configured) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kdq, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kDqSmemBytes));
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kdkv, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kDkvSmemBytes));
+    configured = true;
+  }
+  Attn2Params p{};
+  p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale;
+  const int grid = B * H < sm_count() ? B * H : sm_count();
+  kdq<<<grid, kA2Threads, C::kDqSmemBytes, s>>>(t128, tchunk, tdo128, to128, tout, p);
+  PEFT_LAUNCH_CHECK();
+  kdkv<<<grid, kA2Threads, C::kDkvSmemBytes, s>>>(t128, tchunk, tdochunk, tout, p);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* o, long long ldo, const void* d_o,
                                   long long lddo, const float* lse2, float* delta, void* dqkv, long long lddqkv, int B,
                                   int H, int L, float scale, void* stream) {
@@ -164,6 +197,12 @@ extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* 
   PEFT_REQUIRE(o && d_o && lse2 && delta && dqkv, "peft_attention_bwd: null operand");
   PEFT_REQUIRE(ldo % 8 == 0 && lddo % 8 == 0 && lddqkv % 8 == 0 && aligned16(o) && aligned16(d_o) && aligned16(dqkv),
                "peft_attention_bwd: operands must be 16-byte aligned with pitch % 8 == 0");
+  if (attn_algo().load() != 1 && L <= 288) {
+    cudaStream_t s2 = reinterpret_cast<cudaStream_t>(stream);
+    if (L <= 64) return launch_attn2_bwd<64, 1>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
+    if (L <= 208) return launch_attn2_bwd<208, 1>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
+    return launch_attn2_bwd<144, 2>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
+  }
   const int Lp = attn_lp(L);
   const int smem_dq = (128 + 2 * Lp) * 128;
   const int smem_dkv = (128 + 2 * Lp) * 128 + 2 * Lp * 4;

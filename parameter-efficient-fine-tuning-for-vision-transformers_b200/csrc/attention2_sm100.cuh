@@ -86,33 +86,71 @@ struct Attn2Params {
   float scale;
 };
 
+
+// ---- register-array TMEM helpers (pointer form: with full unrolling the indices are compile-time constants)
+#define PEFT_R8(r, o) "=r"(r[o]), "=r"(r[o + 1]), "=r"(r[o + 2]), "=r"(r[o + 3]), "=r"(r[o + 4]), "=r"(r[o + 5]), "=r"(r[o + 6]), "=r"(r[o + 7])
+#define PEFT_W8(r, o) "r"(r[o]), "r"(r[o + 1]), "r"(r[o + 2]), "r"(r[o + 3]), "r"(r[o + 4]), "r"(r[o + 5]), "r"(r[o + 6]), "r"(r[o + 7])
+__device__ __forceinline__ void tm_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : PEFT_R8(r, 0), PEFT_R8(r, 8), PEFT_R8(r, 16), PEFT_R8(r, 24)
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tm_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : PEFT_R8(r, 0), PEFT_R8(r, 8)
+      : "r"(taddr)
+      : "memory");
+}
+template <int W>
+__device__ __forceinline__ void tm_ld(uint32_t taddr, uint32_t* r) {
+  if constexpr (W == 32) tm_ld32(taddr, r);
+  else tm_ld16(taddr, r);
+}
+__device__ __forceinline__ void tm_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      PEFT_W8(r, 0), PEFT_W8(r, 8)
+      : "memory");
+}
+__device__ __forceinline__ void tm_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), PEFT_W8(r, 0)
+               : "memory");
+}
+template <int W>   // W = number of fp32 source columns (32 or 16) -> W/2 packed columns
+__device__ __forceinline__ void tm_st_packed(uint32_t taddr, const uint32_t* r) {
+  if constexpr (W == 32) tm_st16(taddr, r);
+  else tm_st8(taddr, r);
+}
+
+// =====================================================================================================================
+// forward
+// =====================================================================================================================
 template <int NK>
 struct Attn2Cfg {
   static_assert(NK % 16 == 0 && NK >= 64 && NK <= 272, "padded key count");
-  static constexpr int kCA = ((NK / 2 + 15) / 16) * 16;            // columns of warpgroup A: [0, kCA); B: [kCA, NK)
-  static constexpr int kPB = NK - (NK - kCA) / 2;                  // first TMEM column of warpgroup B's P block
-  static constexpr int kOAlias = ((kCA / 2 + 31) / 32) * 32;       // O aliased between the two P blocks when it fits
-  static constexpr bool kAliasOK = (kOAlias + 64 <= kPB);
-  static constexpr int kOOff = kAliasOK ? kOAlias : NK;
+  static constexpr int kNCh = (NK + 31) / 32;                          // 32-column chunks (the last may be 16 wide)
+  static constexpr int kOAlias = ((NK / 2 + 31) / 32) * 32;           // P occupies [0, NK/2); O aliased above it if it fits
+  static constexpr int kOOff = (kOAlias + 64 <= NK) ? kOAlias : NK;
   static constexpr int kBufCols = (kOOff + 64 > NK) ? (kOOff + 64) : NK;
   static constexpr int kBufs = (2 * kBufCols <= 512) ? 2 : 1;
   static constexpr int kTmemCols = (kBufs * kBufCols <= 128) ? 128 : ((kBufs * kBufCols <= 256) ? 256 : 512);
-  static constexpr int kKVBox = (NK <= 256) ? NK : NK / 2;         // rows per TMA box of K / V
+  static constexpr int kKVBox = (NK <= 256) ? NK : NK / 2;            // rows per TMA box of K / V
   static constexpr int kKVBytes = NK * 128;
   static constexpr int kQBytes = 128 * 128;
-  static_assert((NK - kCA) % 32 == 0, "warpgroup B processes 32-column chunks");
-  // smem: K,V x2 heads | Q x2 tiles | O staging x2 | reductions | barriers
-  static constexpr int kSmemBytes = 4 * kKVBytes + 2 * kQBytes + 2 * kQBytes + 4 * 128 * 4 + 256 + 1024;
+  // smem: K,V x2 heads | Q x2 tiles | O staging x2 (one per warpgroup) | barriers
+  static constexpr int kSmemBytes = 4 * kKVBytes + 2 * kQBytes + 2 * kQBytes + 256 + 1024;
 };
 
-// TMEM column of the P block (A operand of the PV product) holding keys [16 j, 16 j + 16)
-template <int NK>
-__device__ __forceinline__ uint32_t p_col_of_kstep(int j) {
-  using C = Attn2Cfg<NK>;
-  const int key = 16 * j;
-  return key < C::kCA ? (uint32_t)(key >> 1) : (uint32_t)(NK - ((NK - key) >> 1));
-}
-
+// Forward kernel.  Warpgroup w (warps 4+4w .. 7+4w) owns the tiles g = w, w+2, ...: one thread per query row walks all
+// NK columns (pass 1: row max, pass 2: exp2 / row sum / bf16 P written in place), so no cross-thread reduction exists
+// and the two warpgroups run out of phase, which keeps the MUFU pipe and the tensor core busy at the same time.
 template <int NK>
 __global__ void __launch_bounds__(kA2Threads, 1)
 attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
@@ -122,10 +160,8 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sKV = smem;                                   // [2 heads][K | V]
   uint8_t* sQ = sKV + 4 * C::kKVBytes;                   // [2 tiles]
-  uint8_t* sO = sQ + 2 * C::kQBytes;                     // [2] staging for the TMA store
-  float* red_max = reinterpret_cast<float*>(sO + 2 * C::kQBytes);   // [2][128]
-  float* red_sum = red_max + 256;                                   // [2][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(red_sum + 256);
+  uint8_t* sO = sQ + 2 * C::kQBytes;                     // [2 warpgroups] staging for the TMA store
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sO + 2 * C::kQBytes);
   uint64_t* kv_full = bars;            // [2]
   uint64_t* kv_empty = bars + 2;       // [2]
   uint64_t* q_full = bars + 4;         // [2]
@@ -157,9 +193,9 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       ptx::mbar_init(&q_full[i], 1);
       ptx::mbar_init(&q_empty[i], 1);
       ptx::mbar_init(&s_ready[i], 1);
-      ptx::mbar_init(&p_ready[i], 256);
+      ptx::mbar_init(&p_ready[i], 128);
       ptx::mbar_init(&o_ready[i], 1);
-      ptx::mbar_init(&buf_free[i], 256);
+      ptx::mbar_init(&buf_free[i], 128);
     }
     ptx::fence_mbar_init();
   }
@@ -202,15 +238,15 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int hl = g / TQ, t = g % TQ;
         const int kvb = hl & 1;
         const int buf = g % C::kBufs;
-        ptx::mbar_wait(&p_ready[buf], (g / C::kBufs) & 1);
+        ptx::mbar_wait(&p_ready[g & 1], (g >> 1) & 1);
         ptx::tcgen05_fence_after();
         const uint32_t sV = ptx::smem_u32(sKV + kvb * 2 * C::kKVBytes + C::kKVBytes);
         const uint32_t tbuf = tmem_base + (uint32_t)(buf * C::kBufCols);
 #pragma unroll
         for (int j = 0; j < NK / 16; ++j)
-          ptx::umma_bf16_ts(tbuf + C::kOOff, tbuf + p_col_of_kstep<NK>(j), ptx::make_smem_desc_sw128_mn(sV + j * 2048),
-                            idesc_pv, j != 0 ? 1u : 0u);
-        ptx::umma_commit(&o_ready[buf]);
+          ptx::umma_bf16_ts(tbuf + C::kOOff, tbuf + 8 * j, ptx::make_smem_desc_sw128_mn(sV + j * 2048), idesc_pv,
+                            j != 0 ? 1u : 0u);
+        ptx::umma_commit(&o_ready[g & 1]);
         if (t == TQ - 1) ptx::umma_commit(&kv_empty[kvb]);
       };
       for (int g = 0; g < G; ++g) {
@@ -218,7 +254,13 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int kvb = hl & 1, qb = g & 1, buf = g % C::kBufs;
         if (t == 0) ptx::mbar_wait(&kv_full[kvb], (hl >> 1) & 1);
         ptx::mbar_wait(&q_full[qb], (g >> 1) & 1);
-        ptx::mbar_wait(&buf_free[buf], ((g / C::kBufs) & 1) ^ 1);
+        // barriers facing the warpgroups are indexed by the warpgroup slot g & 1 (use count g >> 1); the TMEM buffer is
+        // g % kBufs, so with a single buffer the previous user of the buffer is tile g - 1
+        if constexpr (C::kBufs == 2) {
+          ptx::mbar_wait(&buf_free[g & 1], ((g >> 1) & 1) ^ 1);
+        } else {
+          if (g >= 1) ptx::mbar_wait(&buf_free[(g - 1) & 1], ((g - 1) >> 1) & 1);
+        }
         ptx::tcgen05_fence_after();
         const uint32_t sq = ptx::smem_u32(sQ + qb * C::kQBytes);
         const uint32_t sk = ptx::smem_u32(sKV + kvb * 2 * C::kKVBytes);
@@ -240,7 +282,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                            idesc1, k != 0);
         }
         ptx::umma_commit(&q_empty[qb]);
-        ptx::umma_commit(&s_ready[buf]);
+        ptx::umma_commit(&s_ready[g & 1]);
         if constexpr (C::kBufs == 2) {
           if (g >= 1) issue_pv(g - 1);
         } else {
@@ -252,141 +294,127 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
     }
   } else if (warp >= 4) {
-    // ===================== softmax / epilogue warps =====================
+    // ===================== softmax / epilogue warpgroups =====================
     const int cw = warp - 4;
     const int quarter = warp & 3;          // TMEM lane quarter
-    const int wg = cw >> 2;                // 0: columns [0, kCA)   1: columns [kCA, NK)
+    const int wg = cw >> 2;
     const int rit = quarter * 32 + lane;   // row in tile == TMEM lane
     const float c = p.scale * 1.4426950408889634f;
-    const bool issuer = (threadIdx.x == 128);
-    for (int g = 0; g < G; ++g) {
+    const bool issuer = ((cw & 3) == 0) && lane == 0;
+    uint8_t* stage = sO + wg * C::kQBytes;
+    constexpr int NF = NK / 32;
+    constexpr bool kTail = (NK % 32) != 0;
+    for (int g = wg; g < G; g += 2) {
       const int hl = g / TQ, t = g % TQ;
       const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
       const int b = bh / H, h = bh % H;
       const int buf = g % C::kBufs;
       const int row = t * 128 + rit;
       const bool warp_active = (t * 128 + quarter * 32) < L;
-      const uint32_t tbuf = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + (uint32_t)(buf * C::kBufCols);
-      ptx::mbar_wait(&s_ready[buf], (g / C::kBufs) & 1);
+      const uint32_t tb = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + (uint32_t)(buf * C::kBufCols);
+      ptx::mbar_wait(&s_ready[wg], (g >> 1) & 1);
       ptx::tcgen05_fence_after();
-      // ---- pass 1: row maximum over this warpgroup's valid columns
-      float lmax = -INFINITY;
+      float mx = -INFINITY, sum = 0.f, mc = 0.f;
       if (warp_active) {
-        if (wg == 0) {
-#pragma unroll 1
-          for (int c0 = 0; c0 + 32 <= C::kCA; c0 += 32) {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32b_x32(tbuf + c0, r);
-            ptx::tmem_ld_wait();
+        uint32_t r[2][32];
+        // ---- pass 1: row maximum
+        tm_ld32(tb, r[0]);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) lmax = fmaxf(lmax, (c0 + j < L) ? __uint_as_float(r[j]) : -INFINITY);
-          }
-          if constexpr (C::kCA % 32 != 0) {
-            constexpr int c0 = (C::kCA / 32) * 32;
-            uint32_t r[16];
-            ptx::tmem_ld_32x32b_x16(tbuf + c0, r);
-            ptx::tmem_ld_wait();
+        for (int ci = 0; ci < NF; ++ci) {
+          ptx::tmem_ld_wait();
+          if (ci + 1 < NF) tm_ld32(tb + (ci + 1) * 32, r[(ci + 1) & 1]);
+          else if (kTail) tm_ld16(tb + NF * 32, r[(ci + 1) & 1]);
+          const int c0 = ci * 32;
+          if (c0 + 32 <= L) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) lmax = fmaxf(lmax, (c0 + j < L) ? __uint_as_float(r[j]) : -INFINITY);
-          }
-        } else {
-#pragma unroll 1
-          for (int c0 = C::kCA; c0 < NK; c0 += 32) {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32b_x32(tbuf + c0, r);
-            ptx::tmem_ld_wait();
+            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[ci & 1][j]));
+          } else if (c0 < L) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) lmax = fmaxf(lmax, (c0 + j < L) ? __uint_as_float(r[j]) : -INFINITY);
+            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, (c0 + j < L) ? __uint_as_float(r[ci & 1][j]) : -INFINITY);
           }
         }
-      }
-      red_max[wg * 128 + rit] = lmax;
-      if (issuer) ptx::bulk_wait_read<1>();            // the staging buffer of tile g-2 has been drained
-      ptx::named_bar_sync(1, 256);
-      const float m = fmaxf(red_max[rit], red_max[128 + rit]);
-      const float mc = m * c;
-      // ---- pass 2: P = exp2(S c - m c) -> bf16, written in place; row sum
-      float lsum = 0.f;
-      if (warp_active) {
-        if (wg == 0) {
-#pragma unroll 1
-          for (int c0 = 0; c0 + 32 <= C::kCA; c0 += 32) {
-            uint32_t r[32], pk[16];
-            ptx::tmem_ld_32x32b_x32(tbuf + c0, r);
-            ptx::tmem_ld_wait();
+        if constexpr (kTail) {
+          ptx::tmem_ld_wait();
+          constexpr int c0 = NF * 32;
+          if (c0 < L) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, (c0 + j < L) ? __uint_as_float(r[NF & 1][j]) : -INFINITY);
+          }
+        }
+        mc = mx * c;
+        // ---- pass 2: P = exp2(S c - m c) -> bf16 in place (ascending: writes only touch columns already consumed)
+        tm_ld32(tb, r[0]);
+#pragma unroll
+        for (int ci = 0; ci < NF; ++ci) {
+          ptx::tmem_ld_wait();
+          if (ci + 1 < NF) tm_ld32(tb + (ci + 1) * 32, r[(ci + 1) & 1]);
+          else if (kTail) tm_ld16(tb + NF * 32, r[(ci + 1) & 1]);
+          const int c0 = ci * 32;
+          uint32_t pk[16];
+          if (c0 + 32 <= L) {
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
-              const float p0 = (c0 + j < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[j]), c, -mc)) : 0.f;
-              const float p1 = (c0 + j + 1 < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[j + 1]), c, -mc)) : 0.f;
-              lsum += p0 + p1;
+              const float p0 = ptx::ex2_approx(fmaf(__uint_as_float(r[ci & 1][j]), c, -mc));
+              const float p1 = ptx::ex2_approx(fmaf(__uint_as_float(r[ci & 1][j + 1]), c, -mc));
+              sum += p0 + p1;
               pk[j >> 1] = ptx::pack_bf16x2(p0, p1);
             }
-            ptx::tmem_st_32x32b_x16(tbuf + (c0 >> 1), pk);
-          }
-          if constexpr (C::kCA % 32 != 0) {
-            constexpr int c0 = (C::kCA / 32) * 32;
-            uint32_t r[16], pk[8];
-            ptx::tmem_ld_32x32b_x16(tbuf + c0, r);
-            ptx::tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 16; j += 2) {
-              const float p0 = (c0 + j < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[j]), c, -mc)) : 0.f;
-              const float p1 = (c0 + j + 1 < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[j + 1]), c, -mc)) : 0.f;
-              lsum += p0 + p1;
-              pk[j >> 1] = ptx::pack_bf16x2(p0, p1);
-            }
-            ptx::tmem_st_32x32b_x8(tbuf + (c0 >> 1), pk);
-          }
-        } else {
-          // descending, so that the P block (top of this warpgroup's range) only overwrites columns already consumed
-#pragma unroll 1
-          for (int c0 = NK - 32; c0 >= C::kCA; c0 -= 32) {
-            uint32_t r[32], pk[16];
-            ptx::tmem_ld_32x32b_x32(tbuf + c0, r);
-            ptx::tmem_ld_wait();
+          } else {
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
-              const float p0 = (c0 + j < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[j]), c, -mc)) : 0.f;
-              const float p1 = (c0 + j + 1 < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[j + 1]), c, -mc)) : 0.f;
-              lsum += p0 + p1;
+              const float p0 = (c0 + j < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[ci & 1][j]), c, -mc)) : 0.f;
+              const float p1 = (c0 + j + 1 < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[ci & 1][j + 1]), c, -mc)) : 0.f;
+              sum += p0 + p1;
               pk[j >> 1] = ptx::pack_bf16x2(p0, p1);
             }
-            ptx::tmem_st_32x32b_x16(tbuf + (NK - ((NK - c0) >> 1)), pk);
           }
+          tm_st16(tb + (c0 >> 1), pk);
+        }
+        if constexpr (kTail) {
+          ptx::tmem_ld_wait();
+          constexpr int c0 = NF * 32;
+          uint32_t pk[8];
+#pragma unroll
+          for (int j = 0; j < 16; j += 2) {
+            const float p0 = (c0 + j < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[NF & 1][j]), c, -mc)) : 0.f;
+            const float p1 = (c0 + j + 1 < L) ? ptx::ex2_approx(fmaf(__uint_as_float(r[NF & 1][j + 1]), c, -mc)) : 0.f;
+            sum += p0 + p1;
+            pk[j >> 1] = ptx::pack_bf16x2(p0, p1);
+          }
+          tm_st8(tb + (c0 >> 1), pk);
         }
         ptx::tmem_st_wait();
       }
-      red_sum[wg * 128 + rit] = lsum;
       ptx::tcgen05_fence_before();
-      ptx::named_bar_sync(2, 256);
-      ptx::mbar_arrive(&p_ready[buf]);
-      const float tot = red_sum[rit] + red_sum[128 + rit];
+      ptx::mbar_arrive(&p_ready[wg]);
       // ---- epilogue: O / rowsum -> bf16 -> staging -> TMA store
-      ptx::mbar_wait(&o_ready[buf], (g / C::kBufs) & 1);
+      ptx::mbar_wait(&o_ready[wg], (g >> 1) & 1);
       ptx::tcgen05_fence_after();
-      uint32_t r[32];
+      uint32_t o[64];
       if (warp_active) {
-        ptx::tmem_ld_32x32b_x32(tbuf + C::kOOff + wg * 32, r);
+        tm_ld32(tb + C::kOOff, o);
+        tm_ld32(tb + C::kOOff + 32, o + 32);
         ptx::tmem_ld_wait();
       }
       ptx::tcgen05_fence_before();
-      ptx::mbar_arrive(&buf_free[buf]);
-      uint8_t* stage = sO + (g & 1) * C::kQBytes;
+      ptx::mbar_arrive(&buf_free[wg]);
+      if (issuer) ptx::bulk_wait_read<0>();            // this warpgroup's previous store has drained the staging tile
+      ptx::named_bar_sync(1 + wg, 128);
       if (warp_active) {
-        const float inv = 1.0f / tot;
+        const float inv = 1.0f / sum;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 8; ++j) {
           uint4 u;
-          u.x = ptx::pack_bf16x2(__uint_as_float(r[8 * j]) * inv, __uint_as_float(r[8 * j + 1]) * inv);
-          u.y = ptx::pack_bf16x2(__uint_as_float(r[8 * j + 2]) * inv, __uint_as_float(r[8 * j + 3]) * inv);
-          u.z = ptx::pack_bf16x2(__uint_as_float(r[8 * j + 4]) * inv, __uint_as_float(r[8 * j + 5]) * inv);
-          u.w = ptx::pack_bf16x2(__uint_as_float(r[8 * j + 6]) * inv, __uint_as_float(r[8 * j + 7]) * inv);
-          *reinterpret_cast<uint4*>(stage + rit * 128 + (((wg * 4 + j) ^ (rit & 7)) << 4)) = u;
+          u.x = ptx::pack_bf16x2(__uint_as_float(o[8 * j]) * inv, __uint_as_float(o[8 * j + 1]) * inv);
+          u.y = ptx::pack_bf16x2(__uint_as_float(o[8 * j + 2]) * inv, __uint_as_float(o[8 * j + 3]) * inv);
+          u.z = ptx::pack_bf16x2(__uint_as_float(o[8 * j + 4]) * inv, __uint_as_float(o[8 * j + 5]) * inv);
+          u.w = ptx::pack_bf16x2(__uint_as_float(o[8 * j + 6]) * inv, __uint_as_float(o[8 * j + 7]) * inv);
+          *reinterpret_cast<uint4*>(stage + rit * 128 + ((j ^ (rit & 7)) << 4)) = u;
         }
-        if (wg == 0 && row < L) p.lse2[(long long)bh * L + row] = mc + log2f(tot);
+        if (row < L) p.lse2[(long long)bh * L + row] = mc + log2f(sum);
       }
       ptx::fence_proxy_async();
-      ptx::named_bar_sync(3, 256);
+      ptx::named_bar_sync(1 + wg, 128);
       if (issuer) {
         ptx::tma_store_3d(&tmap_o, stage, h * 64, t * 128, b);
         ptx::bulk_commit();
