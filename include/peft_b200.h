@@ -71,6 +71,13 @@ int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32, const void
                        const float* mean, const float* rstd, const float* gamma, const void* g_in, long long ldgi,
                        void* g_out, long long ldgo, float* dgamma, float* dbeta, int M, int D, void* stream);
 
+/* same with an fp32 residual-gradient stream: g_out(fp32) = (g_in ? g_in : 0) + dLN/dx(dy) (g_in may alias g_out);
+ * g_copy (bf16, optional) receives a rounded copy of g_out — the A operand of the next dX product. */
+int peft_layernorm_bwd_f32g(const void* dy, long long lddy, int dy_is_f32, const void* x, long long ldx, int x_is_bf16,
+                            const float* mean, const float* rstd, const float* gamma, const float* g_in, long long ldgi,
+                            float* g_out, long long ldgo, void* g_copy, long long ldgc, float* dgamma, float* dbeta, int M,
+                            int D, void* stream);
+
 /* softmax(q k^T * scale) v for every (batch, head), head_dim 64, reading the packed projection buffer
  * qkv[B*L, >=3*H*64] (q | k | v column blocks, token row = b*L + l) and writing o[B*L, H*64]; lse2[B*H*L] receives
  * rowmax*scale*log2e + log2(rowsum) for the backward.

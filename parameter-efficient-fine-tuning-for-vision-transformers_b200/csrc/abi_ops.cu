@@ -80,6 +80,39 @@ extern "C" int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32,
   return 0;
 }
 
+// fp32 residual-gradient stream variant: g_in / g_out are fp32 (may alias), g_copy (optional) receives the bf16 copy the
+// next dX GEMM consumes as its A operand.  Keeps the 2 x depth residual-gradient adds out of bf16 (precision).
+extern "C" int peft_layernorm_bwd_f32g(const void* dy, long long lddy, int dy_is_f32, const void* x, long long ldx,
+                                       int x_is_bf16, const float* mean, const float* rstd, const float* gamma,
+                                       const float* g_in, long long ldgi, float* g_out, long long ldgo, void* g_copy,
+                                       long long ldgc, float* dgamma, float* dbeta, int M, int D, void* stream) {
+  PEFT_REQUIRE(M > 0 && D > 0 && D % 128 == 0, "peft_layernorm_bwd_f32g: bad shape M=%d D=%d", M, D);
+  PEFT_REQUIRE(aligned16(dy) && aligned16(x) && aligned16(g_out) && aligned16(gamma) && (g_in == nullptr || aligned16(g_in)) &&
+                   (g_copy == nullptr || aligned16(g_copy)),
+               "peft_layernorm_bwd_f32g: unaligned pointer");
+  PEFT_REQUIRE(lddy % 4 == 0 && ldx % 4 == 0 && ldgo % 4 == 0 && ldgi % 4 == 0 && ldgc % 4 == 0,
+               "peft_layernorm_bwd_f32g: pitches must be multiples of 4");
+  PEFT_REQUIRE((dgamma == nullptr) == (dbeta == nullptr), "peft_layernorm_bwd_f32g: dgamma and dbeta go together");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = ln_grid(M);
+  const bool pg = dgamma != nullptr;
+  using bf = __nv_bfloat16;
+#define LN_BWD_LAUNCH32(DYT, XT, PG) \
+  ln_bwd_kernel<NV, DYT, XT, float, PG><<<grid, 256, 0, s>>>((const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, g_in, ldgi, g_out, ldgo, dgamma, dbeta, M, (bf*)g_copy, ldgc)
+  LN_DISPATCH_NV(D / 128, {
+    if (dy_is_f32) {
+      if (x_is_bf16) { if (pg) LN_BWD_LAUNCH32(float, bf, true); else LN_BWD_LAUNCH32(float, bf, false); }
+      else { if (pg) LN_BWD_LAUNCH32(float, float, true); else LN_BWD_LAUNCH32(float, float, false); }
+    } else {
+      if (x_is_bf16) { if (pg) LN_BWD_LAUNCH32(bf, bf, true); else LN_BWD_LAUNCH32(bf, bf, false); }
+      else { if (pg) LN_BWD_LAUNCH32(bf, float, true); else LN_BWD_LAUNCH32(bf, float, false); }
+    }
+  });
+#undef LN_BWD_LAUNCH32
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 static int attn_lp(int L) { return ((L + 63) / 64) * 64; }
 
 static int attn_check(const AttnParams& p) {

@@ -97,7 +97,8 @@ __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__ x, long long ldx,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               const GT* __restrict__ g_in, long long ldgi, GT* __restrict__ g_out, long long ldgo,
-              float* __restrict__ dgamma, float* __restrict__ dbeta, int M) {
+              float* __restrict__ dgamma, float* __restrict__ dbeta, int M,
+              __nv_bfloat16* __restrict__ g_copy = nullptr, long long ldgc = 0) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;
@@ -143,6 +144,7 @@ ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__
 #pragma unroll
       for (int j = 0; j < 4; ++j) o[j] += rstd * (d[i][j] - s1 - xh[i][j] * s2);
       store4<GT>(g_out + row * ldgo + (i * 32 + lane) * 4, o);
+      if (g_copy != nullptr) store4<__nv_bfloat16>(g_copy + row * ldgc + (i * 32 + lane) * 4, o);
     }
   }
   if constexpr (kParamGrad) {

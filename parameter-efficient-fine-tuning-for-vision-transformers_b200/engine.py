@@ -95,7 +95,8 @@ class _Workspace:
         self.d_o = e(M, D)
         self.dqkv = torch.zeros(M, 3 * D + rp, device=dev, dtype=bf)   # [dq dk dv | dp]
         self.delta = e(B * H * L, dt=f32)
-        self.g = e(M, D)                                         # residual-gradient stream (bf16)
+        self.g = e(M, D, dt=f32)                                 # residual-gradient stream (fp32, like the forward stream)
+        self.gb = e(M, D)                                        # its bf16 copy: A operand of the dX products
         # final LayerNorm on the cls rows
         self.meanf = e(B, dt=f32); self.rstdf = e(B, dt=f32)
         self.yf = e(B, D)                                        # clip: ln_post output (bf16 operand of the projection)
@@ -237,13 +238,15 @@ class VitEngine:
             raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
         dfeat = dfeat.contiguous().float()
         w.g.zero_()
+        w.gb.zero_()
         xcls = w.x0[dep].view(B, L * D)[:, :D]
         gcls = w.g.view(B, L * D)[:, :D]
+        gbcls = w.gb.view(B, L * D)[:, :D]
         if self.vproj is None:
-            ops.layernorm_bwd(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls)
+            ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
         else:
             ops.gemm(dfeat.to(torch.bfloat16), self.vproj, w.dyf)                # dy = dfeat proj^T
-            ops.layernorm_bwd(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls)
+            ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
         dDn = dUpT = None
         if r:
             dDn = torch.zeros(dep, rp, D, device=self.dev, dtype=torch.float32)
@@ -251,11 +254,11 @@ class VitEngine:
         scale = 64 ** -0.5
         for i in reversed(range(dep)):
             # MLP: dh = (g W2) * act'(h) ; dxn2 = dh W1 ; g += LN2'(dxn2)
-            ops.gemm(w.g, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
+            ops.gemm(w.gb, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
             ops.gemm(w.dh, self.wfc1T[i], w.dxn)
-            ops.layernorm_bwd(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g)
+            ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb)
             # attention: d_o = g Wproj ; dqkv = attn'(d_o)
-            ops.gemm(w.g, self.wprojT[i], w.d_o)
+            ops.gemm(w.gb, self.wprojT[i], w.d_o)
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
             if rp:
                 dq = w.dqkv[:, :3 * D]
@@ -264,10 +267,13 @@ class VitEngine:
                     cw = min(64, rp - c)
                     ops.tn_reduce(w.xn1[i][:, D + c:D + c + cw], dq, dUpT[i, c:c + cw])            # dUp^T = p^T dqkv
                     ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])  # dDn = dp^T x
+            if i == 0:
+                break       # block 0's input gradient feeds only the frozen patch embedding: no dX product, no LN1'
+            if rp:
                 ops.gemm(w.dqkv, self.wqkvT[i], w.dxn)                              # dxn1 = [dqkv|dp] [W^T|Dn^T]^T
             else:
                 ops.gemm(w.dqkv[:, :3 * D], self.wqkvT[i][:, :3 * D], w.dxn)
-            ops.layernorm_bwd(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g)
+            ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb)
         # the patch embedding / ln_pre are frozen and the images need no gradient: stop here.
         if r:
             return dDn[:, :r], dUpT[:, :r]

@@ -81,6 +81,25 @@ def layernorm_bwd(dy, x, mean, rstd, gamma, g_in, g_out, dgamma=None, dbeta=None
     return g_out
 
 
+def layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g_in, g_out, g_copy=None, dgamma=None, dbeta=None):
+    """fp32 residual-gradient stream: g_out(fp32) = g_in(fp32, may alias) + LN'(dy); g_copy = bf16(g_out)."""
+    pdy, lddy = _mat(dy, None, "dy")
+    px, ldx = _mat(x, None, "x")
+    pgo, ldgo = _mat(g_out, torch.float32, "g_out")
+    pgi = ldgi = 0
+    if g_in is not None:
+        pgi, ldgi = _mat(g_in, torch.float32, "g_in")
+    pgc = ldgc = 0
+    if g_copy is not None:
+        pgc, ldgc = _mat(g_copy, torch.bfloat16, "g_copy")
+    M, D = x.shape
+    _lib.check(_lib.load().peft_layernorm_bwd_f32g(pdy, lddy, int(dy.dtype == torch.float32), px, ldx,
+                                                   int(x.dtype == torch.bfloat16), _p(mean), _p(rstd), _p(gamma), pgi,
+                                                   ldgi, pgo, ldgo, pgc, ldgc, _p(dgamma), _p(dbeta), M, D, _stream()),
+               "peft_layernorm_bwd_f32g")
+    return g_out
+
+
 def attention_fwd(qkv, o, lse2, B, H, L, scale):
     pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
     po, ldo = _mat(o, torch.bfloat16, "o")

@@ -12,6 +12,7 @@ cases = {
     "kron_n8_r2": VitCfg(dialect="timm", adapter="kron", phm_dim=8, phm_rank=2, img=64, patch=32, depth=2),
     "lora": VitCfg(dialect="timm", adapter="lora", img=64, patch=32, depth=2),
     "kron_n4_L197": VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=224, patch=16, depth=2),
+    "kron_n4_L50_d12": VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=224, patch=32, depth=12),
 }
 B = int(os.environ.get("DIAG_B", "8"))
 for name in sys.argv[1:] or list(cases):

@@ -138,6 +138,29 @@ def test_layernorm_fwd_bwd(ops, M, D):
     assert rel(gout2[:, :D], xr.grad) < 5e-3
 
 
+def test_layernorm_bwd_f32_stream(ops):
+    """fp32 residual-gradient stream variant: in-place accumulate + bf16 copy."""
+    M, D = 777, 768
+    x = _r(M, D, scale=2.0, seed=1) + 0.5
+    gamma = 1.0 + _r(D, scale=0.1, seed=2)
+    beta = _r(D, scale=0.1, seed=3)
+    y = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+    mean = torch.empty(M, device="cuda")
+    rstd = torch.empty(M, device="cuda")
+    ops.layernorm_fwd(x, gamma, beta, y, mean, rstd, eps=1e-5)
+    xr = x.clone().requires_grad_(True)
+    ref = F.layer_norm(xr, (D,), gamma, beta, 1e-5)
+    dy = _r(M, D, dtype=torch.bfloat16, seed=4)
+    g = _r(M, D, seed=5)
+    g0 = g.clone()
+    gb = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+    ops.layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g, g, gb)
+    ref.backward(dy.float())
+    assert rel(g, g0 + xr.grad) < 1e-5
+    assert rel(gb, g0 + xr.grad) < 4e-3
+    assert torch.equal(gb, g.to(torch.bfloat16))
+
+
 @pytest.mark.parametrize("B,H,L", [(2, 12, 50), (3, 12, 197), (2, 16, 257), (1, 2, 64), (2, 3, 5)])
 def test_attention_fwd_bwd(ops, B, H, L):
     D = H * 64
