@@ -72,12 +72,51 @@ def bench_reduce(M=50432):
     print(f"tn_reduce I=32 J=768  M={M}: {t:7.1f} us  {(M * (768 + 32) * 2) / t / 1e3:7.1f} GB/s")
 
 
+def bench_gemm(M=50432, iters=20):
+    cases = [("qkv   [x|p][W|Up]^T+b", 2304, 800, ops.EPI_STORE), ("proj  +resid f32", 768, 768, ops.EPI_RESID_F32),
+             ("fc1   +GELU (h, act)", 3072, 768, ops.EPI_GELU), ("fc2   +resid f32", 768, 3072, ops.EPI_RESID_F32),
+             ("fc2^T *gelu'(h)", 3072, 768, ops.EPI_DGELU), ("fc1^T store", 768, 3072, ops.EPI_STORE),
+             ("proj^T store", 768, 768, ops.EPI_STORE), ("qkv^T [dqkv|dp]", 768, 2336, ops.EPI_STORE)]
+    for name, N, K, epi in cases:
+        a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+        b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+        bias = torch.randn(N, device="cuda")
+        f32 = epi == ops.EPI_RESID_F32
+        out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
+        out2 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16) if epi == ops.EPI_GELU else None
+        aux = None
+        if f32:
+            aux = torch.randn(M, N, device="cuda")
+        elif epi == ops.EPI_DGELU:
+            aux = torch.randn(M, N, device="cuda").to(torch.bfloat16)
+        t = timeit(lambda: ops.gemm(a, b, out, bias=bias, epilogue=epi, out2=out2, aux=aux), iters=iters, warm=2)
+        print(f"gemm {name:24s} M={M} N={N} K={K}: {t:7.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     if what in ("attn", "all"):
         bench_attn()
         bench_attn(128, 16, 257)
         bench_attn(256, 12, 50)
+    if what in ("gemm", "all"):
+        bench_gemm()
+    if what == "prof":      # one pass of each hot kernel, for ncu captures
+        bench_gemm(iters=1)
+        B, H, L = 256, 12, 197
+        D = H * 64
+        qkv = torch.randn(B * L, 3 * D, device="cuda").to(torch.bfloat16)
+        o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+        d_o = torch.randn(B * L, D, device="cuda").to(torch.bfloat16)
+        dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+        lse2 = torch.empty(B * H * L, device="cuda")
+        delta = torch.empty(B * H * L, device="cuda")
+        for _ in range(2):
+            ops.attention_fwd(qkv, o, lse2, B, H, L, 0.125)
+            ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)
+        bench_ln()
+        bench_reduce()
+        torch.cuda.synchronize()
     if what in ("ln", "all"):
         bench_ln()
     if what in ("reduce", "all"):
