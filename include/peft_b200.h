@@ -64,6 +64,12 @@ int peft_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, i
 int peft_layernorm_fwd(const void* x, long long ldx, int x_is_bf16, const float* gamma, const float* beta,
                        void* y, long long ldy, int y_is_f32, float* mean, float* rstd, int M, int D, float eps,
                        void* stream);
+/* y(bf16) = LN(x fp32) and, in the same pass, add_out(fp32) = x + add_in(fp32).
+ * replaces: Adapter / HyperComplexAdapter's adapter_norm_before plus the residual adds of
+ * `x + adapter(mlp(ln_2(x)))` — FS/adapter_model.py:230-232,330-334, FS/compacter_model.py:393-425,477-479. */
+int peft_layernorm_fwd_add(const float* x, long long ldx, const float* gamma, const float* beta, void* y, long long ldy,
+                           float* mean, float* rstd, const float* add_in, long long ldai, float* add_out, long long ldao,
+                           int M, int D, float eps, void* stream);
 /* g_out(bf16) = (g_in ? g_in : 0) + dLN/dx(dy); optional dgamma/dbeta accumulation (fp32 atomics, caller zeroes them).
  * replaces: the autograd backward of the LayerNorms above, fused with the residual-gradient add of Block.forward
  * (FS/kadaptation.py:273-277, FS/model.py:1155-1158). */

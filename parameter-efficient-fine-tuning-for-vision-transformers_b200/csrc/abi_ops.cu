@@ -51,6 +51,26 @@ extern "C" int peft_layernorm_fwd(const void* x, long long ldx, int x_is_bf16, c
   return 0;
 }
 
+// y(bf16) = LN(x), and add_out(fp32) = x + add_in(fp32) in the same pass.  replaces: the adapter's own LayerNorm plus the
+// two residual adds of `x + adapter(mlp(ln_2(x)))` (FS/adapter_model.py:330-334, FS/compacter_model.py:477-479).
+extern "C" int peft_layernorm_fwd_add(const float* x, long long ldx, const float* gamma, const float* beta, void* y,
+                                      long long ldy, float* mean, float* rstd, const float* add_in, long long ldai,
+                                      float* add_out, long long ldao, int M, int D, float eps, void* stream) {
+  PEFT_REQUIRE(M > 0 && D > 0 && D % 128 == 0, "peft_layernorm_fwd_add: bad shape M=%d D=%d", M, D);
+  PEFT_REQUIRE(aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) && add_in && add_out && aligned16(add_in) &&
+                   aligned16(add_out),
+               "peft_layernorm_fwd_add: null or unaligned pointer");
+  PEFT_REQUIRE(ldx % 4 == 0 && ldy % 4 == 0 && ldai % 4 == 0 && ldao % 4 == 0, "peft_layernorm_fwd_add: pitches must be multiples of 4");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = ln_grid(M);
+  LN_DISPATCH_NV(D / 128, {
+    ln_fwd_kernel<NV, float, __nv_bfloat16><<<grid, 256, 0, s>>>(x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps,
+                                                               add_in, ldai, add_out, ldao);
+  });
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32, const void* x, long long ldx,
                                   int x_is_bf16, const float* mean, const float* rstd, const float* gamma,
                                   const void* g_in, long long ldgi, void* g_out, long long ldgo, float* dgamma,

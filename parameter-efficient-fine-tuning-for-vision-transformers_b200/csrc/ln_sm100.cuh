@@ -46,7 +46,8 @@ template <int NV, typename InT, typename OutT>
 __global__ void __launch_bounds__(256)
 ln_fwd_kernel(const InT* __restrict__ x, long long ldx, const float* __restrict__ gamma, const float* __restrict__ beta,
               OutT* __restrict__ y, long long ldy, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M,
-              float eps) {
+              float eps, const float* __restrict__ add_in = nullptr, long long ldai = 0, float* __restrict__ add_out = nullptr,
+              long long ldao = 0) {
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
   const int D = NV * 128;
@@ -64,6 +65,13 @@ ln_fwd_kernel(const InT* __restrict__ x, long long ldx, const float* __restrict_
     for (int i = 0; i < NV; ++i) {
       load4<InT>(x + row * ldx + (i * 32 + lane) * 4, v[i]);
       s += v[i][0] + v[i][1] + v[i][2] + v[i][3];
+      if (add_out != nullptr) {   // side output: add_out = x + add_in (the residual sum the adapter's up-projection lands on)
+        float a[4];
+        load4<float>(add_in + row * ldai + (i * 32 + lane) * 4, a);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a[j] += v[i][j];
+        store4<float>(add_out + row * ldao + (i * 32 + lane) * 4, a);
+      }
     }
     const float mean = warp_sum(s) * (1.0f / D);
     float q = 0.f;

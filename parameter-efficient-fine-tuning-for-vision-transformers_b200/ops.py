@@ -67,6 +67,18 @@ def layernorm_fwd(x, gamma, beta, y, mean=None, rstd=None, eps=1e-6):
     return y
 
 
+def layernorm_fwd_add(x, gamma, beta, y, mean, rstd, add_in, add_out, eps=1e-5):
+    """y(bf16) = LN(x fp32); add_out(fp32) = x + add_in(fp32)."""
+    px, ldx = _mat(x, torch.float32, "x")
+    py, ldy = _mat(y, torch.bfloat16, "y")
+    pai, ldai = _mat(add_in, torch.float32, "add_in")
+    pao, ldao = _mat(add_out, torch.float32, "add_out")
+    M, D = x.shape
+    _lib.check(_lib.load().peft_layernorm_fwd_add(px, ldx, _p(gamma), _p(beta), py, ldy, _p(mean), _p(rstd), pai, ldai, pao,
+                                                  ldao, M, D, float(eps), _stream()), "peft_layernorm_fwd_add")
+    return y
+
+
 def layernorm_bwd(dy, x, mean, rstd, gamma, g_in, g_out, dgamma=None, dbeta=None):
     pdy, lddy = _mat(dy, None, "dy")
     px, ldx = _mat(x, None, "x")
