@@ -38,6 +38,8 @@ class EngineCfg:
     mlp: int
     out_dim: int = 0      # clip: visual projection width (0 = no projection)
     rank: int = 0         # low-rank q/v adapter columns r' (0 = no q/v adapter)
+    bottleneck: int = 0   # Houlsby / Compacter bottleneck width after the MLP (0 = none; 64 in the reference)
+    bn_act: str = "relu"  # "relu" (Houlsby, FS/adapter_model.py:304-311) | "gelu_tanh" (Compacter gelu_new, FS/compacter_model.py:376)
 
     @property
     def seq(self):
@@ -101,6 +103,21 @@ class _Workspace:
         self.meanf = e(B, dt=f32); self.rstdf = e(B, dt=f32)
         self.yf = e(B, D)                                        # clip: ln_post output (bf16 operand of the projection)
         self.dyf = e(B, D)
+        m = cfg.bottleneck
+        if m:
+            # bottleneck adapter: saved per layer
+            self.hf = [e(M, D, dt=f32) for _ in range(dep)]          # MLP output h (adapter input), fp32
+            self.za = [e(M, D) for _ in range(dep)]                  # LN_a(h), bf16 operand of the down projection
+            self.mean_a = e(dep, M, dt=f32); self.rstd_a = e(dep, M, dt=f32)
+            self.zext = []                                           # [z | 1 0...0]: the ones column turns bias grads into token reductions
+            for _ in range(dep):
+                z = torch.zeros(M, m + 16, device=dev, dtype=bf)
+                z[:, m] = 1.0
+                self.zext.append(z)
+            self.upre = [e(M, m) for _ in range(dep)] if cfg.bn_act != "relu" else None   # pre-activation (gelu_new)
+            self.dz = e(M, m)
+            self.gh = e(M, D, dt=f32)                                # gradient w.r.t. h (fp32) and its bf16 copy
+            self.ghb = e(M, D)
         self.generation = 0
 
 
@@ -182,7 +199,21 @@ class VitEngine:
             self.wqkvT[:, :, 3 * D:3 * D + r].copy_(Dn.transpose(1, 2))
 
     # ------------------------------------------------------------------ forward
-    def forward(self, images, Dn=None, UpT=None):
+    def _refresh_bottleneck(self, bn):
+        """bn = (Wd [dep,m,D], bd [dep,m], Wu [dep,D,m], bu [dep,D], ln_g [dep,D], ln_b [dep,D]) fp32."""
+        Wd, bd, Wu, bu, lg, lb = bn
+        bf = torch.bfloat16
+        with torch.no_grad():
+            self.wd_bf = Wd.detach().to(bf).contiguous()                        # down: B [N=m, K=D]
+            self.wdT_bf = Wd.detach().transpose(1, 2).to(bf).contiguous()       # dza : B [N=D, K=m]
+            self.wu_bf = Wu.detach().to(bf).contiguous()                        # up  : B [N=D, K=m]
+            self.wuT_bf = Wu.detach().transpose(1, 2).to(bf).contiguous()       # dz  : B [N=m, K=D]
+            self.bd_f = bd.detach().float().contiguous()
+            self.bu_f = bu.detach().float().contiguous()
+            self.lga = lg.detach().float().contiguous()
+            self.lba = lb.detach().float().contiguous()
+
+    def forward(self, images, Dn=None, UpT=None, bn=None):
         cfg = self.cfg
         if not self.frozen_loaded:
             raise RuntimeError("VitEngine.forward before load_frozen()")
@@ -192,6 +223,11 @@ class VitEngine:
         B = images.shape[0]
         w = self._workspace(B)
         self._refresh_adapter(Dn, UpT)
+        m = cfg.bottleneck
+        if m:
+            if bn is None:
+                raise RuntimeError("VitEngine.forward: bottleneck adapter operands missing")
+            self._refresh_bottleneck(bn)
         images = images.contiguous().float()
         # patch embedding: unfold -> GEMM (+bias) -> prepend cls, add positions
         ops.im2col_patches(images, w.patches, cfg.patch)
@@ -214,7 +250,18 @@ class VitEngine:
             ops.gemm(w.o[i], self.wproj[i], w.x1[i], bias=self.bproj[i], epilogue=ops.EPI_RESID_F32, aux=w.x0[i])
             ops.layernorm_fwd(w.x1[i], self.ln2_w[i], self.ln2_b[i], w.xn2, w.mean2[i], w.rstd2[i], cfg.eps)
             ops.gemm(w.xn2, self.wfc1[i], w.h[i], bias=self.bfc1[i], epilogue=self.act_fwd, out2=w.act)
-            ops.gemm(w.act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i])
+            if not m:
+                ops.gemm(w.act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i])
+            else:
+                # x_{i+1} = x1 + h + up(act(down(LN_a(h)))),  h = mlp(ln2(x1))     (adapter_model.py:330-334 computed once, Q6)
+                ops.gemm(w.act, self.wfc2[i], w.hf[i], bias=self.bfc2[i], epilogue=ops.EPI_STORE_F32)
+                ops.layernorm_fwd_add(w.hf[i], self.lga[i], self.lba[i], w.za[i], w.mean_a[i], w.rstd_a[i], w.x1[i], w.x0[i + 1], 1e-5)
+                z = w.zext[i][:, :m]
+                if cfg.bn_act == "relu":
+                    ops.gemm(w.za[i], self.wd_bf[i], z, bias=self.bd_f[i], epilogue=ops.EPI_RELU)
+                else:
+                    ops.gemm(w.za[i], self.wd_bf[i], w.upre[i], bias=self.bd_f[i], epilogue=ops.EPI_GELU_TANH, out2=z)
+                ops.gemm(z, self.wu_bf[i], w.x0[i + 1], bias=self.bu_f[i], epilogue=ops.EPI_RESID_F32, aux=w.x0[i + 1])
         # final LayerNorm on the cls rows (+ CLIP projection)
         xcls = w.x0[dep].view(B, L * D)[:, :D]
         if self.vproj is None:
@@ -252,11 +299,34 @@ class VitEngine:
             dDn = torch.zeros(dep, rp, D, device=self.dev, dtype=torch.float32)
             dUpT = torch.zeros(dep, rp, 3 * D, device=self.dev, dtype=torch.float32)
         scale = 64 ** -0.5
+        m = cfg.bottleneck
+        bng = None
+        if m:
+            f32 = torch.float32
+            z0 = lambda *sh: torch.zeros(*sh, device=self.dev, dtype=f32)
+            dWuT, dWd = z0(dep, m, D), z0(dep, m, D)
+            dbu16, dbd16 = z0(dep, 16, D), z0(dep, 16, m)
+            dlg, dlb = z0(dep, D), z0(dep, D)
+            bn_dact = ops.EPI_DRELU if cfg.bn_act == "relu" else ops.EPI_DGELU_TANH
         for i in reversed(range(dep)):
+            gmlp = w.gb                  # gradient w.r.t. the MLP output h (bf16 operand)
+            if m:
+                # bottleneck adapter backward; g = dL/dx_{i+1} is also dL/dx1 (residual) and part of dL/dh
+                z, ones = w.zext[i][:, :m], w.zext[i][:, m:m + 16]
+                ops.tn_reduce(ones, w.gb, dbu16[i])                                   # dbu  = colsum(g)       (row 0)
+                ops.tn_reduce(z, w.gb, dWuT[i])                                       # dWu^T = z^T g
+                ops.gemm(w.gb, self.wuT_bf[i], w.dz, epilogue=bn_dact, aux=(z if cfg.bn_act == "relu" else w.upre[i]))
+                ops.tn_reduce(ones, w.dz, dbd16[i])                                   # dbd  = colsum(dz)
+                ops.tn_reduce(w.dz, w.za[i], dWd[i])                                  # dWd  = dz^T LN_a(h)
+                ops.gemm(w.dz, self.wdT_bf[i], w.dxn)                                 # dza  = dz Wd
+                ops.layernorm_bwd_f32g(w.dxn, w.hf[i], w.mean_a[i], w.rstd_a[i], self.lga[i], w.g, w.gh, w.ghb, dlg[i], dlb[i])
+                gmlp = w.ghb
             # MLP: dh = (g W2) * act'(h) ; dxn2 = dh W1 ; g += LN2'(dxn2)
-            ops.gemm(w.gb, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
+            ops.gemm(gmlp, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
             ops.gemm(w.dh, self.wfc1T[i], w.dxn)
             ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb)
+            if i == 0 and not rp:
+                break       # nothing trainable is upstream of block 0's attention when there is no q/v adapter
             # attention: d_o = g Wproj ; dqkv = attn'(d_o)
             ops.gemm(w.gb, self.wprojT[i], w.d_o)
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
@@ -275,24 +345,27 @@ class VitEngine:
                 ops.gemm(w.dqkv[:, :3 * D], self.wqkvT[i][:, :3 * D], w.dxn)
             ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb)
         # the patch embedding / ln_pre are frozen and the images need no gradient: stop here.
+        if m:
+            bng = (dWd, dbd16[:, 0], dWuT.transpose(1, 2), dbu16[:, 0], dlg, dlb)
         if r:
-            return dDn[:, :r], dUpT[:, :r]
-        return None, None
+            return dDn[:, :r], dUpT[:, :r], bng
+        return None, None, bng
 
 
 class _BackboneFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, engine, images, Dn, UpT):
+    def forward(ctx, engine, images, Dn, UpT, *bn):
         ctx.engine = engine
-        ctx.has_adapter = Dn is not None
-        return engine.forward(images, Dn, UpT)
+        ctx.nbn = len(bn)
+        return engine.forward(images, Dn, UpT, bn if bn else None)
 
     @staticmethod
     def backward(ctx, dfeat):
-        dDn, dUpT = ctx.engine.backward(dfeat)
-        return None, None, dDn, dUpT
+        dDn, dUpT, bng = ctx.engine.backward(dfeat)
+        extra = tuple(bng) if bng is not None else (None,) * ctx.nbn
+        return (None, None, dDn, dUpT) + extra
 
 
-def backbone(engine: VitEngine, images, Dn=None, UpT=None):
-    """Differentiable (w.r.t. Dn / UpT) visual-tower feature extraction through the CUDA engine."""
-    return _BackboneFn.apply(engine, images, Dn, UpT)
+def backbone(engine: VitEngine, images, Dn=None, UpT=None, bn=None):
+    """Differentiable (w.r.t. Dn / UpT / the bottleneck-adapter operands) visual-tower feature extraction."""
+    return _BackboneFn.apply(engine, images, Dn, UpT, *(bn if bn is not None else ()))

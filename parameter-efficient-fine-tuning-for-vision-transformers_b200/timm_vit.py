@@ -79,8 +79,63 @@ class Attention(nn.Module):
             nn.init.normal_(self.v_proj_adapter1.weight, std=0.02)
             self.v_proj_adapter2 = nn.Linear(lora_attn_dim, dim, bias=False)
             self.v_proj_adapter2.weight.data.zero_()
-        elif adapter not in ("none", "houlsby"):
+        elif adapter not in ("none", "houlsby", "compacter"):
             raise ValueError(adapter)
+
+    forward = _no_eager
+
+
+class Adapter(nn.Module):
+    """Houlsby bottleneck adapter — FS/adapter.py:308-400 (= FS/adapter_model.py:204-295): LayerNorm -> Linear(D, m) -> ReLU
+    -> Linear(m, D) + residual.  As in the reference, the LayerNorm is registered both as `adapter_norm_before` and as
+    `adapter_down.0` (state_dict carries both keys; named_parameters de-duplicates)."""
+
+    def __init__(self, input_size, down_sample=64, non_linearity="relu", init_bert_weights=True):
+        super().__init__()
+        if non_linearity != "relu":
+            raise NotImplementedError("the Houlsby adapter kernels implement the reference's ReLU bottleneck")
+        self.input_size, self.down_sample = input_size, down_sample
+        self.adapter_norm_before = nn.LayerNorm(input_size)
+        self.adapter_down = nn.Sequential(self.adapter_norm_before, nn.Linear(input_size, down_sample), nn.ReLU())
+        self.adapter_up = nn.Linear(down_sample, input_size)
+        if init_bert_weights:
+            for lin in (self.adapter_down[1], self.adapter_up):
+                nn.init.normal_(lin.weight, std=0.02)
+                nn.init.zeros_(lin.bias)
+
+    forward = _no_eager
+
+
+class PHMLinear(nn.Module):
+    """FS/compacter_model.py:213-355 — y = x (sum_i phm_rule[i] kron W[i]) + b; parameters only (phm_rule is initialised
+    N(0, 0.01^2): the reference leaves it uninitialised)."""
+
+    def __init__(self, in_features, out_features, phm_dim):
+        super().__init__()
+        assert in_features % phm_dim == 0 and out_features % phm_dim == 0
+        self.in_features, self.out_features, self.phm_dim = in_features, out_features, phm_dim
+        self.phm_rule = nn.Parameter(torch.empty(phm_dim, phm_dim, phm_dim).normal_(0, 0.01))
+        self.W = nn.Parameter(torch.empty(phm_dim, in_features // phm_dim, out_features // phm_dim))
+        nn.init.xavier_uniform_(self.W, gain=2 ** 0.5)
+        self.b = nn.Parameter(torch.zeros(out_features))
+
+    def dense(self):
+        """H [in, out] = sum_i phm_rule[i] (x) W[i]  (kronecker_product_einsum_batched, FS/compacter_model.py:190-208)."""
+        n = self.phm_dim
+        return torch.einsum("iac,ikp->akcp", self.phm_rule, self.W).reshape(self.in_features, self.out_features)
+
+    forward = _no_eager
+
+
+class HyperComplexAdapter(nn.Module):
+    """Compacter — FS/compacter_model.py:358-425: LayerNorm -> PHMLinear(D, m, n=32) -> gelu_new -> PHMLinear(m, D, n=4)."""
+
+    def __init__(self, input_size, down_sample=64, n_down=32, n_up=4):
+        super().__init__()
+        self.input_size, self.down_sample = input_size, down_sample
+        self.adapter_norm_before = nn.LayerNorm(input_size)
+        self.down_PHM = PHMLinear(input_size, down_sample, n_down)
+        self.up_sampler = PHMLinear(down_sample, input_size, n_up)
 
     forward = _no_eager
 
@@ -89,7 +144,8 @@ class Block(nn.Module):
     """FS/kadaptation.py:241-283 (pre-norm only)."""
 
     def __init__(self, dim, num_heads, mlp_ratio=4., qkv_bias=False, qk_scale=None, drop=0., attn_drop=0., drop_path=0.,
-                 act_layer=nn.GELU, norm_layer=nn.LayerNorm, pre_norm=True, res_score=False, **adapter_kw):
+                 act_layer=nn.GELU, norm_layer=nn.LayerNorm, pre_norm=True, res_score=False, bottleneck=64,
+                 compacter_n_down=32, compacter_n_up=4, **adapter_kw):
         super().__init__()
         if not pre_norm:
             raise NotImplementedError("post-norm blocks are not supported")
@@ -100,6 +156,11 @@ class Block(nn.Module):
                               proj_drop=drop, res_score=res_score, **adapter_kw)
         self.norm2 = norm_layer(dim)
         self.mlp = Mlp(in_features=dim, hidden_features=int(dim * mlp_ratio), act_layer=act_layer, drop=drop)
+        kind = adapter_kw.get("adapter", "kron")
+        if kind == "houlsby":
+            self.adapter = Adapter(dim, down_sample=bottleneck)
+        elif kind == "compacter":
+            self.compacter = HyperComplexAdapter(dim, down_sample=bottleneck, n_down=compacter_n_down, n_up=compacter_n_up)
 
     forward = _no_eager
 
@@ -194,7 +255,7 @@ class VisionTransformer(nn.Module):
         return {'pos_embed', 'cls_token'}
 
     # ---------------------------------------------------------------- adapter -> low-rank operands
-    _ADAPTER_KEYS = ("phm_rule", "W_left", "W_right", "phmb", "_proj_adapter")
+    _ADAPTER_KEYS = ("phm_rule", "W_left", "W_right", "phmb", "_proj_adapter", ".adapter.", ".compacter.")
 
     def _rank(self):
         a0 = self.blocks[0].attn
@@ -226,6 +287,29 @@ class VisionTransformer(nn.Module):
         UpT = torch.cat([torch.cat([uq, z, z], dim=2), torch.cat([z, z, uv], dim=2)], dim=1)
         return Dn, UpT
 
+    def bottleneck_operands(self):
+        """(Wd [dep,m,D], bd [dep,m], Wu [dep,D,m], bu [dep,D], ln_g [dep,D], ln_b [dep,D]) built differentiably from the
+        reference-named Houlsby / Compacter parameters; None when the model has no bottleneck adapter."""
+        st = torch.stack
+        if self.adapter_kind == "houlsby":
+            ad = [b.adapter for b in self.blocks]
+            return (st([a.adapter_down[1].weight for a in ad]), st([a.adapter_down[1].bias for a in ad]),
+                    st([a.adapter_up.weight for a in ad]), st([a.adapter_up.bias for a in ad]),
+                    st([a.adapter_norm_before.weight for a in ad]), st([a.adapter_norm_before.bias for a in ad]))
+        if self.adapter_kind == "compacter":
+            ad = [b.compacter for b in self.blocks]
+            return (st([a.down_PHM.dense().t() for a in ad]), st([a.down_PHM.b for a in ad]),
+                    st([a.up_sampler.dense().t() for a in ad]), st([a.up_sampler.b for a in ad]),
+                    st([a.adapter_norm_before.weight for a in ad]), st([a.adapter_norm_before.bias for a in ad]))
+        return None
+
+    def _bottleneck_cfg(self):
+        if self.adapter_kind == "houlsby":
+            return dict(bottleneck=self.blocks[0].adapter.down_sample, bn_act="relu")
+        if self.adapter_kind == "compacter":
+            return dict(bottleneck=self.blocks[0].compacter.down_sample, bn_act="gelu_tanh")
+        return {}
+
     # ---------------------------------------------------------------- engine plumbing
     def _frozen_items(self):
         return [(k, v) for k, v in self.state_dict(keep_vars=True).items()
@@ -235,7 +319,7 @@ class VisionTransformer(nn.Module):
         items = self._frozen_items()
         sig = tuple((k, v.data_ptr(), v._version) for k, v in items)
         if self._engine is None or self._engine.dev != device:
-            self._engine = VitEngine(EngineCfg(dialect="timm", rank=self._rank(), **self._cfg), device)
+            self._engine = VitEngine(EngineCfg(dialect="timm", rank=self._rank(), **self._bottleneck_cfg(), **self._cfg), device)
             self._frozen_sig = None
         if sig != self._frozen_sig:
             sd = dict(items)
@@ -251,7 +335,7 @@ class VisionTransformer(nn.Module):
             raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
         eng = self._ensure_engine(x.device)
         Dn, UpT = self.lowrank_operands()
-        return backbone(eng, x, Dn, UpT)
+        return backbone(eng, x, Dn, UpT, self.bottleneck_operands())
 
     def forward(self, x):
         return self.forward_features(x)
