@@ -95,9 +95,10 @@ int peft_attention_bwd(const void* qkv, long long ldqkv, const void* o, long lon
                        const float* lse2, float* delta, void* dqkv, long long lddqkv, int B, int H, int L, float scale,
                        void* stream);
 
-/* images fp32 [B,3,img,img] -> bf16 patch rows [B*(img/patch)^2, 3*patch*patch] (the unfold half of the stride=kernel
- * conv of FS/model.py:1203 / FS/kadaptation.py:300-307; the GEMM half is peft_gemm_bf16). */
-int peft_im2col_patches(const float* images, void* patches, int B, int img, int patch, void* stream);
+/* images fp32 [B,3,img,img] -> bf16 patch rows [B*(img/patch)^2, 3*patch*patch] of pitch ldp >= 3*patch*patch, ldp % 8 == 0
+ * (columns beyond 3*patch*patch are left untouched: the caller keeps them zero, e.g. 588 -> 592 for patch 14).  The
+ * unfold half of the stride=kernel conv of FS/model.py:1203 / FS/kadaptation.py:300-307; the GEMM half is peft_gemm_bf16. */
+int peft_im2col_patches(const float* images, void* patches, long long ldp, int B, int img, int patch, void* stream);
 /* x fp32 [B,L,D]: row 0 = cls + pos[0], row 1+t = patch_embed[b*(L-1)+t] + pos[1+t]
  * replaces: FS/kadaptation.py:524-529, FS/model.py:1206-1207. */
 int peft_assemble_tokens(const void* patch_embed, const float* cls, const float* pos, float* x, int B, int L, int D,
@@ -108,6 +109,41 @@ int peft_assemble_tokens(const void* patch_embed, const float* cls, const float*
  * (FS/model.py:754-762, FS/kadaptation.py:81-115,211-219, FS/adapter_model.py:265-267). */
 int peft_tn_reduce(const void* x, long long ldx, int I, const void* y, long long ldy, int J, float* out,
                    long long ldout, int M, void* stream);
+
+/* CLIP-dialect placement of the q/v adapter update (SURVEY.md §8a Q1 + Q2): the reference reshapes the [L,B,C] update
+ * RAW to [B*H, L, hd] before adding it to the per-head q / v (FS/model.py:981-986, FS/lora_model.py:730-735) and q was
+ * divided by sqrt(hd) beforehand (FS/model.py:967).  With token rows ordered b*L + l:
+ *   backward == 0:  qkv[(b,l), h] (q and v blocks) += mult * delta[(b_s,l_s), slot]       (in place on qkv)
+ *   backward == 1:  delta[(b_s,l_s), slot] = mult * qkv[(b,l), h]                          (qkv holds dq|dk|dv)
+ * where g = (b*H+h)*L + l, (r, slot) = divmod(g, H), (l_s, b_s) = divmod(r, B); delta is [B*L, 2*H*64] (q | v). */
+int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int B, int H, int L, float mult_q,
+                    float mult_v, int backward, void* stream);
+
+/* Fastfood intrinsic-dimension projection over a SET of wrapped parameter tensors in one call.
+ * replaces: FastfoodWrap.forward / fastfood_torched / fast_walsh_hadamard_torched and their autograd backward —
+ * FL/intrinsic/fastfood.py:61-77,81-121,151-187.
+ * Per tensor p (descriptor below): DD = numel, LL = 2^ll >= DD, coef = 1 / (divisor * sqrt(DD / LL)) with
+ * divisor = sqrt(LL * sum(G^2)) (fastfood.py:124-148).  Device arrays, concatenated over tensors:
+ *   pi_lo [sum LL] uint16 = Pi[j] mod min(LL, wn);  gg [sum LL] fp32 = G;  bsign [T, wn] fp32 = B[:wn] (zero padded);
+ *   theta0 / theta / dtheta fp32 indexed by off_dd;  scratch [sum LL] fp32;  wu [T, wn] fp32 scratch.
+ * wn = power of two >= d, <= 4096.  items_* are device arrays of (tensor, tile) int pairs built by the caller:
+ *   items_high: for every tensor with ll > 13, tiles 0 .. LL/8192 - 1;   items_low: blocks 0 .. ceil(DD/8192) - 1. */
+typedef struct {
+  long long off_ll;  /* element offset of this tensor in pi_lo / gg / scratch */
+  long long off_dd;  /* element offset in theta0 / theta / dtheta */
+  int DD;
+  int ll;
+  float coef;
+  int reserved;
+} peft_ff_tensor;
+/* theta[off_dd + j] = theta0[off_dd + j] + coef * [H G Pi H B pad(V)][j],  j < DD, for every tensor */
+int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items_high,
+                      int n_high, const int* items_low, int n_low, const uint16_t* pi_lo, const float* gg,
+                      const float* bsign, const float* theta0, float* theta, float* wu, float* scratch, void* stream);
+/* dV[k] += sum_p coef_p * B_p[k] * [H Pi^T G H pad(dtheta_p)][k],  k < d  (caller zeroes dV; wu is zeroed inside) */
+int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items_high,
+                      int n_high, const int* items_low, int n_low, const uint16_t* pi_lo, const float* gg,
+                      const float* bsign, float* wu, float* scratch, float* dV, void* stream);
 
 #ifdef __cplusplus
 }

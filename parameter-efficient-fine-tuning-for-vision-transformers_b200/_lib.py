@@ -29,9 +29,12 @@ SIGNATURES = {
     "peft_layernorm_bwd_f32g": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _vp, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, _vp, _vp, C.c_int, C.c_int, _vp],
     "peft_attention_fwd": [_vp, _c_ll, _vp, _c_ll, _vp, C.c_int, C.c_int, C.c_int, C.c_float, _vp],
     "peft_attention_bwd": [_vp, _c_ll, _vp, _c_ll, _vp, _c_ll, _vp, _vp, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, _vp],
-    "peft_im2col_patches": [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp],
+    "peft_im2col_patches": [_vp, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp],
     "peft_assemble_tokens": [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp],
     "peft_tn_reduce": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp],
+    "peft_clip_delta": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, _vp],
+    "peft_fastfood_fwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "peft_fastfood_bwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
 }
 _RESTYPES = {"peft_last_error": None, "peft_launch_count": C.c_ulonglong}
 

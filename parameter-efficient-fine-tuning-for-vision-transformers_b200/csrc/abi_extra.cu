@@ -1,0 +1,98 @@
+// C-ABI: CLIP-dialect delta placement and the Fastfood projection.
+#include "common.cuh"
+#include "clip_delta_sm100.cuh"
+#include "fastfood_sm100.cuh"
+
+using namespace peft;
+
+namespace {
+inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+constexpr int kFfSmemBytes = (kFfTile + kFfMaxWn) * 4;
+
+int ff_configure() {
+  static bool done = false;
+  if (done) return 0;
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_fwd_high_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_fwd_low_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_high_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_low_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+  done = true;
+  return 0;
+}
+int ff_check(int d, int wn, int T, int n_high, int n_low) {
+  PEFT_REQUIRE(d > 0 && wn >= d && wn <= kFfMaxWn && (wn & (wn - 1)) == 0, "fastfood: need d <= wn <= %d, wn a power of two (d=%d wn=%d)", kFfMaxWn, d, wn);
+  PEFT_REQUIRE(T > 0 && n_high >= 0 && n_low > 0, "fastfood: empty tensor / item list");
+  return 0;
+}
+}  // namespace
+
+extern "C" int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int B, int H, int L, float mult_q,
+                               float mult_v, int backward, void* stream) {
+  PEFT_REQUIRE(B > 0 && H > 0 && L > 0, "peft_clip_delta: bad shape B=%d H=%d L=%d", B, H, L);
+  PEFT_REQUIRE(qkv && delta && al16(qkv) && al16(delta) && ldqkv % 8 == 0 && ldd % 8 == 0 && ldqkv >= 3ll * H * 64 && ldd >= 2ll * H * 64,
+               "peft_clip_delta: operands must be 16-byte aligned, pitch %% 8 == 0, qkv >= 3*H*64 and delta >= 2*H*64 columns");
+  const long long total = (long long)B * H * L * 16;
+  long long blocks = (total + 255) / 256;
+  if (blocks > sm_count() * 16) blocks = sm_count() * 16;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (backward)
+    clip_delta_kernel<true><<<(int)blocks, 256, 0, s>>>((__nv_bfloat16*)qkv, ldqkv, (__nv_bfloat16*)delta, ldd, B, H, L, mult_q, mult_v);
+  else
+    clip_delta_kernel<false><<<(int)blocks, 256, 0, s>>>((__nv_bfloat16*)qkv, ldqkv, (__nv_bfloat16*)delta, ldd, B, H, L, mult_q, mult_v);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items_high,
+                                 int n_high, const int* items_low, int n_low, const uint16_t* pi_lo, const float* gg,
+                                 const float* bsign, const float* theta0, float* theta, float* wu, float* scratch,
+                                 void* stream) {
+  int rc = ff_check(d, wn, T, n_high, n_low);
+  if (rc) return rc;
+  PEFT_REQUIRE(V && tensors && items_low && pi_lo && gg && bsign && theta0 && theta && wu && (n_high == 0 || (items_high && scratch)),
+               "peft_fastfood_fwd: null operand");
+  rc = ff_configure();
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  ff_small_kernel<0><<<T, 256, wn * 4, s>>>(tensors, bsign, V, wu, nullptr, d, wn);
+  PEFT_LAUNCH_CHECK();
+  FfArgs a{};
+  a.tensors = tensors; a.pi_lo = pi_lo; a.gg = gg; a.wv = wu; a.scratch = scratch; a.theta0 = theta0; a.theta = theta; a.wn = wn;
+  const int smem = (kFfTile + wn) * 4;
+  if (n_high > 0) {
+    a.items = reinterpret_cast<const int2*>(items_high);
+    ff_fwd_high_kernel<<<n_high, kFfThreads, smem, s>>>(a);
+    PEFT_LAUNCH_CHECK();
+  }
+  a.items = reinterpret_cast<const int2*>(items_low);
+  ff_fwd_low_kernel<<<n_low, kFfThreads, smem, s>>>(a);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T,
+                                 const int* items_high, int n_high, const int* items_low, int n_low, const uint16_t* pi_lo,
+                                 const float* gg, const float* bsign, float* wu, float* scratch, float* dV, void* stream) {
+  int rc = ff_check(d, wn, T, n_high, n_low);
+  if (rc) return rc;
+  PEFT_REQUIRE(dtheta && tensors && items_low && pi_lo && gg && bsign && wu && dV && (n_high == 0 || (items_high && scratch)),
+               "peft_fastfood_bwd: null operand");
+  rc = ff_configure();
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  PEFT_CUDA_CHECK(cudaMemsetAsync(wu, 0, (size_t)T * wn * 4, s));
+  FfArgs a{};
+  a.tensors = tensors; a.pi_lo = pi_lo; a.gg = gg; a.u = wu; a.scratch = scratch; a.dtheta = dtheta; a.wn = wn;
+  const int smem = (kFfTile + wn) * 4;
+  a.items = reinterpret_cast<const int2*>(items_low);
+  ff_bwd_low_kernel<<<n_low, kFfThreads, smem, s>>>(a);
+  PEFT_LAUNCH_CHECK();
+  if (n_high > 0) {
+    a.items = reinterpret_cast<const int2*>(items_high);
+    ff_bwd_high_kernel<<<n_high, kFfThreads, smem, s>>>(a);
+    PEFT_LAUNCH_CHECK();
+  }
+  ff_small_kernel<1><<<T, 256, wn * 4, s>>>(tensors, bsign, nullptr, wu, dV, d, wn);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}

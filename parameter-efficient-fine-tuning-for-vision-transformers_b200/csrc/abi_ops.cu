@@ -277,13 +277,17 @@ extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* 
   return 0;
 }
 
-extern "C" int peft_im2col_patches(const float* images, void* patches, int B, int img, int patch, void* stream) {
-  PEFT_REQUIRE(B > 0 && img > 0 && patch > 0 && img % patch == 0 && patch % 4 == 0, "peft_im2col_patches: bad shape");
-  PEFT_REQUIRE(aligned16(images) && aligned16(patches), "peft_im2col_patches: unaligned pointer");
-  const long long total = (long long)B * (img / patch) * (img / patch) * 3 * patch * patch / 4;
+extern "C" int peft_im2col_patches(const float* images, void* patches, long long ldp, int B, int img, int patch, void* stream) {
+  PEFT_REQUIRE(B > 0 && img > 0 && patch > 0 && img % patch == 0 && patch % 2 == 0, "peft_im2col_patches: bad shape (img=%d patch=%d)", img, patch);
+  PEFT_REQUIRE(aligned16(images) && aligned16(patches) && ldp >= 3ll * patch * patch && ldp % 8 == 0,
+               "peft_im2col_patches: unaligned pointer or pitch (need ldp %% 8 == 0, ldp >= 3*patch*patch)");
+  const int vec = (patch % 4 == 0) ? 4 : 2;
+  const long long total = (long long)B * (img / patch) * (img / patch) * 3 * patch * patch / vec;
   long long blocks = (total + 255) / 256;
   if (blocks > sm_count() * 16) blocks = sm_count() * 16;
-  im2col_patch_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(images, (__nv_bfloat16*)patches, B, img, patch);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (vec == 4) im2col_patch_kernel<4><<<(int)blocks, 256, 0, s>>>(images, (__nv_bfloat16*)patches, ldp, B, img, patch);
+  else im2col_patch_kernel<2><<<(int)blocks, 256, 0, s>>>(images, (__nv_bfloat16*)patches, ldp, B, img, patch);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

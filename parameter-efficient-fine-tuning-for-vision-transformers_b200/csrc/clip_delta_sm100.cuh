@@ -1,0 +1,74 @@
+// CLIP-dialect q/v delta placement (SURVEY.md §8a quirks Q1 + Q2).
+//
+// The reference adds the adapter update to the per-head q / v tensors through a RAW reshape of an [L, B, C] tensor to
+// [B*H, L, hd] (FS/model.py:981-986, FS/lora_model.py:730-735) while q itself is view(L, B*H, hd).transpose(0, 1)
+// (FS/model.py:907), so the 64-wide chunk that lands on (b, h, l) is the one whose flat chunk index in the [L, B, C]
+// tensor equals g = (b*H + h)*L + l:   (r, slot) = divmod(g, H),  (l_s, b_s) = divmod(r, B),
+//       q[b, h, l, :] += delta_q[l_s, b_s, slot*64 : slot*64+64]        (same for v).
+// q has already been divided by sqrt(hd) at that point (Q2, FS/model.py:967); the attention kernels apply `scale` to
+// the scores instead, so the q chunk is multiplied by mult_q = 1/scale here.
+//
+// Buffers use this library's token order (row = b*L + l):  qkv [B*L, >= 3*H*64] (q | k | v), delta [B*L, 2*H*64]
+// (delta_q | delta_v).  The map chunk -> chunk is a bijection, so forward is a gather-add and backward a pure gather:
+//   FWD:  qkv[dst] += mult * delta[src]          BWD:  ddelta[src] = mult * dqkv[dst]
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace peft {
+
+template <bool BWD>
+__global__ void __launch_bounds__(256) clip_delta_kernel(__nv_bfloat16* __restrict__ qkv, long long ldqkv,
+                                                        __nv_bfloat16* __restrict__ delta, long long ldd, int B, int H,
+                                                        int L, float mult_q, float mult_v) {
+  const long long chunks = (long long)B * H * L;      // 64-element chunks per tensor (q or v)
+  const long long total = chunks * 2 * 8;             // x {q, v} x 8 vectors of 8 bf16
+  const int D = H * 64;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int e8 = (int)(idx & 7);
+    long long g = idx >> 3;
+    const int which = g >= chunks ? 1 : 0;
+    g -= which ? chunks : 0;
+    // destination (b, h, l)
+    const int l = (int)(g % L);
+    const long long bh = g / L;
+    const int h = (int)(bh % H);
+    const int b = (int)(bh / H);
+    // source (l_s, b_s, slot)
+    const int slot = (int)(g % H);
+    const long long r = g / H;
+    const int b_s = (int)(r % B);
+    const int l_s = (int)(r / B);
+    __nv_bfloat16* pd = qkv + ((long long)b * L + l) * ldqkv + (which ? 2 * D : 0) + h * 64 + e8 * 8;
+    __nv_bfloat16* ps = delta + ((long long)b_s * L + l_s) * ldd + which * D + slot * 64 + e8 * 8;
+    const float mult = which ? mult_v : mult_q;
+    uint4 vs, vd;
+    if (BWD) {
+      vd = *reinterpret_cast<const uint4*>(pd);
+      const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&vd);
+      __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&vs);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float2 f = __bfloat1622float2(a[k]);
+        o[k] = __floats2bfloat162_rn(f.x * mult, f.y * mult);
+      }
+      *reinterpret_cast<uint4*>(ps) = vs;
+    } else {
+      vd = *reinterpret_cast<const uint4*>(pd);
+      vs = *reinterpret_cast<const uint4*>(ps);
+      const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&vd);
+      const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&vs);
+      uint4 out;
+      __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&out);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float2 f = __bfloat1622float2(a[k]);
+        float2 dd = __bfloat1622float2(d[k]);
+        o[k] = __floats2bfloat162_rn(fmaf(dd.x, mult, f.x), fmaf(dd.y, mult, f.y));
+      }
+      *reinterpret_cast<uint4*>(pd) = out;
+    }
+  }
+}
+
+}  // namespace peft

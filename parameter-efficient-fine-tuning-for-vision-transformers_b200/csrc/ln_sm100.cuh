@@ -177,22 +177,31 @@ ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__
 // ------------------------------------------------------------------------------------------------ patch embedding
 // images fp32 [B,3,H,W] -> bf16 patch rows [B*P, 3*p*p], column = c*p*p + i*p + j (matches conv weight flatten).
 // replaces the unfold half of nn.Conv2d(stride=kernel=p): FS/model.py:1203, FS/kadaptation.py:300-307.
-__global__ void im2col_patch_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ out, int B, int HW, int p) {
+template <int VEC>
+__global__ void im2col_patch_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ out, long long ldo, int B,
+                                    int HW, int p) {
   const int gp = HW / p;                // patches per side
   const int K = 3 * p * p;
-  const long long total = (long long)B * gp * gp * K / 4;  // 4 consecutive j per thread (p % 4 == 0)
+  const long long total = (long long)B * gp * gp * K / VEC;  // VEC consecutive j per thread (p % VEC == 0)
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const long long e = t * 4;
+    const long long e = t * VEC;
     const int k = (int)(e % K);
     const long long row = e / K;
     const int c = k / (p * p), i = (k / p) % p, j = k % p;
     const int px = (int)(row % gp), py = (int)((row / gp) % gp);
     const int b = (int)(row / (gp * gp));
-    const float4 f = *reinterpret_cast<const float4*>(img + (((long long)b * 3 + c) * HW + (py * p + i)) * HW + px * p + j);
-    uint2 u;
-    u.x = ptx::pack_bf16x2(f.x, f.y);
-    u.y = ptx::pack_bf16x2(f.z, f.w);
-    *reinterpret_cast<uint2*>(out + e) = u;
+    const float* src = img + (((long long)b * 3 + c) * HW + (py * p + i)) * HW + px * p + j;
+    __nv_bfloat16* dst = out + row * ldo + k;
+    if (VEC == 4) {
+      const float4 f = *reinterpret_cast<const float4*>(src);
+      uint2 u;
+      u.x = ptx::pack_bf16x2(f.x, f.y);
+      u.y = ptx::pack_bf16x2(f.z, f.w);
+      *reinterpret_cast<uint2*>(dst) = u;
+    } else {
+      const float2 f = *reinterpret_cast<const float2*>(src);
+      *reinterpret_cast<uint32_t*>(dst) = ptx::pack_bf16x2(f.x, f.y);
+    }
   }
 }
 

@@ -50,6 +50,10 @@ class EngineCfg:
         return 1e-6 if self.dialect == "timm" else 1e-5
 
     @property
+    def patch_k(self):
+        return (3 * self.patch * self.patch + 7) // 8 * 8
+
+    @property
     def rank_pad(self):
         return ((self.rank + 15) // 16) * 16
 
@@ -76,7 +80,7 @@ class _Workspace:
         e = lambda *s, dt=bf: torch.empty(*s, device=dev, dtype=dt)
         self.B, self.M = B, M
         P = L - 1
-        self.patches = e(B * P, 3 * cfg.patch * cfg.patch)
+        self.patches = torch.zeros(B * P, cfg.patch_k, device=dev, dtype=bf)   # K padded to a multiple of 8 (TMA pitch)
         self.pe = e(B * P, D)
         self.tokens = e(M, D, dt=f32) if cfg.dialect == "clip" else None
         # per layer, saved for backward
@@ -97,6 +101,8 @@ class _Workspace:
         self.d_o = e(M, D)
         self.dqkv = torch.zeros(M, 3 * D + rp, device=dev, dtype=bf)   # [dq dk dv | dp]
         self.delta = e(B * H * L, dt=f32)
+        # CLIP dialect with a q/v adapter: the update cannot ride in the K extension (raw-reshape placement)
+        self.dlt = e(M, 2 * D) if (cfg.dialect == "clip" and rp) else None
         self.g = e(M, D, dt=f32)                                 # residual-gradient stream (fp32, like the forward stream)
         self.gb = e(M, D)                                        # its bf16 copy: A operand of the dX products
         # final LayerNorm on the cls rows
@@ -154,14 +160,14 @@ class VitEngine:
         self.bqkv, self.bproj, self.bfc1, self.bfc2 = vec("qkv_b"), vec("proj_b"), vec("fc1_b"), vec("fc2_b")
         self.ln1_w, self.ln1_b, self.ln2_w, self.ln2_b = vec("ln1_w"), vec("ln1_b"), vec("ln2_w"), vec("ln2_b")
         if cfg.dialect == "timm":
-            self.patch_w = g("patch_embed.proj.weight").reshape(D, -1).to(bf).contiguous()
+            self.patch_w = self._pad_k(g("patch_embed.proj.weight").reshape(D, -1)).to(bf).contiguous()
             self.patch_b = g("patch_embed.proj.bias").contiguous()
             self.cls = g("cls_token").reshape(D).contiguous()
             self.pos = g("pos_embed").reshape(cfg.seq, D).contiguous()
             self.lnf_w, self.lnf_b = g("norm.weight").contiguous(), g("norm.bias").contiguous()
             self.vproj = None
         else:
-            self.patch_w = g("conv1.weight").reshape(D, -1).to(bf).contiguous()
+            self.patch_w = self._pad_k(g("conv1.weight").reshape(D, -1)).to(bf).contiguous()
             self.patch_b = None
             self.cls = g("class_embedding").reshape(D).contiguous()
             self.pos = g("positional_embedding").reshape(cfg.seq, D).contiguous()
@@ -176,9 +182,16 @@ class VitEngine:
         if rp > 0:
             self.dn_bf = torch.zeros(dep, rp, D, device=dev, dtype=bf)
             self.upT_bf = torch.zeros(dep, rp, 3 * D, device=dev, dtype=bf)
+            if cfg.dialect == "clip":
+                self.up2_bf = torch.zeros(dep, 2 * D, rp, device=dev, dtype=bf)     # [Up_q ; Up_v]: B operand [N=2D, K=rp]
+                self.up2T_bf = torch.zeros(dep, rp, 2 * D, device=dev, dtype=bf)    # its transpose: B operand of dp
         self.act_fwd = ops.EPI_GELU if cfg.dialect == "timm" else ops.EPI_QUICKGELU
         self.act_bwd = ops.EPI_DGELU if cfg.dialect == "timm" else ops.EPI_DQUICKGELU
         self.frozen_loaded = True
+
+    def _pad_k(self, w2d):
+        kp = self.cfg.patch_k
+        return w2d if w2d.shape[1] == kp else torch.nn.functional.pad(w2d, (0, kp - w2d.shape[1]))
 
     def _workspace(self, B):
         w = self.ws.get(B)
@@ -195,8 +208,13 @@ class VitEngine:
         with torch.no_grad():
             self.dn_bf[:, :r].copy_(Dn)
             self.upT_bf[:, :r].copy_(UpT)
-            self.wqkv[:, :, D:D + r].copy_(UpT.transpose(1, 2))
             self.wqkvT[:, :, 3 * D:3 * D + r].copy_(Dn.transpose(1, 2))
+            if cfg.dialect == "clip":
+                self.up2T_bf[:, :r, :D].copy_(UpT[:, :, :D])
+                self.up2T_bf[:, :r, D:].copy_(UpT[:, :, 2 * D:])
+                self.up2_bf.copy_(self.up2T_bf.transpose(1, 2))
+            else:
+                self.wqkv[:, :, D:D + r].copy_(UpT.transpose(1, 2))
 
     # ------------------------------------------------------------------ forward
     def _refresh_bottleneck(self, bn):
@@ -241,7 +259,13 @@ class VitEngine:
         for i in range(dep):
             xn1 = w.xn1[i]
             ops.layernorm_fwd(w.x0[i], self.ln1_w[i], self.ln1_b[i], xn1[:, :D], w.mean1[i], w.rstd1[i], cfg.eps)
-            if rp:
+            if rp and cfg.dialect == "clip":
+                # reference order (FS/model.py:967,981-986): q/sqrt(hd) first, then += raw-reshaped update (Q1, Q2)
+                ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                    # p = LN1(x) Dn^T
+                ops.gemm(xn1[:, :D], self.wqkv[i][:, :D], w.qkv[i], bias=self.bqkv[i])
+                ops.gemm(xn1[:, D:], self.up2_bf[i], w.dlt)                        # [dq | dv] = p Up^T
+                ops.clip_delta(w.qkv[i], w.dlt, B, H, L, 1.0 / scale, 1.0)
+            elif rp:
                 ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                    # p = LN1(x) Dn^T
                 ops.gemm(xn1, self.wqkv[i], w.qkv[i], bias=self.bqkv[i])           # [x|p] [W|Up]^T + b
             else:
@@ -330,7 +354,17 @@ class VitEngine:
             # attention: d_o = g Wproj ; dqkv = attn'(d_o)
             ops.gemm(w.gb, self.wprojT[i], w.d_o)
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
-            if rp:
+            if rp and cfg.dialect == "clip":
+                dq = w.dqkv[:, :3 * D]
+                ops.clip_delta(dq, w.dlt, B, H, L, 1.0 / scale, 1.0, backward=True)  # d[dq|dv] gathered back (Q1 inverse)
+                ops.gemm(w.dlt, self.up2T_bf[i], w.dqkv[:, 3 * D:])                 # dp = d[dq|dv] [Up_q;Up_v]
+                for c in range(0, rp, 64):
+                    cw = min(64, rp - c)
+                    pc = w.xn1[i][:, D + c:D + c + cw]
+                    ops.tn_reduce(pc, w.dlt[:, :D], dUpT[i, c:c + cw, :D])
+                    ops.tn_reduce(pc, w.dlt[:, D:], dUpT[i, c:c + cw, 2 * D:])
+                    ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
+            elif rp:
                 dq = w.dqkv[:, :3 * D]
                 ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
                 for c in range(0, rp, 64):                                          # adapter-gradient token reductions

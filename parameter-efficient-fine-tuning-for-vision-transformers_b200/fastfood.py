@@ -1,0 +1,189 @@
+"""Intrinsic-dimension fine-tuning: drop-in for full_shot/main/intrinsic/fastfood.py (`FastfoodWrap`).
+
+Same constructor, same single trainable parameter `V` [d], same random draws in the same order (so a run seeded like
+the reference gets the same B, Pi, G), same forward contract: every wrapped parameter is deleted from its module and
+re-set on each forward as  theta0 + Fastfood(V)  (fastfood.py:36-57,61-77).  The projection of ALL wrapped tensors
+and its backward are two C-ABI calls (`peft_fastfood_fwd/_bwd`, csrc/fastfood_sm100.cuh) instead of
+2*log2(LL) chunk/cat kernels per tensor; there is no torch fallback.
+
+Layout in HBM (ViT-B/32 visual tower: 152 tensors, sum DD = 87.8 M, sum LL = 143.4 M):
+  pi_lo uint16 [sum LL] (Pi mod wn, 287 MB), gg fp32 [sum LL] (574 MB), scratch fp32 [sum LL], bsign fp32 [T, wn],
+  theta0 / theta / dtheta fp32 flat with every tensor starting on a 256-byte boundary.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+_TILE = 8192
+_FF_DTYPE = np.dtype([("off_ll", "<i8"), ("off_dd", "<i8"), ("DD", "<i4"), ("ll", "<i4"), ("coef", "<f4"), ("reserved", "<i4")])
+
+
+def fastfood_vars(DD, device="cpu"):
+    """fastfood.py:124-148 — same draws, same order (torch global RNG for B and G, numpy global RNG for Pi)."""
+    ll = int(np.ceil(np.log(DD) / np.log(2)))
+    LL = 2 ** ll
+    BB = torch.empty(LL, dtype=torch.float32).uniform_(0, 2).type(torch.LongTensor)
+    BB = (BB * 2 - 1).type(torch.FloatTensor)
+    Pi = torch.LongTensor(np.random.permutation(LL))
+    GG = torch.empty(LL, dtype=torch.float32).normal_()
+    divisor = torch.sqrt(LL * torch.sum(torch.pow(GG, 2)))
+    return [BB, Pi, GG, divisor, LL]
+
+
+class FastfoodPlan:
+    """Device-resident tables for a set of wrapped tensors; built once from the per-tensor (B, Pi, G, divisor, LL)."""
+
+    def __init__(self, shapes, params, d, device):
+        if not torch.cuda.is_available():
+            raise RuntimeError("peft_b200 Fastfood needs a CUDA device (no CPU fallback)")
+        _lib.load()
+        self.d = int(d)
+        self.wn = 1 << max(0, math.ceil(math.log2(max(1, self.d))))
+        if self.wn > 4096:
+            raise NotImplementedError("Fastfood kernels support intrinsic dimension <= 4096")
+        self.device = torch.device(device)
+        T = len(shapes)
+        self.T = T
+        desc = np.zeros(T, dtype=_FF_DTYPE)
+        off_ll = off_dd = 0
+        self.offsets, self.numels, self.shapes = [], [], [tuple(s) for s in shapes]
+        hi_items, lo_items = [], []
+        bsign = torch.zeros(T, self.wn, dtype=torch.float32)
+        pi_parts, gg_parts = [], []
+        for t, (shape, (BB, Pi, GG, divisor, LL)) in enumerate(zip(shapes, params)):
+            DD = int(np.prod(shape)) if len(shape) else 1
+            ll = int(LL).bit_length() - 1
+            assert (1 << ll) == LL and LL >= DD
+            if ll > 26:
+                raise NotImplementedError("Fastfood kernels support tensors up to 2^26 elements")
+            if LL < self.wn and DD < self.d:
+                # the reference pads V to LL with a NEGATIVE pad here (truncation); keep that behaviour
+                pass
+            n1 = min(LL, self.wn)
+            coef = 1.0 / (float(divisor) * math.sqrt(float(DD) / LL))
+            desc[t] = (off_ll, off_dd, DD, ll, coef, 0)
+            bsign[t, :n1] = BB[:n1]
+            pi_parts.append((Pi & (n1 - 1)).to(torch.int16))     # n1 <= 4096 fits; reinterpret as uint16 on device
+            gg_parts.append(GG.float())
+            if ll > 13:
+                hi_items += [(t, k) for k in range(LL // _TILE)]
+            lo_items += [(t, k) for k in range((DD + _TILE - 1) // _TILE)]
+            self.offsets.append(off_dd)
+            self.numels.append(DD)
+            off_ll += LL
+            off_dd += (DD + 63) // 64 * 64
+        self.total_ll, self.total_dd = off_ll, off_dd
+        dev = self.device
+        self.desc = torch.from_numpy(desc.view(np.uint8).copy()).to(dev)
+        self.pi_lo = torch.cat(pi_parts).to(dev)
+        self.gg = torch.cat(gg_parts).to(dev)
+        self.bsign = bsign.to(dev)
+        mk = lambda items: torch.tensor(items if items else [(0, 0)], dtype=torch.int32).reshape(-1, 2).contiguous().to(dev)
+        self.items_high, self.n_high = mk(hi_items), len(hi_items)
+        self.items_low, self.n_low = mk(lo_items), len(lo_items)
+        self.scratch = torch.empty(max(1, off_ll if hi_items else 1), dtype=torch.float32, device=dev)
+        self.wu = torch.zeros(T, self.wn, dtype=torch.float32, device=dev)
+        self.theta0 = torch.zeros(off_dd, dtype=torch.float32, device=dev)
+        self.theta = torch.zeros(off_dd, dtype=torch.float32, device=dev)
+        self.dtheta = torch.zeros(off_dd, dtype=torch.float32, device=dev)
+
+    # algorithmic HBM bytes of one forward / backward: 6 B per LL element + 8 / 4 B per DD element
+    def algorithmic_bytes(self):
+        dd = sum(self.numels)
+        return 6 * self.total_ll + 8 * dd, 6 * self.total_ll + 4 * dd
+
+    def set_theta0(self, tensors):
+        for off, n, t in zip(self.offsets, self.numels, tensors):
+            self.theta0[off:off + n].copy_(t.detach().reshape(-1).to(self.device, torch.float32))
+
+    def views(self, flat):
+        return [flat[off:off + n].view(shape) for off, n, shape in zip(self.offsets, self.numels, self.shapes)]
+
+    def project(self, V):
+        """theta (flat) = theta0 + Fastfood(V); returns the persistent flat buffer."""
+        if not V.is_cuda or V.dtype != torch.float32 or V.numel() != self.d or not V.is_contiguous():
+            raise RuntimeError("Fastfood: V must be a contiguous CUDA fp32 vector of the intrinsic dimension")
+        s = torch.cuda.current_stream().cuda_stream
+        _lib.check(_lib.load().peft_fastfood_fwd(V.data_ptr(), self.d, self.wn, self.desc.data_ptr(), self.T,
+                                                 self.items_high.data_ptr(), self.n_high, self.items_low.data_ptr(), self.n_low,
+                                                 self.pi_lo.data_ptr(), self.gg.data_ptr(), self.bsign.data_ptr(),
+                                                 self.theta0.data_ptr(), self.theta.data_ptr(), self.wu.data_ptr(),
+                                                 self.scratch.data_ptr(), s), "peft_fastfood_fwd")
+        return self.theta
+
+    def project_backward(self, dtheta_flat):
+        """dV [d] from the flat gradient w.r.t. theta."""
+        dV = torch.zeros(self.d, dtype=torch.float32, device=self.device)
+        s = torch.cuda.current_stream().cuda_stream
+        _lib.check(_lib.load().peft_fastfood_bwd(dtheta_flat.data_ptr(), self.d, self.wn, self.desc.data_ptr(), self.T,
+                                                 self.items_high.data_ptr(), self.n_high, self.items_low.data_ptr(), self.n_low,
+                                                 self.pi_lo.data_ptr(), self.gg.data_ptr(), self.bsign.data_ptr(),
+                                                 self.wu.data_ptr(), self.scratch.data_ptr(), dV.data_ptr(), s), "peft_fastfood_bwd")
+        return dV
+
+
+class _FastfoodFn(torch.autograd.Function):
+    """V -> tuple of per-tensor views of the flat theta buffer."""
+
+    @staticmethod
+    def forward(ctx, V, plan: FastfoodPlan):
+        ctx.plan = plan
+        flat = plan.project(V.contiguous())
+        return tuple(plan.views(flat))
+
+    @staticmethod
+    def backward(ctx, *grads):
+        plan = ctx.plan
+        dst = plan.views(plan.dtheta)
+        for g, d in zip(grads, dst):
+            if g is None:
+                d.zero_()
+            else:
+                d.copy_(g)
+        return plan.project_backward(plan.dtheta), None
+
+
+class FastfoodWrap(nn.Module):
+    def __init__(self, module, intrinsic_dimension, device=0):
+        super().__init__()
+        self.m = [module]                    # hidden from parameters(), as in the reference (:19)
+        self.name_base_localname = []
+        self.initial_value = dict()
+        self.fastfood_params = {}
+        dev = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("peft_b200 FastfoodWrap runs on CUDA only (no CPU fallback)")
+        self.V = nn.Parameter(torch.zeros(intrinsic_dimension, device=dev))
+        shapes, params = [], []
+        for name, param in module.named_parameters():
+            if param.requires_grad:
+                self.initial_value[name] = v0 = param.clone().detach().requires_grad_(False).to(dev)
+                DD = int(np.prod(v0.size()))
+                self.fastfood_params[name] = fp = fastfood_vars(DD)
+                shapes.append(tuple(v0.size()))
+                params.append(fp)
+                base, localname = module, name
+                while "." in localname:
+                    prefix, localname = localname.split(".", 1)
+                    base = base.__getattr__(prefix)
+                self.name_base_localname.append((name, base, localname))
+        for name, base, localname in self.name_base_localname:
+            delattr(base, localname)
+        self.plan = FastfoodPlan(shapes, params, intrinsic_dimension, dev)
+        self.plan.set_theta0([self.initial_value[n] for n, _, _ in self.name_base_localname])
+
+    def project(self):
+        """The wrapped tensors theta0 + Fastfood(V), in wrap order (differentiable w.r.t. V)."""
+        return _FastfoodFn.apply(self.V, self.plan)
+
+    def forward(self, x):
+        thetas = self.project()
+        for (name, base, localname), th in zip(self.name_base_localname, thetas):
+            setattr(base, localname, th)
+        return self.m[0](x)

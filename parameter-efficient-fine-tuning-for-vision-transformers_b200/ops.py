@@ -134,7 +134,7 @@ def im2col_patches(images, patches, patch):
     B, C, Hh, Ww = images.shape
     if C != 3 or Hh != Ww or images.dtype != torch.float32 or not images.is_contiguous() or not images.is_cuda:
         raise ValueError("im2col_patches: images must be contiguous CUDA fp32 [B,3,S,S]")
-    _lib.check(_lib.load().peft_im2col_patches(images.data_ptr(), patches.data_ptr(), B, Hh, patch, _stream()),
+    _lib.check(_lib.load().peft_im2col_patches(images.data_ptr(), patches.data_ptr(), patches.stride(0), B, Hh, patch, _stream()),
                "peft_im2col_patches")
     return patches
 
@@ -156,3 +156,14 @@ def tn_reduce(x, y, out):
         raise ValueError("tn_reduce: shape mismatch")
     _lib.check(_lib.load().peft_tn_reduce(px, ldx, I, py, ldy, J, po, ldo, M, _stream()), "peft_tn_reduce")
     return out
+
+
+def clip_delta(qkv, delta, B, H, L, mult_q, mult_v, backward=False):
+    """CLIP-dialect raw-reshape placement of the q/v update, see peft_clip_delta."""
+    pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
+    pd, ldd = _mat(delta, torch.bfloat16, "delta")
+    if qkv.shape[0] != B * L or delta.shape[0] != B * L or delta.shape[1] != 2 * H * 64:
+        raise ValueError("clip_delta: shape mismatch")
+    _lib.check(_lib.load().peft_clip_delta(pq, ldq, pd, ldd, B, H, L, float(mult_q), float(mult_v), int(backward),
+                                           _stream()), "peft_clip_delta")
+    return delta if backward else qkv

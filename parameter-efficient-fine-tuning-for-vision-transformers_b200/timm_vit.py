@@ -191,6 +191,89 @@ def lowrank_factors_kron(rule, w_left, w_right):
     return Dn, UpT
 
 
+def lowrank_operands(attns, kind):
+    """Dn [depth, r', D], UpT [depth, r', 3D] from the attention modules' reference-named adapter parameters
+    (`phm_rule / W_left{1,2} / W_right{1,2}` or `{q,v}_proj_adapter{1,2}.weight`); shared by both dialects."""
+    if kind == "kron":
+        rule = torch.stack([a.phm_rule for a in attns])
+        dq, uq = lowrank_factors_kron(rule, torch.stack([a.W_left1 for a in attns]), torch.stack([a.W_right1 for a in attns]))
+        dv, uv = lowrank_factors_kron(rule, torch.stack([a.W_left2 for a in attns]), torch.stack([a.W_right2 for a in attns]))
+    elif kind == "lora":
+        s = attns[0].lora_attn_alpha / attns[0].lora_attn_dim
+        dq = torch.stack([a.q_proj_adapter1.weight for a in attns])
+        dv = torch.stack([a.v_proj_adapter1.weight for a in attns])
+        uq = torch.stack([a.q_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
+        uv = torch.stack([a.v_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
+    else:
+        return None, None
+    z = torch.zeros_like(uq)
+    Dn = torch.cat([dq, dv], dim=1)
+    UpT = torch.cat([torch.cat([uq, z, z], dim=2), torch.cat([z, z, uv], dim=2)], dim=1)
+    return Dn, UpT
+
+
+def lowrank_rank(attn, kind):
+    if kind == "kron":
+        n = attn.phm_rule.shape[0]
+        return 2 * n * attn.phm_rank * n
+    if kind == "lora":
+        return 2 * attn.lora_attn_dim
+    return 0
+
+
+def bottleneck_operands(blocks, kind):
+    st = torch.stack
+    if kind == "houlsby":
+        ad = [b.adapter for b in blocks]
+        return (st([a.adapter_down[1].weight for a in ad]), st([a.adapter_down[1].bias for a in ad]),
+                st([a.adapter_up.weight for a in ad]), st([a.adapter_up.bias for a in ad]),
+                st([a.adapter_norm_before.weight for a in ad]), st([a.adapter_norm_before.bias for a in ad]))
+    if kind == "compacter":
+        ad = [b.compacter for b in blocks]
+        return (st([a.down_PHM.dense().t() for a in ad]), st([a.down_PHM.b for a in ad]),
+                st([a.up_sampler.dense().t() for a in ad]), st([a.up_sampler.b for a in ad]),
+                st([a.adapter_norm_before.weight for a in ad]), st([a.adapter_norm_before.bias for a in ad]))
+    return None
+
+
+def bottleneck_cfg(block0, kind):
+    if kind == "houlsby":
+        return dict(bottleneck=block0.adapter.down_sample, bn_act="relu")
+    if kind == "compacter":
+        return dict(bottleneck=block0.compacter.down_sample, bn_act="gelu_tanh")
+    return {}
+
+
+def add_qv_adapter_params(mod, dim, adapter, phm_dim=4, phm_rank=1, phm_init_range=0.01, lora_attn_dim=4, lora_attn_alpha=128):
+    """Registers the reference-named q/v adapter parameters on an attention module (both dialects use the same names:
+    FS/kadaptation.py:143-187, FS/model.py:719-736)."""
+    mod.adapter_kind = adapter
+    if adapter == "kron":
+        assert dim % phm_dim == 0
+        mod.phm_rank = phm_rank
+        mod.phm_init_range = phm_init_range
+        n, k = phm_dim, dim // phm_dim
+        mod.phm_rule = nn.Parameter(torch.empty(n, n, n).normal_(0, phm_init_range))
+        mod.W_left1 = nn.Parameter(torch.empty(n, k, phm_rank).normal_(0, phm_init_range))
+        mod.W_right1 = nn.Parameter(torch.empty(n, phm_rank, k).normal_(0, phm_init_range))
+        mod.W_left2 = nn.Parameter(torch.empty(n, k, phm_rank).normal_(0, phm_init_range))
+        mod.W_right2 = nn.Parameter(torch.empty(n, phm_rank, k).normal_(0, phm_init_range))
+        mod.phmb = nn.Parameter(torch.zeros(dim))      # allocated but unused by the reference forward (:100-101)
+    elif adapter == "lora":
+        mod.lora_attn_dim = lora_attn_dim
+        mod.lora_attn_alpha = lora_attn_alpha
+        mod.q_proj_adapter1 = nn.Linear(dim, lora_attn_dim, bias=False)
+        nn.init.normal_(mod.q_proj_adapter1.weight, std=0.02)
+        mod.q_proj_adapter2 = nn.Linear(lora_attn_dim, dim, bias=False)
+        mod.q_proj_adapter2.weight.data.zero_()
+        mod.v_proj_adapter1 = nn.Linear(dim, lora_attn_dim, bias=False)
+        nn.init.normal_(mod.v_proj_adapter1.weight, std=0.02)
+        mod.v_proj_adapter2 = nn.Linear(lora_attn_dim, dim, bias=False)
+        mod.v_proj_adapter2.weight.data.zero_()
+    elif adapter not in ("none", "houlsby", "compacter"):
+        raise ValueError(adapter)
+
+
 class VisionTransformer(nn.Module):
     """FS/kadaptation.py:352-551.  forward(x) returns the final-LayerNorm cls feature (the head is applied by the
     trainer's Classifier, as in the reference: `# x = self.head(x)`)."""
@@ -258,57 +341,19 @@ class VisionTransformer(nn.Module):
     _ADAPTER_KEYS = ("phm_rule", "W_left", "W_right", "phmb", "_proj_adapter", ".adapter.", ".compacter.")
 
     def _rank(self):
-        a0 = self.blocks[0].attn
-        if self.adapter_kind == "kron":
-            n = a0.phm_rule.shape[0]
-            return 2 * n * a0.phm_rank * n
-        if self.adapter_kind == "lora":
-            return 2 * a0.lora_attn_dim
-        return 0
+        return lowrank_rank(self.blocks[0].attn, self.adapter_kind)
 
     def lowrank_operands(self):
         """Dn [depth, r', D], UpT [depth, r', 3D] built differentiably from the reference-named parameters."""
-        D = self.embed_dim
-        attns = [b.attn for b in self.blocks]
-        if self.adapter_kind == "kron":
-            rule = torch.stack([a.phm_rule for a in attns])
-            dq, uq = lowrank_factors_kron(rule, torch.stack([a.W_left1 for a in attns]), torch.stack([a.W_right1 for a in attns]))
-            dv, uv = lowrank_factors_kron(rule, torch.stack([a.W_left2 for a in attns]), torch.stack([a.W_right2 for a in attns]))
-        elif self.adapter_kind == "lora":
-            s = attns[0].lora_attn_alpha / attns[0].lora_attn_dim
-            dq = torch.stack([a.q_proj_adapter1.weight for a in attns])
-            dv = torch.stack([a.v_proj_adapter1.weight for a in attns])
-            uq = torch.stack([a.q_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
-            uv = torch.stack([a.v_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
-        else:
-            return None, None
-        z = torch.zeros_like(uq)
-        Dn = torch.cat([dq, dv], dim=1)
-        UpT = torch.cat([torch.cat([uq, z, z], dim=2), torch.cat([z, z, uv], dim=2)], dim=1)
-        return Dn, UpT
+        return lowrank_operands([b.attn for b in self.blocks], self.adapter_kind)
 
     def bottleneck_operands(self):
         """(Wd [dep,m,D], bd [dep,m], Wu [dep,D,m], bu [dep,D], ln_g [dep,D], ln_b [dep,D]) built differentiably from the
         reference-named Houlsby / Compacter parameters; None when the model has no bottleneck adapter."""
-        st = torch.stack
-        if self.adapter_kind == "houlsby":
-            ad = [b.adapter for b in self.blocks]
-            return (st([a.adapter_down[1].weight for a in ad]), st([a.adapter_down[1].bias for a in ad]),
-                    st([a.adapter_up.weight for a in ad]), st([a.adapter_up.bias for a in ad]),
-                    st([a.adapter_norm_before.weight for a in ad]), st([a.adapter_norm_before.bias for a in ad]))
-        if self.adapter_kind == "compacter":
-            ad = [b.compacter for b in self.blocks]
-            return (st([a.down_PHM.dense().t() for a in ad]), st([a.down_PHM.b for a in ad]),
-                    st([a.up_sampler.dense().t() for a in ad]), st([a.up_sampler.b for a in ad]),
-                    st([a.adapter_norm_before.weight for a in ad]), st([a.adapter_norm_before.bias for a in ad]))
-        return None
+        return bottleneck_operands(list(self.blocks), self.adapter_kind)
 
     def _bottleneck_cfg(self):
-        if self.adapter_kind == "houlsby":
-            return dict(bottleneck=self.blocks[0].adapter.down_sample, bn_act="relu")
-        if self.adapter_kind == "compacter":
-            return dict(bottleneck=self.blocks[0].compacter.down_sample, bn_act="gelu_tanh")
-        return {}
+        return bottleneck_cfg(self.blocks[0], self.adapter_kind)
 
     # ---------------------------------------------------------------- engine plumbing
     def _frozen_items(self):
