@@ -27,13 +27,35 @@ import torch  # noqa: E402
 
 # FLOP per image, fwd + bwd with a frozen backbone (dX only, no dW): SURVEY.md §8d / BASELINE.md §3
 CONFIGS = {
-    "C3": dict(model="ViT-B/16", adapter="kron", patch=16, width=768, depth=12, heads=12, batch=256, gflop_img=71.45 + 0.17,
-               desc="ViT-B/16 + KAdaptation (n=4, rank 1) on q/v"),
-    "C2": dict(model="ViT-B/16", adapter="lora", patch=16, width=768, depth=12, heads=12, batch=256, gflop_img=71.45 + 0.17,
-               desc="ViT-B/16 + LoRA (r=4, alpha=128) on q/v"),
-    "B32": dict(model="ViT-B/32", adapter="kron", patch=32, width=768, depth=12, heads=12, batch=256, gflop_img=17.50 + 0.04,
-                desc="ViT-B/32 + KAdaptation (n=4, rank 1) on q/v"),
+    "C3": dict(model="ViT-B/16", dialect="timm", adapter="kron", patch=16, width=768, depth=12, heads=12, batch=256,
+               gflop_img=71.45 + 0.17, desc="ViT-B/16 + KAdaptation (n=4, rank 1) on q/v"),
+    "C2": dict(model="ViT-B/16", dialect="timm", adapter="lora", patch=16, width=768, depth=12, heads=12, batch=256,
+               gflop_img=71.45 + 0.17, desc="ViT-B/16 + LoRA (r=4, alpha=128) on q/v"),
+    "B32": dict(model="ViT-B/32", dialect="timm", adapter="kron", patch=32, width=768, depth=12, heads=12, batch=256,
+                gflop_img=17.50 + 0.04, desc="ViT-B/32 + KAdaptation (n=4, rank 1) on q/v"),
+    # BASELINE.json configs[0]: the reference's own CPU-runnable case (CLIP dialect: Q1/Q2 delta placement)
+    "C1": dict(model="CLIP ViT-B/32", dialect="clip", adapter="kron", patch=32, width=768, depth=12, heads=12, batch=32,
+               out_dim=512, gflop_img=17.50 + 0.04, desc="CLIP ViT-B/32 visual + KAdaptation (n=4, rank 1) on q/v"),
+    # BASELINE.json configs[3]: CLIP ViT-L/14 (seq 257) + Houlsby / Compacter (bottleneck 64), batch 128
+    "C4": dict(model="CLIP ViT-L/14", dialect="clip", adapter="houlsby", patch=14, width=1024, depth=24, heads=16, batch=128,
+               out_dim=768, gflop_img=330.2 + 4.85, desc="CLIP ViT-L/14 visual + Houlsby adapter (bottleneck 64)"),
+    "C4c": dict(model="CLIP ViT-L/14", dialect="clip", adapter="compacter", patch=14, width=1024, depth=24, heads=16, batch=128,
+                out_dim=768, gflop_img=330.2 + 4.85, desc="CLIP ViT-L/14 visual + Compacter (PHM n=32/4, bottleneck 64)"),
 }
+
+
+def vit_cfg(c, depth=None):
+    from oracle.synth import VitCfg
+    return VitCfg(dialect=c["dialect"], adapter=c["adapter"], img=224, patch=c["patch"], width=c["width"],
+                  depth=depth or c["depth"], heads=c["heads"], out_dim=c.get("out_dim", 512))
+
+
+def adapter_kwargs(c):
+    if c["adapter"] == "kron":
+        return dict(phm_dim=4, phm_rank=1)
+    if c["adapter"] == "lora":
+        return dict(lora_attn_dim=4, lora_attn_alpha=128)
+    return dict(bottleneck=64)
 
 
 def peaks():
@@ -94,9 +116,8 @@ class ClockSampler:
 def build_oracle_step(cfg_name, batch):
     from oracle import peft_oracle as O
     from oracle import synth
-    from oracle.synth import VitCfg
     c = CONFIGS[cfg_name]
-    cfg = VitCfg(dialect="timm", adapter=c["adapter"], img=224, patch=c["patch"], width=c["width"], depth=c["depth"], heads=c["heads"])
+    cfg = vit_cfg(c)
     sd = synth.make_state_dict(cfg, seed=0, grad_test=False)
     head = synth.make_head(cfg)
     names = synth.trainable_names(cfg, sd)
@@ -176,11 +197,9 @@ def main():
     import torch.distributed as dist
     import torch.nn.functional as F
     from oracle import synth                      # synthetic-weight factory only (not the oracle math)
-    from oracle.synth import VitCfg
     from peft_b200 import _lib, ops
     from peft_b200.classifier import Classifier
     from peft_b200.dist import GradBucket
-    from peft_b200.timm_vit import VisionTransformer
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -190,12 +209,17 @@ def main():
     c = dict(CONFIGS[args.config])
     depth = args.depth or c["depth"]
     Bpg = args.batch or c["batch"]
-    cfg = VitCfg(dialect="timm", adapter=c["adapter"], img=224, patch=c["patch"], width=c["width"], depth=depth, heads=c["heads"])
+    cfg = vit_cfg(c, depth)
     sd = synth.make_state_dict(cfg, seed=0, grad_test=False)
     names = set(synth.trainable_names(cfg, sd))
-    kw = dict(phm_dim=4, phm_rank=1) if c["adapter"] == "kron" else dict(lora_attn_dim=4, lora_attn_alpha=128)
-    vit = VisionTransformer(img_size=224, patch_size=c["patch"], num_classes=10, embed_dim=c["width"], depth=depth,
-                            num_heads=c["heads"], qkv_bias=True, adapter=c["adapter"], **kw)
+    kw = adapter_kwargs(c)
+    if c["dialect"] == "timm":
+        from peft_b200.timm_vit import VisionTransformer
+        vit = VisionTransformer(img_size=224, patch_size=c["patch"], num_classes=10, embed_dim=c["width"], depth=depth,
+                                num_heads=c["heads"], qkv_bias=True, adapter=c["adapter"], **kw)
+    else:
+        from peft_b200.clip_model import VisionTransformer
+        vit = VisionTransformer(224, c["patch"], c["width"], depth, c["heads"], c["out_dim"], adapter=c["adapter"], **kw)
     vit.load_state_dict(sd, strict=False)
     model = Classifier(vit, cfg.feat_dim, 10, trainable_filter=lambda n: n in names).to(dev)
     head = synth.make_head(cfg)
@@ -321,7 +345,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"{args.config}: {c['desc']}, 224x224 synthetic images, per-GPU batch {Bpg}, SGD m=0.9, 10-class BN+Linear head",
                        "global_batch": Bpg * world, "seq_len": cfg.seq, "parallelism": f"dp{world}",
-                       "l2": "per-step working set (~12 GB of activations) >> 126 MB L2; no flush needed",
+                       "l2": "per-step working set (GBs of saved activations) >> 126 MB L2; no flush needed",
                        "allreduce_bytes": bucket.nbytes},
             "step_frac_of_bf16_peak": value * flop_img / (pk["tflops"] * 1e12),
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel (all dense products of the step)",

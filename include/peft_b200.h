@@ -125,9 +125,12 @@ int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int 
  * Per tensor p (descriptor below): DD = numel, LL = 2^ll >= DD, coef = 1 / (divisor * sqrt(DD / LL)) with
  * divisor = sqrt(LL * sum(G^2)) (fastfood.py:124-148).  Device arrays, concatenated over tensors:
  *   pi_lo [sum LL] uint16 = Pi[j] mod min(LL, wn);  gg [sum LL] fp32 = G;  bsign [T, wn] fp32 = B[:wn] (zero padded);
- *   theta0 / theta / dtheta fp32 indexed by off_dd;  scratch [sum LL] fp32;  wu [T, wn] fp32 scratch.
- * wn = power of two >= d, <= 4096.  items_* are device arrays of (tensor, tile) int pairs built by the caller:
- *   items_high: for every tensor with ll > 13, tiles 0 .. LL/8192 - 1;   items_low: blocks 0 .. ceil(DD/8192) - 1. */
+ *   theta0 / theta / dtheta fp32 indexed by off_dd;  scratch [sum LL] fp32;  wu [T, wn] fp32 scratch;  counters [T] int.
+ * wn = power of two >= d, <= 4096.  `items` is a device array of (tensor, tile | kind << 30) int pairs built by the
+ * caller and ordered tensor by tensor — kind 1 = "high" tile (tensors with ll > 13: tiles 0 .. LL/8192 - 1), kind 0 =
+ * "low" block (blocks 0 .. ceil(DD/8192) - 1).  Forward lists a tensor's high tiles BEFORE its low blocks, backward
+ * its low blocks BEFORE its high tiles (the second pass waits for the first through `counters`, which relies on CTAs
+ * being dispatched in list order). */
 typedef struct {
   long long off_ll;  /* element offset of this tensor in pi_lo / gg / scratch */
   long long off_dd;  /* element offset in theta0 / theta / dtheta */
@@ -137,13 +140,13 @@ typedef struct {
   int reserved;
 } peft_ff_tensor;
 /* theta[off_dd + j] = theta0[off_dd + j] + coef * [H G Pi H B pad(V)][j],  j < DD, for every tensor */
-int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items_high,
-                      int n_high, const int* items_low, int n_low, const uint16_t* pi_lo, const float* gg,
-                      const float* bsign, const float* theta0, float* theta, float* wu, float* scratch, void* stream);
+int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items, int n_items,
+                      const uint16_t* pi_lo, const float* gg, const float* bsign, const float* theta0, float* theta,
+                      float* wu, float* scratch, int* counters, void* stream);
 /* dV[k] += sum_p coef_p * B_p[k] * [H Pi^T G H pad(dtheta_p)][k],  k < d  (caller zeroes dV; wu is zeroed inside) */
-int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items_high,
-                      int n_high, const int* items_low, int n_low, const uint16_t* pi_lo, const float* gg,
-                      const float* bsign, float* wu, float* scratch, float* dV, void* stream);
+int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items,
+                      int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign, float* wu, float* scratch,
+                      int* counters, float* dV, void* stream);
 
 #ifdef __cplusplus
 }

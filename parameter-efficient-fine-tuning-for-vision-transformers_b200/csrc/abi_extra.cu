@@ -12,16 +12,14 @@ constexpr int kFfSmemBytes = (kFfTile + kFfMaxWn) * 4;
 int ff_configure() {
   static bool done = false;
   if (done) return 0;
-  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_fwd_high_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
-  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_fwd_low_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
-  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_high_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
-  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_low_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
   done = true;
   return 0;
 }
-int ff_check(int d, int wn, int T, int n_high, int n_low) {
+int ff_check(int d, int wn, int T, int n_items) {
   PEFT_REQUIRE(d > 0 && wn >= d && wn <= kFfMaxWn && (wn & (wn - 1)) == 0, "fastfood: need d <= wn <= %d, wn a power of two (d=%d wn=%d)", kFfMaxWn, d, wn);
-  PEFT_REQUIRE(T > 0 && n_high >= 0 && n_low > 0, "fastfood: empty tensor / item list");
+  PEFT_REQUIRE(T > 0 && n_items > 0, "fastfood: empty tensor / item list");
   return 0;
 }
 }  // namespace
@@ -43,55 +41,42 @@ extern "C" int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long lon
   return 0;
 }
 
-extern "C" int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items_high,
-                                 int n_high, const int* items_low, int n_low, const uint16_t* pi_lo, const float* gg,
-                                 const float* bsign, const float* theta0, float* theta, float* wu, float* scratch,
-                                 void* stream) {
-  int rc = ff_check(d, wn, T, n_high, n_low);
+extern "C" int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items,
+                                 int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign,
+                                 const float* theta0, float* theta, float* wu, float* scratch, int* counters, void* stream) {
+  int rc = ff_check(d, wn, T, n_items);
   if (rc) return rc;
-  PEFT_REQUIRE(V && tensors && items_low && pi_lo && gg && bsign && theta0 && theta && wu && (n_high == 0 || (items_high && scratch)),
-               "peft_fastfood_fwd: null operand");
+  PEFT_REQUIRE(V && tensors && items && pi_lo && gg && bsign && theta0 && theta && wu && scratch && counters, "peft_fastfood_fwd: null operand");
   rc = ff_configure();
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  PEFT_CUDA_CHECK(cudaMemsetAsync(counters, 0, (size_t)T * sizeof(int), s));
   ff_small_kernel<0><<<T, 256, wn * 4, s>>>(tensors, bsign, V, wu, nullptr, d, wn);
   PEFT_LAUNCH_CHECK();
   FfArgs a{};
-  a.tensors = tensors; a.pi_lo = pi_lo; a.gg = gg; a.wv = wu; a.scratch = scratch; a.theta0 = theta0; a.theta = theta; a.wn = wn;
-  const int smem = (kFfTile + wn) * 4;
-  if (n_high > 0) {
-    a.items = reinterpret_cast<const int2*>(items_high);
-    ff_fwd_high_kernel<<<n_high, kFfThreads, smem, s>>>(a);
-    PEFT_LAUNCH_CHECK();
-  }
-  a.items = reinterpret_cast<const int2*>(items_low);
-  ff_fwd_low_kernel<<<n_low, kFfThreads, smem, s>>>(a);
+  a.tensors = tensors; a.items = reinterpret_cast<const int2*>(items); a.pi_lo = pi_lo; a.gg = gg; a.wv = wu; a.scratch = scratch;
+  a.theta0 = theta0; a.theta = theta; a.counters = counters; a.wn = wn;
+  ff_fwd_kernel<<<n_items, kFfThreads, (kFfTile + wn) * 4, s>>>(a);
   PEFT_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T,
-                                 const int* items_high, int n_high, const int* items_low, int n_low, const uint16_t* pi_lo,
-                                 const float* gg, const float* bsign, float* wu, float* scratch, float* dV, void* stream) {
-  int rc = ff_check(d, wn, T, n_high, n_low);
+extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items,
+                                 int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign, float* wu,
+                                 float* scratch, int* counters, float* dV, void* stream) {
+  int rc = ff_check(d, wn, T, n_items);
   if (rc) return rc;
-  PEFT_REQUIRE(dtheta && tensors && items_low && pi_lo && gg && bsign && wu && dV && (n_high == 0 || (items_high && scratch)),
-               "peft_fastfood_bwd: null operand");
+  PEFT_REQUIRE(dtheta && tensors && items && pi_lo && gg && bsign && wu && scratch && counters && dV, "peft_fastfood_bwd: null operand");
   rc = ff_configure();
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  PEFT_CUDA_CHECK(cudaMemsetAsync(counters, 0, (size_t)T * sizeof(int), s));
   PEFT_CUDA_CHECK(cudaMemsetAsync(wu, 0, (size_t)T * wn * 4, s));
   FfArgs a{};
-  a.tensors = tensors; a.pi_lo = pi_lo; a.gg = gg; a.u = wu; a.scratch = scratch; a.dtheta = dtheta; a.wn = wn;
-  const int smem = (kFfTile + wn) * 4;
-  a.items = reinterpret_cast<const int2*>(items_low);
-  ff_bwd_low_kernel<<<n_low, kFfThreads, smem, s>>>(a);
+  a.tensors = tensors; a.items = reinterpret_cast<const int2*>(items); a.pi_lo = pi_lo; a.gg = gg; a.u = wu; a.scratch = scratch;
+  a.dtheta = dtheta; a.counters = counters; a.wn = wn;
+  ff_bwd_kernel<<<n_items, kFfThreads, (kFfTile + wn) * 4, s>>>(a);
   PEFT_LAUNCH_CHECK();
-  if (n_high > 0) {
-    a.items = reinterpret_cast<const int2*>(items_high);
-    ff_bwd_high_kernel<<<n_high, kFfThreads, smem, s>>>(a);
-    PEFT_LAUNCH_CHECK();
-  }
   ff_small_kernel<1><<<T, 256, wn * 4, s>>>(tensors, bsign, nullptr, wu, dV, d, wn);
   PEFT_LAUNCH_CHECK();
   return 0;

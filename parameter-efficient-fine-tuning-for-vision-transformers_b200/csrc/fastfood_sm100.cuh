@@ -13,8 +13,12 @@
 //     contiguous "low" pass over bits [0, 13), each an 8192-element shared-memory tile (512 threads x 16 registers,
 //     radix-16 register butterflies, XOR-swizzled transposes).  Forward runs high -> low so that the low pass touches
 //     only the blocks below DD; backward runs low (non-zero blocks only) -> high.
-// HBM traffic per step: forward 10 B per LL element + 12 B per DD element, backward 8 B + (6+4) B; the single-pass
-// algorithmic minimum is 6 B per LL element + 8 B (fwd) / 4 B (bwd) per DD element.
+//   * both passes of one direction run in ONE launch: the work list is ordered tensor by tensor (forward: high tiles
+//     then low blocks; backward: low blocks then high tiles) and the second pass of a tensor waits on a per-tensor
+//     completion counter, so the fp32 intermediate of a tensor (<= 16 MB) is still in the 126 MB L2 when it is re-read
+//     (read with ld.global.cg).  CTAs are dispatched in blockIdx order, and producers never wait, so the spin is safe.
+// HBM traffic per step is then the algorithmic minimum: 6 B per LL element (uint16 Pi mod wn + fp32 G) plus 8 B (fwd:
+// theta0 read, theta write) or 4 B (bwd: dtheta read) per DD element.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -49,26 +53,32 @@ __device__ __forceinline__ void ff_butterfly16(float (&x)[16], int base, int lc,
 
 // Unnormalised Walsh-Hadamard butterflies over element bits [lc, hc) of an 8192-element tile.  On entry and exit thread
 // `tid` holds elements e = i*512 + tid (i = 0..15).  `s` is 8192 floats of shared memory (clobbered).
+// Shared-memory layout: element idx lives at ff_swz(idx) = idx ^ (((idx >> 5) & 15) << 1); the three access patterns
+// below are bank-conflict free under it, and each reduces to a per-thread constant plus a compile-time term.
 __device__ __forceinline__ void ff_tile_fwht(float (&x)[16], float* s, int lc, int hc) {
   const int tid = threadIdx.x;
   ff_butterfly16(x, 9, lc, hc);                       // bits 9..12 live in the register index
   if (lc >= 9 || hc <= 0) return;
+  float* sa = s + (tid ^ (((tid >> 5) & 15) << 1));   // ff_swz(i*512 + tid) = i*512 + (tid ^ ...)
 #pragma unroll
-  for (int i = 0; i < 16; ++i) s[ff_swz(i * 512 + tid)] = x[i];
+  for (int i = 0; i < 16; ++i) sa[i * 512] = x[i];
   __syncthreads();
-  if (hc > 5) {                                       // bits 5..8: idx = hi*512 + i*32 + lane
-    const int lane = tid & 31, hi = tid >> 5;
+  if (hc > 5) {                                       // bits 5..8: idx = hi*512 + i*32 + lane, swz = idx ^ (i << 1)
+    const int lane = tid & 31;
+    float* sb = s + (tid >> 5) * 512;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) x[i] = s[ff_swz(hi * 512 + i * 32 + lane)];
+    for (int i = 0; i < 16; ++i) x[i] = sb[i * 32 + (lane ^ (i << 1))];
     ff_butterfly16(x, 5, lc, hc);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) s[ff_swz(hi * 512 + i * 32 + lane)] = x[i];
+    for (int i = 0; i < 16; ++i) sb[i * 32 + (lane ^ (i << 1))] = x[i];
     __syncthreads();
   }
   if (lc < 5) {                                       // bits 1..4 in registers, bit 0 across the lane pair
-    const int c0 = tid & 1, q = tid >> 1;
+    const int c0 = tid & 1, q = tid >> 1;             // idx = q*32 + i*2 + c0, swz = idx ^ ((q & 15) << 1)
+    float* sc = s + q * 32 + c0;
+    const int r2 = (q & 15) << 1;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) x[i] = s[ff_swz(q * 32 + i * 2 + c0)];
+    for (int i = 0; i < 16; ++i) x[i] = sc[(i << 1) ^ r2];
     ff_butterfly16(x, 1, lc, hc);
     if (lc == 0) {
 #pragma unroll
@@ -78,16 +88,16 @@ __device__ __forceinline__ void ff_tile_fwht(float (&x)[16], float* s, int lc, i
       }
     }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) s[ff_swz(q * 32 + i * 2 + c0)] = x[i];
+    for (int i = 0; i < 16; ++i) sc[(i << 1) ^ r2] = x[i];
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 16; ++i) x[i] = s[ff_swz(i * 512 + tid)];
+  for (int i = 0; i < 16; ++i) x[i] = sa[i * 512];
 }
 
 struct FfArgs {
   const peft_ff_tensor* tensors;
-  const int2* items;            // (tensor, tile)
+  const int2* items;            // (tensor, tile | kind << 30): kind 0 = low block, 1 = high tile; ordered tensor by tensor
   const uint16_t* pi_lo;        // Pi[j] mod min(LL, wn), concatenated over tensors (off_ll)
   const float* gg;              // G, same layout
   const float* wv;              // [T, wn]: forward w = H (B .* V); unused in backward
@@ -96,138 +106,157 @@ struct FfArgs {
   const float* theta0;          // [sum DD (padded offsets)]
   float* theta;                 // forward output
   const float* dtheta;          // backward input
+  int* counters;                // [T] completed first-pass CTAs per tensor (zeroed by the host wrapper)
   int wn;
 };
 
-// ---- forward, high bits: x[j] = w[Pi[j] mod wn] * G[j] generated on the fly, butterflies over bits [13, ll) -----------
-__global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_high_kernel(FfArgs a) {
-  extern __shared__ float ff_smem[];
-  float* s = ff_smem;
-  float* w = ff_smem + kFfTile;
-  const int2 it = a.items[blockIdx.x];
-  const peft_ff_tensor t = a.tensors[it.x];
-  const int tid = threadIdx.x;
-  for (int k = tid; k < a.wn; k += kFfThreads) w[k] = a.wv[(long long)it.x * a.wn + k];
+// offset of element e = i*512 + tid of a high-pass tile inside its tensor: ((e >> lc) << 13) + (e & (2^lc - 1)), split
+// into a per-thread constant and a term that only depends on (i, lc) and therefore lives on the uniform datapath
+__device__ __forceinline__ int ff_hi_tconst(int tid, int lc) {
+  return lc >= 9 ? tid : (((tid >> lc) << kFfTileBits) + (tid & ((1 << lc) - 1)));
+}
+__device__ __forceinline__ int ff_hi_ioff(int i, int lc) {
+  return lc >= 9 ? (((i >> (lc - 9)) << kFfTileBits) + ((i & ((1 << (lc - 9)) - 1)) << 9)) : (i << (22 - lc));
+}
+__device__ __forceinline__ void ff_signal(int* counter) {       // all of this CTA's global writes -> visible, then count
+  __threadfence();
   __syncthreads();
-  const int lc = kFfTileBits - (t.ll - kFfTileBits);     // log2(columns per tile)
-  const int cmask = (1 << lc) - 1;
-  const long long base = t.off_ll + ((long long)it.y << lc);
-  float x[16];
-  auto jof = [&](int i) {
-    const int e = i * 512 + tid;
-    return base + ((long long)(e >> lc) << kFfTileBits) + (e & cmask);
-  };
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const long long j = jof(i);
-    x[i] = w[a.pi_lo[j]] * a.gg[j];
+  if (threadIdx.x == 0) atomicAdd(counter, 1);
+}
+__device__ __forceinline__ void ff_wait(const int* counter, int target) {
+  if (threadIdx.x == 0) {
+    int v;
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+      if (v < target) __nanosleep(200);
+    } while (v < target);
   }
-  ff_tile_fwht(x, s, lc, kFfTileBits);
-#pragma unroll
-  for (int i = 0; i < 16; ++i) a.scratch[jof(i)] = x[i];
+  __syncthreads();
 }
 
-// ---- forward, low bits: butterflies over bits [0, min(ll, 13)), theta = theta0 + coef * x for j < DD ------------------
-__global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_low_kernel(FfArgs a) {
+// ---- forward ---------------------------------------------------------------------------------------------------------
+// high tile: x[j] = w[Pi[j] mod wn] * G[j] generated on the fly, butterflies over bits [13, ll), fp32 intermediate out
+// low block: butterflies over bits [0, min(ll, 13)), theta = theta0 + coef * x for j < DD
+__global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_kernel(FfArgs a) {
   extern __shared__ float ff_smem[];
   float* s = ff_smem;
   float* w = ff_smem + kFfTile;
   const int2 it = a.items[blockIdx.x];
   const peft_ff_tensor t = a.tensors[it.x];
   const int tid = threadIdx.x;
-  const bool gen = t.ll <= kFfTileBits;                 // single-pass tensor: generate the input here
-  const long long LL = 1ll << t.ll;
-  const long long blk = (long long)it.y << kFfTileBits;
+  const int tile = it.y & 0x3fffffff;
+  const bool high = (it.y >> 30) != 0;
+  const uint16_t* pi = a.pi_lo + t.off_ll;
+  const float* gg = a.gg + t.off_ll;
+  float* scr = a.scratch + t.off_ll;
   float x[16];
-  if (gen) {
-    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = a.wv[(long long)it.x * a.wn + k];
+  if (high || t.ll <= kFfTileBits) {
+    const float* wv = a.wv + (long long)it.x * a.wn;
+    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = wv[k];
     __syncthreads();
+  }
+  if (high) {
+    const int lc = 2 * kFfTileBits - t.ll;               // log2(columns per tile)
+    const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const long long j = blk + i * 512 + tid;
-      x[i] = j < LL ? w[a.pi_lo[t.off_ll + j]] * a.gg[t.off_ll + j] : 0.f;
+      const int j = tc + ff_hi_ioff(i, lc);
+      x[i] = w[pi[j]] * gg[j];
     }
-  } else {
+    ff_tile_fwht(x, s, lc, kFfTileBits);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) x[i] = a.scratch[t.off_ll + blk + i * 512 + tid];
-  }
-  ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const long long j = blk + i * 512 + tid;
-    if (j < t.DD) a.theta[t.off_dd + j] = a.theta0[t.off_dd + j] + t.coef * x[i];
-  }
-}
-
-// ---- backward, low bits: x = pad(dtheta), butterflies over bits [0, min(ll,13)); single-pass tensors bin here ---------
-__global__ void __launch_bounds__(kFfThreads, 2) ff_bwd_low_kernel(FfArgs a) {
-  extern __shared__ float ff_smem[];
-  float* s = ff_smem;
-  float* bins = ff_smem + kFfTile;
-  const int2 it = a.items[blockIdx.x];
-  const peft_ff_tensor t = a.tensors[it.x];
-  const int tid = threadIdx.x;
-  const bool fin = t.ll <= kFfTileBits;
-  const long long LL = 1ll << t.ll;
-  const long long blk = (long long)it.y << kFfTileBits;
-  float x[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const long long j = blk + i * 512 + tid;
-    x[i] = j < t.DD ? a.dtheta[t.off_dd + j] : 0.f;
-  }
-  if (fin) {
-    for (int k = tid; k < a.wn; k += kFfThreads) bins[k] = 0.f;
-  }
-  ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
-  if (!fin) {
-#pragma unroll
-    for (int i = 0; i < 16; ++i) a.scratch[t.off_ll + blk + i * 512 + tid] = x[i];
+    for (int i = 0; i < 16; ++i) scr[tc + ff_hi_ioff(i, lc)] = x[i];
+    ff_signal(a.counters + it.x);
     return;
   }
-  __syncthreads();
+  const int j0 = (tile << kFfTileBits) + tid;
+  if (t.ll <= kFfTileBits) {                             // single-pass tensor: generate the input here
+    const int LL = 1 << t.ll;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int j = j0 + i * 512;
+      x[i] = j < LL ? w[pi[j]] * gg[j] : 0.f;
+    }
+  } else {
+    ff_wait(a.counters + it.x, 1 << (t.ll - kFfTileBits));
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = __ldcg(scr + j0 + i * 512);
+  }
+  ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
+  const float* th0 = a.theta0 + t.off_dd;
+  float* th = a.theta + t.off_dd;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    const long long j = blk + i * 512 + tid;
-    if (j < LL) atomicAdd(&bins[a.pi_lo[t.off_ll + j]], x[i] * a.gg[t.off_ll + j]);
+    const int j = j0 + i * 512;
+    if (j < t.DD) th[j] = th0[j] + t.coef * x[i];
   }
-  __syncthreads();
-  const int n1 = LL < a.wn ? (int)LL : a.wn;
-  for (int k = tid; k < n1; k += kFfThreads) atomicAdd(&a.u[(long long)it.x * a.wn + k], bins[k]);
 }
 
-// ---- backward, high bits: butterflies over bits [13, ll), times G, folded through Pi^T into wn bins -------------------
-__global__ void __launch_bounds__(kFfThreads, 2) ff_bwd_high_kernel(FfArgs a) {
+// ---- backward --------------------------------------------------------------------------------------------------------
+// low block: x = pad(dtheta), butterflies over bits [0, min(ll,13)); single-pass tensors bin here, others write fp32
+// high tile: butterflies over bits [13, ll), times G, folded through Pi^T into wn bins (shared atomics, then global)
+__global__ void __launch_bounds__(kFfThreads, 2) ff_bwd_kernel(FfArgs a) {
   extern __shared__ float ff_smem[];
   float* s = ff_smem;
   float* bins = ff_smem + kFfTile;
   const int2 it = a.items[blockIdx.x];
   const peft_ff_tensor t = a.tensors[it.x];
   const int tid = threadIdx.x;
-  for (int k = tid; k < a.wn; k += kFfThreads) bins[k] = 0.f;
-  const int lc = kFfTileBits - (t.ll - kFfTileBits);
-  const int cmask = (1 << lc) - 1;
-  const long long base = t.off_ll + ((long long)it.y << lc);
-  const int nblk = (t.DD + kFfTile - 1) >> kFfTileBits;   // rows (low blocks) that bwd_low wrote; the rest are zero
+  const int tile = it.y & 0x3fffffff;
+  const bool high = (it.y >> 30) != 0;
+  const uint16_t* pi = a.pi_lo + t.off_ll;
+  const float* gg = a.gg + t.off_ll;
+  float* scr = a.scratch + t.off_ll;
+  float* u = a.u + (long long)it.x * a.wn;
+  const int nblk = (t.DD + kFfTile - 1) >> kFfTileBits;   // low blocks that carry data; the rest of pad(dtheta) is zero
   float x[16];
-  auto jof = [&](int i) {
-    const int e = i * 512 + tid;
-    return base + ((long long)(e >> lc) << kFfTileBits) + (e & cmask);
-  };
+  if (high || t.ll <= kFfTileBits) {
+    for (int k = tid; k < a.wn; k += kFfThreads) bins[k] = 0.f;
+  }
+  if (!high) {
+    const int j0 = (tile << kFfTileBits) + tid;
+    const float* dth = a.dtheta + t.off_dd;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int j = j0 + i * 512;
+      x[i] = j < t.DD ? dth[j] : 0.f;
+    }
+    ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
+    if (t.ll > kFfTileBits) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) scr[j0 + i * 512] = x[i];
+      ff_signal(a.counters + it.x);
+      return;
+    }
+    __syncthreads();
+    const int LL = 1 << t.ll;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int j = j0 + i * 512;
+      if (j < LL) atomicAdd(&bins[pi[j]], x[i] * gg[j]);
+    }
+    __syncthreads();
+    const int n1 = LL < a.wn ? LL : a.wn;
+    for (int k = tid; k < n1; k += kFfThreads) atomicAdd(&u[k], bins[k]);
+    return;
+  }
+  const int lc = 2 * kFfTileBits - t.ll;
+  const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
+  ff_wait(a.counters + it.x, nblk);
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    const int row = (i * 512 + tid) >> lc;
-    x[i] = row < nblk ? a.scratch[jof(i)] : 0.f;
+    const int j = tc + ff_hi_ioff(i, lc);
+    x[i] = (j >> kFfTileBits) < nblk ? __ldcg(scr + j) : 0.f;
   }
   ff_tile_fwht(x, s, lc, kFfTileBits);
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    const long long j = jof(i);
-    atomicAdd(&bins[a.pi_lo[j]], x[i] * a.gg[j]);
+    const int j = tc + ff_hi_ioff(i, lc);
+    atomicAdd(&bins[pi[j]], x[i] * gg[j]);
   }
   __syncthreads();
-  for (int k = tid; k < a.wn; k += kFfThreads) atomicAdd(&a.u[(long long)it.x * a.wn + k], bins[k]);
+  for (int k = tid; k < a.wn; k += kFfThreads) atomicAdd(&u[k], bins[k]);
 }
 
 // ---- the wn-point transforms at the V end (one CTA per tensor) -------------------------------------------------------

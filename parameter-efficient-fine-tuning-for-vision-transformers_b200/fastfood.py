@@ -53,7 +53,7 @@ class FastfoodPlan:
         desc = np.zeros(T, dtype=_FF_DTYPE)
         off_ll = off_dd = 0
         self.offsets, self.numels, self.shapes = [], [], [tuple(s) for s in shapes]
-        hi_items, lo_items = [], []
+        fwd_items, bwd_items = [], []
         bsign = torch.zeros(T, self.wn, dtype=torch.float32)
         pi_parts, gg_parts = [], []
         for t, (shape, (BB, Pi, GG, divisor, LL)) in enumerate(zip(shapes, params)):
@@ -71,9 +71,10 @@ class FastfoodPlan:
             bsign[t, :n1] = BB[:n1]
             pi_parts.append((Pi & (n1 - 1)).to(torch.int16))     # n1 <= 4096 fits; reinterpret as uint16 on device
             gg_parts.append(GG.float())
-            if ll > 13:
-                hi_items += [(t, k) for k in range(LL // _TILE)]
-            lo_items += [(t, k) for k in range((DD + _TILE - 1) // _TILE)]
+            hi = [(t, k | (1 << 30)) for k in range(LL // _TILE)] if ll > 13 else []
+            lo = [(t, k) for k in range((DD + _TILE - 1) // _TILE)]
+            fwd_items += hi + lo           # forward: high tiles, then the low blocks that wait for them
+            bwd_items += lo + hi           # backward: the other way round
             self.offsets.append(off_dd)
             self.numels.append(DD)
             off_ll += LL
@@ -84,10 +85,10 @@ class FastfoodPlan:
         self.pi_lo = torch.cat(pi_parts).to(dev)
         self.gg = torch.cat(gg_parts).to(dev)
         self.bsign = bsign.to(dev)
-        mk = lambda items: torch.tensor(items if items else [(0, 0)], dtype=torch.int32).reshape(-1, 2).contiguous().to(dev)
-        self.items_high, self.n_high = mk(hi_items), len(hi_items)
-        self.items_low, self.n_low = mk(lo_items), len(lo_items)
-        self.scratch = torch.empty(max(1, off_ll if hi_items else 1), dtype=torch.float32, device=dev)
+        mk = lambda items: torch.tensor(items, dtype=torch.int32).reshape(-1, 2).contiguous().to(dev)
+        self.items_fwd, self.items_bwd, self.n_items = mk(fwd_items), mk(bwd_items), len(fwd_items)
+        self.counters = torch.zeros(T, dtype=torch.int32, device=dev)
+        self.scratch = torch.empty(off_ll, dtype=torch.float32, device=dev)
         self.wu = torch.zeros(T, self.wn, dtype=torch.float32, device=dev)
         self.theta0 = torch.zeros(off_dd, dtype=torch.float32, device=dev)
         self.theta = torch.zeros(off_dd, dtype=torch.float32, device=dev)
@@ -111,10 +112,10 @@ class FastfoodPlan:
             raise RuntimeError("Fastfood: V must be a contiguous CUDA fp32 vector of the intrinsic dimension")
         s = torch.cuda.current_stream().cuda_stream
         _lib.check(_lib.load().peft_fastfood_fwd(V.data_ptr(), self.d, self.wn, self.desc.data_ptr(), self.T,
-                                                 self.items_high.data_ptr(), self.n_high, self.items_low.data_ptr(), self.n_low,
+                                                 self.items_fwd.data_ptr(), self.n_items,
                                                  self.pi_lo.data_ptr(), self.gg.data_ptr(), self.bsign.data_ptr(),
                                                  self.theta0.data_ptr(), self.theta.data_ptr(), self.wu.data_ptr(),
-                                                 self.scratch.data_ptr(), s), "peft_fastfood_fwd")
+                                                 self.scratch.data_ptr(), self.counters.data_ptr(), s), "peft_fastfood_fwd")
         return self.theta
 
     def project_backward(self, dtheta_flat):
@@ -122,9 +123,10 @@ class FastfoodPlan:
         dV = torch.zeros(self.d, dtype=torch.float32, device=self.device)
         s = torch.cuda.current_stream().cuda_stream
         _lib.check(_lib.load().peft_fastfood_bwd(dtheta_flat.data_ptr(), self.d, self.wn, self.desc.data_ptr(), self.T,
-                                                 self.items_high.data_ptr(), self.n_high, self.items_low.data_ptr(), self.n_low,
+                                                 self.items_bwd.data_ptr(), self.n_items,
                                                  self.pi_lo.data_ptr(), self.gg.data_ptr(), self.bsign.data_ptr(),
-                                                 self.wu.data_ptr(), self.scratch.data_ptr(), dV.data_ptr(), s), "peft_fastfood_bwd")
+                                                 self.wu.data_ptr(), self.scratch.data_ptr(), self.counters.data_ptr(),
+                                                 dV.data_ptr(), s), "peft_fastfood_bwd")
         return dV
 
 

@@ -93,6 +93,39 @@ def bench_gemm(M=50432, iters=20):
         print(f"gemm {name:24s} M={M} N={N} K={K}: {t:7.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
 
 
+def vit_b32_shapes(D=768):
+    shapes = [(D, 3, 32, 32), (D,), (50, D), (D,), (D,)]
+    for _ in range(12):
+        shapes += [(D,), (D,), (3 * D, D), (3 * D,), (D, D), (D,), (D,), (D,), (4 * D, D), (4 * D,), (D, 4 * D), (D,)]
+    return shapes + [(D,), (D,), (D, 512)]
+
+
+def bench_fastfood(d=1000, iters=10, peak_gbs=6552.0):
+    """C5: Fastfood projection of the whole ViT-B/32 visual parameter set (152 tensors) and its backward."""
+    import numpy as np
+    from peft_b200.fastfood import FastfoodPlan
+    shapes = vit_b32_shapes()
+    gn = np.random.RandomState(0)
+    params = []
+    for s in shapes:
+        DD = int(np.prod(s))
+        LL = 2 ** int(np.ceil(np.log(DD) / np.log(2)))
+        BB = torch.randint(0, 2, (LL,)).float() * 2 - 1
+        Pi = torch.from_numpy(gn.permutation(LL)).long()
+        GG = torch.randn(LL)
+        params.append([BB, Pi, GG, torch.sqrt(LL * torch.sum(GG ** 2)), LL])
+    plan = FastfoodPlan(shapes, params, d, "cuda")
+    V = torch.randn(d, device="cuda") * 0.01
+    plan.dtheta.normal_()
+    bf, bb = plan.algorithmic_bytes()
+    tf = timeit(lambda: plan.project(V), iters=iters, warm=2)
+    tb = timeit(lambda: plan.project_backward(plan.dtheta), iters=iters, warm=2)
+    print(f"fastfood ViT-B/32 T={plan.T} sumLL={plan.total_ll / 1e6:.1f}M sumDD={sum(plan.numels) / 1e6:.2f}M d={d}: "
+          f"fwd {tf:8.1f} us  {bf / tf / 1e3:7.1f} GB/s algorithmic ({bf / 1e9:.2f} GB, {bf / tf / 1e3 / peak_gbs:.2f} of copy peak)  "
+          f"bwd {tb:8.1f} us  {bb / tb / 1e3:7.1f} GB/s ({bb / 1e9:.2f} GB, {bb / tb / 1e3 / peak_gbs:.2f})", flush=True)
+    return plan, V
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     if what in ("attn", "all"):
@@ -116,6 +149,11 @@ if __name__ == "__main__":
             ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)
         bench_ln()
         bench_reduce()
+        torch.cuda.synchronize()
+    if what in ("fastfood", "all"):
+        bench_fastfood()
+    if what == "prof_fastfood":
+        bench_fastfood(iters=1)
         torch.cuda.synchronize()
     if what in ("ln", "all"):
         bench_ln()
