@@ -119,6 +119,12 @@ int peft_tn_reduce(const void* x, long long ldx, int I, const void* y, long long
 int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int B, int H, int L, float mult_q,
                     float mult_v, int backward, void* stream);
 
+/* out[c, r] = in[r, c], bf16 [rows, cols] (pitch ldin) -> [cols, rows] (pitch ldout).  Brings the operands of a
+ * weight-gradient product dW = dY^T X (contraction over tokens) into the K-major form peft_gemm_bf16 consumes; only the
+ * full-fine-tuning / intrinsic-dimension mode computes dW (FL/intrinsic/fastfood.py:61-77 makes every wrapped weight
+ * a function of V, so autograd needs dL/dW for all of them). */
+int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream);
+
 /* Fastfood intrinsic-dimension projection over a SET of wrapped parameter tensors in one call.
  * replaces: FastfoodWrap.forward / fastfood_torched / fast_walsh_hadamard_torched and their autograd backward —
  * FL/intrinsic/fastfood.py:61-77,81-121,151-187.

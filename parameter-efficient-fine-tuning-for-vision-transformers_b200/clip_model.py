@@ -21,9 +21,8 @@ from collections import OrderedDict
 import torch
 import torch.nn as nn
 
-from .engine import EngineCfg, VitEngine, backbone
 from .timm_vit import (Adapter, HyperComplexAdapter, _no_eager, add_qv_adapter_params, bottleneck_cfg,
-                       bottleneck_operands, lowrank_operands, lowrank_rank)
+                       bottleneck_operands, lowrank_operands, lowrank_rank, run_tower)
 
 
 class LayerNorm(nn.LayerNorm):
@@ -106,7 +105,9 @@ class VisionTransformer(nn.Module):
         self.proj = nn.Parameter(scale * torch.randn(width, output_dim))
         self._geom = dict(img=input_resolution, patch=patch_size, width=width, depth=layers, heads=heads, mlp=4 * width)
         self._engine = None
+        self._engine_full = None
         self._frozen_sig = None
+        self._tower_keys = [k for k, _ in self._frozen_items()]
 
     # ---------------------------------------------------------------- engine plumbing
     def _blocks(self):
@@ -115,28 +116,14 @@ class VisionTransformer(nn.Module):
     def _frozen_items(self):
         return [(k, v) for k, v in self.state_dict(keep_vars=True).items() if not any(t in k for t in self._ADAPTER_KEYS)]
 
-    def _ensure_engine(self, device):
-        items = self._frozen_items()
-        sig = tuple((k, v.data_ptr(), v._version) for k, v in items) + (self.proj is None,)
-        if self._engine is None or self._engine.dev != device:
-            blocks = self._blocks()
-            cfg = EngineCfg(dialect="clip", rank=lowrank_rank(blocks[0].attn, self.adapter_kind),
-                            out_dim=(self.output_dim if self.proj is not None else 0),
-                            **bottleneck_cfg(blocks[0], self.adapter_kind), **self._geom)
-            self._engine = VitEngine(cfg, device)
-            self._frozen_sig = None
-        if sig != self._frozen_sig:
-            self._engine.load_frozen(dict(items))
-            self._frozen_sig = sig
-        return self._engine
-
     def forward(self, x):
-        if not x.is_cuda:
-            raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
-        eng = self._ensure_engine(x.device)
         blocks = self._blocks()
-        Dn, UpT = lowrank_operands([b.attn for b in blocks], self.adapter_kind)
-        return backbone(eng, x, Dn, UpT, bottleneck_operands(blocks, self.adapter_kind))
+        extra = dict(rank=lowrank_rank(blocks[0].attn, self.adapter_kind),
+                     out_dim=(self.output_dim if getattr(self, "proj", None) is not None else 0),
+                     **bottleneck_cfg(blocks[0], self.adapter_kind))
+        return run_tower(self, x, "clip", self._geom, extra,
+                         lambda: lowrank_operands([b.attn for b in blocks], self.adapter_kind),
+                         lambda: bottleneck_operands(blocks, self.adapter_kind))
 
 
 class CLIP(nn.Module):

@@ -41,6 +41,18 @@ extern "C" int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long lon
   return 0;
 }
 
+extern "C" int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream) {
+  PEFT_REQUIRE(rows > 0 && cols > 0 && in && out, "peft_transpose_bf16: bad shape rows=%d cols=%d", rows, cols);
+  PEFT_REQUIRE(ldin % 2 == 0 && ldout % 2 == 0 && ldin >= cols && ldout >= rows && (reinterpret_cast<uintptr_t>(in) & 3) == 0 &&
+                   (reinterpret_cast<uintptr_t>(out) & 3) == 0,
+               "peft_transpose_bf16: pitches must be even and pointers 4-byte aligned");
+  dim3 grid((cols + 63) / 64, (rows + 63) / 64);
+  transpose_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows, cols,
+                                                                                 (__nv_bfloat16*)out, ldout);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items,
                                  int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign,
                                  const float* theta0, float* theta, float* wu, float* scratch, int* counters, void* stream) {

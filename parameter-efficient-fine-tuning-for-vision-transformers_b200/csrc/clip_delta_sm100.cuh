@@ -71,4 +71,50 @@ __global__ void __launch_bounds__(256) clip_delta_kernel(__nv_bfloat16* __restri
   }
 }
 
+// out[c, r] = in[r, c] for a bf16 matrix [rows, cols] (pitch ldin) -> [cols, rows] (pitch ldout).  Used to bring the two
+// operands of a weight-gradient product dW = dY^T X (contraction over the token dimension) into the K-major form the
+// tcgen05 GEMM consumes (full fine-tuning / intrinsic-dimension mode only, SURVEY R12: "backward needs full dW").
+__global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows,
+                                                            int cols, __nv_bfloat16* __restrict__ out, long long ldout) {
+  __shared__ __nv_bfloat16 tile[64][66];
+  const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;
+  const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
+  // load: 8 warps x 8 passes, each warp reads one 64-element row as 32 x bf16x2
+#pragma unroll
+  for (int p = 0; p < 8; ++p) {
+    const int r = p * 8 + wy;
+    const int gr = r0 + r, gc = c0 + lane * 2;
+    __nv_bfloat16 a = __float2bfloat16(0.f), b = a;
+    if (gr < rows) {
+      const __nv_bfloat16* src = in + (long long)gr * ldin + gc;
+      if (gc + 1 < cols) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(src);
+        a = v.x; b = v.y;
+      } else if (gc < cols) {
+        a = src[0];
+      }
+    }
+    tile[r][lane * 2] = a;
+    tile[r][lane * 2 + 1] = b;
+  }
+  __syncthreads();
+  // store: output row = c, 64 consecutive r per row, lane writes r = 2*lane, 2*lane+1
+#pragma unroll
+  for (int p = 0; p < 8; ++p) {
+    const int c = p * 8 + wy;
+    const int gc = c0 + c, gr = r0 + lane * 2;
+    if (gc < cols) {
+      __nv_bfloat16* dst = out + (long long)gc * ldout + gr;
+      if (gr + 1 < rows) {
+        __nv_bfloat162 v;
+        v.x = tile[lane * 2][c];
+        v.y = tile[lane * 2 + 1][c];
+        *reinterpret_cast<__nv_bfloat162*>(dst) = v;
+      } else if (gr < rows) {
+        dst[0] = tile[lane * 2][c];
+      }
+    }
+  }
+}
+
 }  // namespace peft

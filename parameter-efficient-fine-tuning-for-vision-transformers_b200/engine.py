@@ -40,6 +40,7 @@ class EngineCfg:
     rank: int = 0         # low-rank q/v adapter columns r' (0 = no q/v adapter)
     bottleneck: int = 0   # Houlsby / Compacter bottleneck width after the MLP (0 = none; 64 in the reference)
     bn_act: str = "relu"  # "relu" (Houlsby, FS/adapter_model.py:304-311) | "gelu_tanh" (Compacter gelu_new, FS/compacter_model.py:376)
+    train_all: bool = False  # full fine-tuning / intrinsic-dimension mode: backward also emits dL/dW for EVERY tower tensor
 
     @property
     def seq(self):
@@ -124,6 +125,16 @@ class _Workspace:
             self.dz = e(M, m)
             self.gh = e(M, D, dt=f32)                                # gradient w.r.t. h (fp32) and its bf16 copy
             self.ghb = e(M, D)
+        if cfg.train_all:
+            # everything a weight-gradient product needs that the PEFT path recomputes or never keeps
+            self.xn2_l = [e(M, D) for _ in range(dep)]
+            self.act_l = [e(M, F) for _ in range(dep)]
+            self.ones = torch.zeros(M, 16, device=dev, dtype=bf)
+            self.ones[:, 0] = 1.0
+            Mp = (M + 7) // 8 * 8
+            self.tA = torch.zeros(max(F, 3 * D), Mp, device=dev, dtype=bf)            # dY^T  [N, tokens]
+            self.tB = torch.zeros(max(F, D, cfg.patch_k), Mp, device=dev, dtype=bf)   # X^T   [K, tokens]
+            self.mean_pre = e(M, dt=f32); self.rstd_pre = e(M, dt=f32)
         self.generation = 0
 
 
@@ -145,6 +156,10 @@ class VitEngine:
         bf, f32 = torch.bfloat16, torch.float32
         keys = _TIMM_KEYS if cfg.dialect == "timm" else _CLIP_KEYS
         g = lambda k: sd[k].detach().to(dev, f32)
+        if keys["qkv_b"].format(i=0) not in sd:           # timm qkv_bias=False
+            sd = dict(sd)
+            for i in range(dep):
+                sd[keys["qkv_b"].format(i=i)] = torch.zeros(3 * D)
         L = {k: [g(v.format(i=i)) for i in range(dep)] for k, v in keys.items()}
         # forward operands: W [N, K]; the qkv weight carries rp extra K columns for scale*Up (refreshed every step)
         self.wqkv = torch.zeros(dep, 3 * D, D + rp, device=dev, dtype=bf)
@@ -252,7 +267,9 @@ class VitEngine:
         ops.gemm(w.patches, self.patch_w, w.pe, bias=self.patch_b)
         if cfg.dialect == "clip":
             ops.assemble_tokens(w.pe, self.cls, self.pos, w.tokens, B, L, D)
-            ops.layernorm_fwd(w.tokens, self.lnpre_w, self.lnpre_b, w.x0[0], None, None, cfg.eps)
+            ta = cfg.train_all
+            ops.layernorm_fwd(w.tokens, self.lnpre_w, self.lnpre_b, w.x0[0], w.mean_pre if ta else None,
+                              w.rstd_pre if ta else None, cfg.eps)
         else:
             ops.assemble_tokens(w.pe, self.cls, self.pos, w.x0[0], B, L, D)
         scale = 64 ** -0.5
@@ -272,13 +289,15 @@ class VitEngine:
                 ops.gemm(xn1[:, :D], self.wqkv[i][:, :D], w.qkv[i], bias=self.bqkv[i])
             ops.attention_fwd(w.qkv[i], w.o[i], w.lse2[i], B, H, L, scale)
             ops.gemm(w.o[i], self.wproj[i], w.x1[i], bias=self.bproj[i], epilogue=ops.EPI_RESID_F32, aux=w.x0[i])
-            ops.layernorm_fwd(w.x1[i], self.ln2_w[i], self.ln2_b[i], w.xn2, w.mean2[i], w.rstd2[i], cfg.eps)
-            ops.gemm(w.xn2, self.wfc1[i], w.h[i], bias=self.bfc1[i], epilogue=self.act_fwd, out2=w.act)
+            xn2 = w.xn2_l[i] if cfg.train_all else w.xn2
+            act = w.act_l[i] if cfg.train_all else w.act
+            ops.layernorm_fwd(w.x1[i], self.ln2_w[i], self.ln2_b[i], xn2, w.mean2[i], w.rstd2[i], cfg.eps)
+            ops.gemm(xn2, self.wfc1[i], w.h[i], bias=self.bfc1[i], epilogue=self.act_fwd, out2=act)
             if not m:
-                ops.gemm(w.act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i])
+                ops.gemm(act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i])
             else:
                 # x_{i+1} = x1 + h + up(act(down(LN_a(h)))),  h = mlp(ln2(x1))     (adapter_model.py:330-334 computed once, Q6)
-                ops.gemm(w.act, self.wfc2[i], w.hf[i], bias=self.bfc2[i], epilogue=ops.EPI_STORE_F32)
+                ops.gemm(act, self.wfc2[i], w.hf[i], bias=self.bfc2[i], epilogue=ops.EPI_STORE_F32)
                 ops.layernorm_fwd_add(w.hf[i], self.lga[i], self.lba[i], w.za[i], w.mean_a[i], w.rstd_a[i], w.x1[i], w.x0[i + 1], 1e-5)
                 z = w.zext[i][:, :m]
                 if cfg.bn_act == "relu":
@@ -384,6 +403,139 @@ class VitEngine:
         if r:
             return dDn[:, :r], dUpT[:, :r], bng
         return None, None, bng
+
+
+
+    # ------------------------------------------------------------------ backward, full fine-tuning mode
+    def _dw(self, w, dY, X, out):
+        """out[N, K] (fp32) = dY[M, N]^T X[M, K]: both operands transposed to K-major, then the tcgen05 GEMM."""
+        M = dY.shape[0]
+        Mp = (M + 7) // 8 * 8                      # contraction length padded to the GEMM's K granularity; the pad
+        a = w.tA[:dY.shape[1]]                     # columns [M, Mp) of tA / tB are never written and stay zero
+        b = w.tB[:X.shape[1]]
+        ops.transpose(dY, a[:, :M])
+        ops.transpose(X, b[:, :M])
+        ops.gemm(a[:, :Mp], b[:, :Mp], out, epilogue=ops.EPI_STORE_F32)
+
+    def backward_full(self, dfeat):
+        """dL/d(every tower tensor) -> {reference key: fp32 grad}.  Only for cfg.train_all (no adapters): the Fastfood /
+        full-fine-tuning configuration C5, where theta is a function of V and autograd needs every dW
+        (FL/intrinsic/fastfood.py:61-77).  Same kernels as the PEFT backward plus, per linear layer, one weight-gradient
+        product (two transposes + GEMM) and one bias column-sum; LayerNorm backward also emits dgamma / dbeta."""
+        cfg = self.cfg
+        if not cfg.train_all or cfg.rank or cfg.bottleneck:
+            raise RuntimeError("backward_full needs an engine built with train_all=True and no adapter")
+        D, L, H, dep, F = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.mlp
+        B = dfeat.shape[0]
+        w = self._workspace(B)
+        if self._fwd_generation != (B, w.generation):
+            raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
+        dev, f32 = self.dev, torch.float32
+        z = lambda *sh: torch.zeros(*sh, device=dev, dtype=f32)
+        e = lambda *sh: torch.empty(*sh, device=dev, dtype=f32)
+        dfeat = dfeat.contiguous().float()
+        keys = _TIMM_KEYS if cfg.dialect == "timm" else _CLIP_KEYS
+        G = {}
+        w.g.zero_()
+        w.gb.zero_()
+        xcls = w.x0[dep].view(B, L * D)[:, :D]
+        gcls = w.g.view(B, L * D)[:, :D]
+        gbcls = w.gb.view(B, L * D)[:, :D]
+        dlnf_w, dlnf_b = z(D), z(D)
+        if self.vproj is None:
+            ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dlnf_w, dlnf_b)
+        else:
+            dfb = dfeat.to(torch.bfloat16)
+            dproj = e(D, cfg.out_dim)
+            self._dw(w, w.yf, dfb, dproj)                                          # proj [D, E] = yf^T dfeat
+            G["proj"] = dproj
+            ops.gemm(dfb, self.vproj, w.dyf)
+            ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dlnf_w, dlnf_b)
+        if cfg.dialect == "timm":
+            G["norm.weight"], G["norm.bias"] = dlnf_w, dlnf_b
+        else:
+            G["ln_post.weight"], G["ln_post.bias"] = dlnf_w, dlnf_b
+        scale = 64 ** -0.5
+        dq = w.dqkv[:, :3 * D]
+        for i in reversed(range(dep)):
+            k = lambda n: keys[n].format(i=i)
+            # MLP
+            c16 = z(16, D); self_dw = e(D, F)
+            ops.tn_reduce(w.ones, w.gb, c16)
+            self._dw(w, w.gb, w.act_l[i], self_dw)
+            G[k("fc2_b")], G[k("fc2_w")] = c16[0], self_dw
+            ops.gemm(w.gb, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
+            c16 = z(16, F); dw1 = e(F, D)
+            ops.tn_reduce(w.ones, w.dh, c16)
+            self._dw(w, w.dh, w.xn2_l[i], dw1)
+            G[k("fc1_b")], G[k("fc1_w")] = c16[0], dw1
+            ops.gemm(w.dh, self.wfc1T[i], w.dxn)
+            dg, db = z(D), z(D)
+            ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb, dg, db)
+            G[k("ln2_w")], G[k("ln2_b")] = dg, db
+            # attention
+            c16 = z(16, D); dwp = e(D, D)
+            ops.tn_reduce(w.ones, w.gb, c16)
+            self._dw(w, w.gb, w.o[i], dwp)
+            G[k("proj_b")], G[k("proj_w")] = c16[0], dwp
+            ops.gemm(w.gb, self.wprojT[i], w.d_o)
+            ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
+            c16 = z(16, 3 * D); dwq = e(3 * D, D)
+            ops.tn_reduce(w.ones, dq, c16)
+            self._dw(w, dq, w.xn1[i][:, :D], dwq)
+            G[k("qkv_b")], G[k("qkv_w")] = c16[0], dwq
+            ops.gemm(dq, self.wqkvT[i][:, :3 * D], w.dxn)
+            dg, db = z(D), z(D)
+            ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb, dg, db)
+            G[k("ln1_w")], G[k("ln1_b")] = dg, db
+        # embedding: w.g = dL/dx0 (fp32 [B, L, D])
+        if cfg.dialect == "clip":
+            dg, db = z(D), z(D)
+            ops.layernorm_bwd_f32g(w.g, w.tokens, w.mean_pre, w.rstd_pre, self.lnpre_w, None, w.x1[0], w.gb, dg, db)
+            G["ln_pre.weight"], G["ln_pre.bias"] = dg, db
+            g3 = w.x1[0].view(B, L, D)          # x1[0] is dead by now: reuse it for dL/d(tokens before ln_pre)
+        else:
+            g3 = w.g.view(B, L, D)
+        dpos = g3.sum(0)                                     # [L, D] batch reduction of the token gradient (glue)
+        P = L - 1
+        dpe = w.gb.view(B, L, D)[:, 1:, :].reshape(B * P, D)
+        kk = 3 * cfg.patch * cfg.patch
+        dconv = e(D, kk)
+        self._dw(w, dpe, w.patches[:, :kk], dconv)
+        if cfg.dialect == "timm":
+            c16 = z(16, D)
+            ops.tn_reduce(w.ones[:B * P], dpe, c16)
+            G["patch_embed.proj.weight"] = dconv.view(D, 3, cfg.patch, cfg.patch)
+            G["patch_embed.proj.bias"] = c16[0]
+            G["cls_token"] = dpos[0].view(1, 1, D)
+            G["pos_embed"] = dpos.view(1, L, D)
+        else:
+            G["conv1.weight"] = dconv.view(D, 3, cfg.patch, cfg.patch)
+            G["class_embedding"] = dpos[0]
+            G["positional_embedding"] = dpos
+        return G
+
+
+class _BackboneFullFn(torch.autograd.Function):
+    """Tower with EVERY tensor differentiable: forward re-reads the weights (they are functions of V under FastfoodWrap),
+    backward returns dL/dW for each of them in the order they were passed."""
+
+    @staticmethod
+    def forward(ctx, engine, images, names, *tensors):
+        ctx.engine, ctx.names = engine, names
+        engine.load_frozen({n: t.detach() for n, t in zip(names, tensors)})
+        return engine.forward(images)
+
+    @staticmethod
+    def backward(ctx, dfeat):
+        G = ctx.engine.backward_full(dfeat)
+        return (None, None, None) + tuple(G.get(n) for n in ctx.names)
+
+
+def backbone_full(engine: VitEngine, images, named_tensors):
+    """Differentiable w.r.t. every tower tensor; `named_tensors` = [(reference key, tensor)]."""
+    names = tuple(n for n, _ in named_tensors)
+    return _BackboneFullFn.apply(engine, images, names, *[t for _, t in named_tensors])
 
 
 class _BackboneFn(torch.autograd.Function):

@@ -167,3 +167,14 @@ def clip_delta(qkv, delta, B, H, L, mult_q, mult_v, backward=False):
     _lib.check(_lib.load().peft_clip_delta(pq, ldq, pd, ldd, B, H, L, float(mult_q), float(mult_v), int(backward),
                                            _stream()), "peft_clip_delta")
     return delta if backward else qkv
+
+
+def transpose(x, out):
+    """out[c, r] = x[r, c] (bf16)."""
+    px, ldx = _mat(x, torch.bfloat16, "x")
+    po, ldo = _mat(out, torch.bfloat16, "out")
+    R, Cc = x.shape
+    if tuple(out.shape) != (Cc, R):
+        raise ValueError("transpose: out must be [cols, rows]")
+    _lib.check(_lib.load().peft_transpose_bf16(px, ldx, R, Cc, po, ldo, _stream()), "peft_transpose_bf16")
+    return out

@@ -18,7 +18,7 @@ from functools import partial
 import torch
 import torch.nn as nn
 
-from .engine import EngineCfg, VitEngine, backbone
+from .engine import EngineCfg, VitEngine, backbone, backbone_full
 
 
 def _no_eager(self, *a, **k):
@@ -274,6 +274,48 @@ def add_qv_adapter_params(mod, dim, adapter, phm_dim=4, phm_rank=1, phm_init_ran
         raise ValueError(adapter)
 
 
+def tower_tensors(root, keys):
+    """[(key, tensor)] read through ATTRIBUTE ACCESS on every call: under FastfoodWrap the parameters have been deleted
+    and are re-set as plain (non-leaf) tensors each forward (FL/intrinsic/fastfood.py:52-57,61-77)."""
+    out = []
+    for key in keys:
+        obj = root
+        *path, leaf = key.split(".")
+        for p in path:
+            obj = getattr(obj, p)
+        t = getattr(obj, leaf)
+        if t is not None:
+            out.append((key, t))
+    return out
+
+
+def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck):
+    """Shared forward of both dialects' VisionTransformer: picks the PEFT engine (frozen tower, adapters trainable) or the
+    full engine (any tower tensor requires grad: full fine-tuning, bias/LayerNorm tuning, Fastfood)."""
+    if not x.is_cuda:
+        raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
+    tensors = tower_tensors(model, model._tower_keys)
+    full = torch.is_grad_enabled() and any(t.requires_grad for _, t in tensors)
+    if full and model.adapter_kind != "none":
+        raise NotImplementedError("training tower weights together with an adapter is not supported: freeze the tower "
+                                  "(PEFT) or build the model with adapter='none' (full fine-tuning / Fastfood)")
+    slot = "_engine_full" if full else "_engine"
+    eng = getattr(model, slot, None)
+    if eng is None or eng.dev != x.device:
+        eng = VitEngine(EngineCfg(dialect=dialect, train_all=full, **extra_cfg, **geom), x.device)
+        setattr(model, slot, eng)
+        model._frozen_sig = None
+    if full:
+        return backbone_full(eng, x, tensors)
+    cacheable = all(isinstance(t, nn.Parameter) for _, t in tensors)
+    sig = (slot,) + tuple((k, t.data_ptr(), t._version) for k, t in tensors) if cacheable else None
+    if sig is None or sig != model._frozen_sig:
+        eng.load_frozen({k: t.detach() for k, t in tensors})
+        model._frozen_sig = sig
+    Dn, UpT = lowrank()
+    return backbone(eng, x, Dn, UpT, bottleneck())
+
+
 class VisionTransformer(nn.Module):
     """FS/kadaptation.py:352-551.  forward(x) returns the final-LayerNorm cls feature (the head is applied by the
     trainer's Classifier, as in the reference: `# x = self.head(x)`)."""
@@ -311,7 +353,10 @@ class VisionTransformer(nn.Module):
         self._cfg = dict(img=img_size, patch=patch_size, width=embed_dim, depth=depth, heads=num_heads,
                          mlp=int(embed_dim * mlp_ratio))
         self._engine = None
+        self._engine_full = None
         self._frozen_sig = None
+        self._tower_keys = [k for k, _ in self._frozen_items()]
+        self._qkv_bias = qkv_bias
 
     @staticmethod
     def _init_weights_trunc_normal(m):
@@ -360,27 +405,9 @@ class VisionTransformer(nn.Module):
         return [(k, v) for k, v in self.state_dict(keep_vars=True).items()
                 if not any(t in k for t in self._ADAPTER_KEYS) and not k.startswith("head.")]
 
-    def _ensure_engine(self, device):
-        items = self._frozen_items()
-        sig = tuple((k, v.data_ptr(), v._version) for k, v in items)
-        if self._engine is None or self._engine.dev != device:
-            self._engine = VitEngine(EngineCfg(dialect="timm", rank=self._rank(), **self._bottleneck_cfg(), **self._cfg), device)
-            self._frozen_sig = None
-        if sig != self._frozen_sig:
-            sd = dict(items)
-            if self.blocks[0].attn.qkv.bias is None:
-                for i in range(len(self.blocks)):
-                    sd[f"blocks.{i}.attn.qkv.bias"] = torch.zeros(3 * self.embed_dim)
-            self._engine.load_frozen(sd)
-            self._frozen_sig = sig
-        return self._engine
-
     def forward_features(self, x):
-        if not x.is_cuda:
-            raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
-        eng = self._ensure_engine(x.device)
-        Dn, UpT = self.lowrank_operands()
-        return backbone(eng, x, Dn, UpT, self.bottleneck_operands())
+        extra = dict(rank=self._rank(), **self._bottleneck_cfg())
+        return run_tower(self, x, "timm", self._cfg, extra, self.lowrank_operands, self.bottleneck_operands)
 
     def forward(self, x):
         return self.forward_features(x)
