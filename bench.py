@@ -39,6 +39,9 @@ CONFIGS = {
     # BASELINE.json configs[3]: CLIP ViT-L/14 (seq 257) + Houlsby / Compacter (bottleneck 64), batch 128
     "C4": dict(model="CLIP ViT-L/14", dialect="clip", adapter="houlsby", patch=14, width=1024, depth=24, heads=16, batch=128,
                out_dim=768, gflop_img=330.2 + 4.85, desc="CLIP ViT-L/14 visual + Houlsby adapter (bottleneck 64)"),
+    # BASELINE.json configs[4]: intrinsic-dimension fine-tuning, Fastfood d=1000 over the whole visual tower (dW needed)
+    "C5": dict(model="ViT-B/32", dialect="timm", adapter="none", patch=32, width=768, depth=12, heads=12, batch=256,
+               gflop_img=26.22, fastfood_d=1000, desc="ViT-B/32 + Fastfood intrinsic dimension d=1000 over all 152 tower tensors"),
     "C4c": dict(model="CLIP ViT-L/14", dialect="clip", adapter="compacter", patch=14, width=1024, depth=24, heads=16, batch=128,
                 out_dim=768, gflop_img=330.2 + 4.85, desc="CLIP ViT-L/14 visual + Compacter (PHM n=32/4, bottleneck 64)"),
 }
@@ -122,6 +125,27 @@ def build_oracle_step(cfg_name, batch):
     head = synth.make_head(cfg)
     names = synth.trainable_names(cfg, sd)
     images, labels = synth.make_batch(cfg, batch)
+    if c.get("fastfood_d"):
+        import numpy as np
+        d = c["fastfood_d"]
+        gn, gt = np.random.RandomState(0), torch.Generator().manual_seed(0)
+        ff = {k: O.fastfood_vars(v.numel(), gn, gt) for k, v in sd.items()}
+        V = torch.zeros(d)
+        momV = torch.zeros(d)
+
+        def ff_step():
+            V.requires_grad_(True)
+            V.grad = None
+            sdp = {k: v + O.fastfood_torched(V, v.numel(), ff[k]).view(v.shape) for k, v in sd.items()}
+            feat = O.visual_forward(images, sdp, cfg)
+            loss = torch.nn.functional.cross_entropy(O.classifier_logits(feat, head, True), labels)
+            loss.backward()
+            with torch.no_grad():
+                momV.mul_(0.9).add_(V.grad)
+                V.requires_grad_(False)
+                V.sub_(1e-3 * momV)
+            return float(loss)
+        return ff_step
     mom = {k: torch.zeros_like(sd[k]) for k in names}
 
     def step():
@@ -221,6 +245,15 @@ def main():
         from peft_b200.clip_model import VisionTransformer
         vit = VisionTransformer(224, c["patch"], c["width"], depth, c["heads"], c["out_dim"], adapter=c["adapter"], **kw)
     vit.load_state_dict(sd, strict=False)
+    if c.get("fastfood_d"):
+        from peft_b200.fastfood import FastfoodWrap
+        import numpy as np
+        torch.manual_seed(0)
+        np.random.seed(0)
+        for n_, p_ in vit.named_parameters():
+            p_.requires_grad_(not n_.startswith("head."))
+        vit = FastfoodWrap(vit.to(dev), c["fastfood_d"], device=local_rank)
+        names = {"V"}
     model = Classifier(vit, cfg.feat_dim, 10, trainable_filter=lambda n: n in names).to(dev)
     head = synth.make_head(cfg)
     model.layers[0].load_state_dict({"weight": head["layers.0.weight"], "bias": head["layers.0.bias"]})
