@@ -427,7 +427,13 @@ def main():
             line["cpu_baseline"] = base
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # A process group whose NCCL kernels were captured into a live CUDA graph can hang in destroy_process_group();
+        # every rank has its result by now, so synchronise, flush and leave without the teardown.
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
