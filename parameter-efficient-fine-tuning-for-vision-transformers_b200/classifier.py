@@ -12,14 +12,18 @@ import torch.nn.functional as F
 
 
 class Classifier(nn.Module):
-    def __init__(self, backbone: nn.Module, feat_dim: int, num_classes: int, trainable_filter=None):
+    def __init__(self, backbone: nn.Module, feat_dim: int, num_classes: int, trainable_filter=None, sync_bn: bool = False):
         super().__init__()
         self.backbone = backbone
         if trainable_filter is not None:
             # the reference freezes everything whose name does not match ('adapter' / 'compacter' / 'W'), :99-116
             for n, p in self.backbone.named_parameters():
                 p.requires_grad = bool(trainable_filter(n))
-        self.channel_bn = nn.BatchNorm1d(feat_dim, affine=False)
+        if sync_bn:     # multi-GPU option: batch statistics over the global batch (peft_b200.dist.GlobalBatchNorm1d)
+            from .dist import GlobalBatchNorm1d
+            self.channel_bn = GlobalBatchNorm1d(feat_dim)
+        else:
+            self.channel_bn = nn.BatchNorm1d(feat_dim, affine=False)
         self.layers = nn.Sequential(nn.Linear(feat_dim, num_classes))
 
     def forward(self, img):

@@ -150,19 +150,22 @@ __global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_kernel(FfArgs a) {
   const float* gg = a.gg + t.off_ll;
   float* scr = a.scratch + t.off_ll;
   float x[16];
-  if (high || t.ll <= kFfTileBits) {
-    const float* wv = a.wv + (long long)it.x * a.wn;
-    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = wv[k];
-    __syncthreads();
-  }
+  const float* wv = a.wv + (long long)it.x * a.wn;
   if (high) {
+    // all global loads of the tile are issued before the first barrier so that their latencies overlap
     const int lc = 2 * kFfTileBits - t.ll;               // log2(columns per tile)
     const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
+    uint16_t pv[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int j = tc + ff_hi_ioff(i, lc);
-      x[i] = w[pi[j]] * gg[j];
+      pv[i] = pi[j];
+      x[i] = gg[j];
     }
+    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = wv[k];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] *= w[pv[i]];
     ff_tile_fwht(x, s, lc, kFfTileBits);
 #pragma unroll
     for (int i = 0; i < 16; ++i) scr[tc + ff_hi_ioff(i, lc)] = x[i];
@@ -170,25 +173,37 @@ __global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_kernel(FfArgs a) {
     return;
   }
   const int j0 = (tile << kFfTileBits) + tid;
+  const float* th0 = a.theta0 + t.off_dd;
+  float* th = a.theta + t.off_dd;
+  float t0v[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {                         // theta0 is independent of everything else: fetch it first
+    const int j = j0 + i * 512;
+    t0v[i] = j < t.DD ? th0[j] : 0.f;
+  }
   if (t.ll <= kFfTileBits) {                             // single-pass tensor: generate the input here
     const int LL = 1 << t.ll;
+    uint16_t pv[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int j = j0 + i * 512;
-      x[i] = j < LL ? w[pi[j]] * gg[j] : 0.f;
+      pv[i] = j < LL ? pi[j] : (uint16_t)0;
+      x[i] = j < LL ? gg[j] : 0.f;
     }
+    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = wv[k];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] *= w[pv[i]];
   } else {
     ff_wait(a.counters + it.x, 1 << (t.ll - kFfTileBits));
 #pragma unroll
     for (int i = 0; i < 16; ++i) x[i] = __ldcg(scr + j0 + i * 512);
   }
   ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
-  const float* th0 = a.theta0 + t.off_dd;
-  float* th = a.theta + t.off_dd;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
     const int j = j0 + i * 512;
-    if (j < t.DD) th[j] = th0[j] + t.coef * x[i];
+    if (j < t.DD) th[j] = fmaf(t.coef, x[i], t0v[i]);
   }
 }
 
@@ -242,6 +257,14 @@ __global__ void __launch_bounds__(kFfThreads, 2) ff_bwd_kernel(FfArgs a) {
   }
   const int lc = 2 * kFfTileBits - t.ll;
   const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
+  uint16_t pv[16];
+  float gv[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {                         // Pi and G do not depend on the first pass: fetch before waiting
+    const int j = tc + ff_hi_ioff(i, lc);
+    pv[i] = pi[j];
+    gv[i] = gg[j];
+  }
   ff_wait(a.counters + it.x, nblk);
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
@@ -251,10 +274,7 @@ __global__ void __launch_bounds__(kFfThreads, 2) ff_bwd_kernel(FfArgs a) {
   ff_tile_fwht(x, s, lc, kFfTileBits);
   __syncthreads();
 #pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int j = tc + ff_hi_ioff(i, lc);
-    atomicAdd(&bins[pi[j]], x[i] * gg[j]);
-  }
+  for (int i = 0; i < 16; ++i) atomicAdd(&bins[pv[i]], x[i] * gv[i]);
   __syncthreads();
   for (int k = tid; k < a.wn; k += kFfThreads) atomicAdd(&u[k], bins[k]);
 }

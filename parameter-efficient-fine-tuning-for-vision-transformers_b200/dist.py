@@ -53,3 +53,37 @@ class GradBucket:
             return
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
         self.flat.mul_(1.0 / ws)
+
+
+class GlobalBatchNorm1d(torch.nn.Module):
+    """BatchNorm1d(affine=False) whose TRAIN-mode statistics are taken over the global batch (all ranks), so that an N-rank
+    step equals the 1-rank step on the concatenated batch (SURVEY §8e "BN head").  The reference head is
+    `nn.BatchNorm1d(E, affine=False)` (few_shot/vision_benchmark/evaluation/kadaptation_clip.py:122-125) on a single GPU;
+    this module is the optional multi-GPU counterpart (`Classifier(..., sync_bn=True)`), differentiable through the
+    exchange (`torch.distributed.nn.functional.all_reduce` of [sum x, sum x^2, count]: 2E + 1 floats).  Works on NCCL and on
+    gloo (CPU tests).  Running statistics follow nn.BatchNorm1d (momentum 0.1, unbiased running variance)."""
+
+    def __init__(self, num_features, eps=1e-5, momentum=0.1, process_group=None):
+        super().__init__()
+        self.num_features, self.eps, self.momentum, self.group = num_features, eps, momentum, process_group
+        self.register_buffer("running_mean", torch.zeros(num_features))
+        self.register_buffer("running_var", torch.ones(num_features))
+        self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
+
+    def forward(self, x):
+        if not self.training:
+            return (x - self.running_mean) / torch.sqrt(self.running_var + self.eps)
+        n_local = x.shape[0]
+        stats = torch.cat([x.sum(0), (x * x).sum(0), x.new_full((1,), float(n_local))])
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            import torch.distributed.nn.functional as dfn
+            stats = dfn.all_reduce(stats, op=dist.ReduceOp.SUM, group=self.group)
+        E = self.num_features
+        n = stats[2 * E]
+        mean = stats[:E] / n
+        var = stats[E:2 * E] / n - mean * mean
+        with torch.no_grad():
+            self.running_mean.mul_(1 - self.momentum).add_(self.momentum * mean)
+            self.running_var.mul_(1 - self.momentum).add_(self.momentum * var * n / (n - 1).clamp(min=1))
+            self.num_batches_tracked += 1
+        return (x - mean) / torch.sqrt(var + self.eps)

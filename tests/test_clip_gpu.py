@@ -35,8 +35,8 @@ def build_clip(cfg: VitCfg, sd):
 
 
 @pytest.mark.parametrize("name", ["clip_lora_modelpy", "clip_lora_lorapy", "clip_lora_b3", "clip_houlsby", "clip_compacter"])
-def test_features_and_grads_match_reference_golden(golden, name):
-    """Forward features AND adapter gradients of a full train_one step against outputs of the unmodified reference."""
+def test_features_match_reference_golden(golden, name):
+    """Forward features against the committed outputs of the UNMODIFIED reference modules (gradients: oracle cases below)."""
     c = golden[name]
     cfg = VitCfg(**c["cfg"])
     sd = synth.make_state_dict(cfg, seed=0, grad_test=True)

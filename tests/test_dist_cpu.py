@@ -57,3 +57,38 @@ def test_bucket_allreduce_two_ranks():
     for p in procs:
         p.join(timeout=60)
     assert all(ok for _, ok in res), res
+
+
+def _bn_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from peft_b200.dist import GlobalBatchNorm1d
+    x = torch.randn(8, 5, generator=torch.Generator().manual_seed(1))
+    wgt = torch.randn(8, 5, generator=torch.Generator().manual_seed(2))
+    xs = x[rank * 4:(rank + 1) * 4].clone().requires_grad_(True)
+    bn = GlobalBatchNorm1d(5)
+    y = bn(xs)
+    (y * wgt[rank * 4:(rank + 1) * 4]).sum().backward()
+    ref_bn = torch.nn.BatchNorm1d(5, affine=False)
+    xr = x.clone().requires_grad_(True)
+    yr = ref_bn(xr)
+    (yr * wgt).sum().backward()
+    ok = (torch.allclose(y, yr[rank * 4:(rank + 1) * 4], atol=1e-5) and torch.allclose(xs.grad, xr.grad[rank * 4:(rank + 1) * 4], atol=1e-5)
+          and torch.allclose(bn.running_mean, ref_bn.running_mean, atol=1e-6) and torch.allclose(bn.running_var, ref_bn.running_var, atol=1e-5))
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_global_batchnorm_two_ranks_equals_single_rank():
+    """with sync_bn the N-rank head equals the 1-rank head on the concatenated batch (values AND gradients)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_bn_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok in res), res
