@@ -29,6 +29,10 @@ import torch  # noqa: E402
 CONFIGS = {
     "C3": dict(model="ViT-B/16", dialect="timm", adapter="kron", patch=16, width=768, depth=12, heads=12, batch=256,
                gflop_img=71.45 + 0.17, desc="ViT-B/16 + KAdaptation (n=4, rank 1) on q/v"),
+    # SURVEY Q4 variant: the COMMITTED KAdaptation hyper-parameters (phm_dim = 768, rank 1): dense fold path, phm_rule frozen
+    "C3n768": dict(model="ViT-B/16", dialect="timm", adapter="kron", phm_dim=768, patch=16, width=768, depth=12, heads=12,
+                   batch=256, gflop_img=71.45 + 3 * 12 * 197 * 2 * 2 * 768 * 768 / 1e9,
+                   desc="ViT-B/16 + KAdaptation with the committed phm_dim=768 (dense fold variant)"),
     "C2": dict(model="ViT-B/16", dialect="timm", adapter="lora", patch=16, width=768, depth=12, heads=12, batch=256,
                gflop_img=71.45 + 0.17, desc="ViT-B/16 + LoRA (r=4, alpha=128) on q/v"),
     "B32": dict(model="ViT-B/32", dialect="timm", adapter="kron", patch=32, width=768, depth=12, heads=12, batch=256,
@@ -50,12 +54,12 @@ CONFIGS = {
 def vit_cfg(c, depth=None):
     from oracle.synth import VitCfg
     return VitCfg(dialect=c["dialect"], adapter=c["adapter"], img=224, patch=c["patch"], width=c["width"],
-                  depth=depth or c["depth"], heads=c["heads"], out_dim=c.get("out_dim", 512))
+                  depth=depth or c["depth"], heads=c["heads"], out_dim=c.get("out_dim", 512), phm_dim=c.get("phm_dim", 4))
 
 
 def adapter_kwargs(c):
     if c["adapter"] == "kron":
-        return dict(phm_dim=4, phm_rank=1)
+        return dict(phm_dim=c.get("phm_dim", 4), phm_rank=1)
     if c["adapter"] == "lora":
         return dict(lora_attn_dim=4, lora_attn_alpha=128)
     return dict(bottleneck=64)
@@ -168,7 +172,7 @@ def cpu_reference_rate(cfg_name, budget_s, steps=None, warmup=1):
     probe()
     t_img = (time.time() - t1) / 2
     n_steps = steps if steps is not None else 2
-    b = int(max(1, min(16, budget_s / max(1e-6, (n_steps + warmup) * t_img))))
+    b = int(max(1, min(32 if CONFIGS[cfg_name]["batch"] <= 32 else 16, budget_s / max(1e-6, (n_steps + warmup) * t_img))))
     step = build_oracle_step(cfg_name, b)
     for _ in range(warmup):
         step()
@@ -239,7 +243,7 @@ def main():
     Bpg = args.batch or c["batch"]
     cfg = vit_cfg(c, depth)
     sd = synth.make_state_dict(cfg, seed=0, grad_test=False)
-    names = set(synth.trainable_names(cfg, sd))
+    names = set(synth.trainable_names(cfg, sd, train_rule=c.get("phm_dim", 4) <= 64))   # few_shot freezes phm_rule ('W' filter)
     kw = adapter_kwargs(c)
     if c["dialect"] == "timm":
         from peft_b200.timm_vit import VisionTransformer

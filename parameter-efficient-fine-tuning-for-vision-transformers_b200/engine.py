@@ -40,6 +40,8 @@ class EngineCfg:
     rank: int = 0         # low-rank q/v adapter columns r' (0 = no q/v adapter)
     bottleneck: int = 0   # Houlsby / Compacter bottleneck width after the MLP (0 = none; 64 in the reference)
     bn_act: str = "relu"  # "relu" (Houlsby, FS/adapter_model.py:304-311) | "gelu_tanh" (Compacter gelu_new, FS/compacter_model.py:376)
+    dense_delta: bool = False  # q/v update given as dense H_q, H_v [D, D] (large-n KAdaptation "fold" variant):
+                               # rank == width, Dn is the identity (not trainable) and UpT = [H_q | 0 | H_v]
     train_all: bool = False  # full fine-tuning / intrinsic-dimension mode: backward also emits dL/dW for EVERY tower tensor
 
     @property
@@ -125,6 +127,10 @@ class _Workspace:
             self.dz = e(M, m)
             self.gh = e(M, D, dt=f32)                                # gradient w.r.t. h (fp32) and its bf16 copy
             self.ghb = e(M, D)
+        if cfg.rank > 128 and not cfg.train_all:
+            Mp = (M + 7) // 8 * 8
+            self.tA = torch.zeros(rp, Mp, device=dev, dtype=bf)           # p^T      [r', tokens]
+            self.tB = torch.zeros(3 * D, Mp, device=dev, dtype=bf)        # dqkv^T   [3D, tokens]
         if cfg.train_all:
             # everything a weight-gradient product needs that the PEFT path recomputes or never keeps
             self.xn2_l = [e(M, D) for _ in range(dep)]
@@ -194,6 +200,10 @@ class VitEngine:
                 self.vprojT = g("proj").T.to(bf).contiguous()         # [E, D]  == B operand [N=E, K=D] of the forward
             else:
                 self.vproj = None
+        if cfg.dense_delta:
+            if cfg.dialect != "timm" or cfg.rank != D:
+                raise NotImplementedError("the dense q/v update is built for the timm dialect with rank == width")
+            self.wqkvT[:, :, 3 * D:] = torch.eye(D, device=dev, dtype=bf)       # [W^T | I]: dxn = dqkv W + dp
         if rp > 0:
             self.dn_bf = torch.zeros(dep, rp, D, device=dev, dtype=bf)
             self.upT_bf = torch.zeros(dep, rp, 3 * D, device=dev, dtype=bf)
@@ -221,8 +231,11 @@ class VitEngine:
         if r == 0:
             return
         with torch.no_grad():
-            self.dn_bf[:, :r].copy_(Dn)
             self.upT_bf[:, :r].copy_(UpT)
+            if cfg.dense_delta:
+                self.wqkv[:, :, D:D + r].copy_(UpT.transpose(1, 2))
+                return
+            self.dn_bf[:, :r].copy_(Dn)
             self.wqkvT[:, :, 3 * D:3 * D + r].copy_(Dn.transpose(1, 2))
             if cfg.dialect == "clip":
                 self.up2T_bf[:, :r, :D].copy_(UpT[:, :, :D])
@@ -283,7 +296,10 @@ class VitEngine:
                 ops.gemm(xn1[:, D:], self.up2_bf[i], w.dlt)                        # [dq | dv] = p Up^T
                 ops.clip_delta(w.qkv[i], w.dlt, B, H, L, 1.0 / scale, 1.0)
             elif rp:
-                ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                    # p = LN1(x) Dn^T
+                if cfg.dense_delta:
+                    xn1[:, D:].copy_(xn1[:, :D])                                   # Dn = I: p is LN1(x) itself
+                else:
+                    ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                # p = LN1(x) Dn^T
                 ops.gemm(xn1, self.wqkv[i], w.qkv[i], bias=self.bqkv[i])           # [x|p] [W|Up]^T + b
             else:
                 ops.gemm(xn1[:, :D], self.wqkv[i][:, :D], w.qkv[i], bias=self.bqkv[i])
@@ -383,6 +399,14 @@ class VitEngine:
                     ops.tn_reduce(pc, w.dlt[:, :D], dUpT[i, c:c + cw, :D])
                     ops.tn_reduce(pc, w.dlt[:, D:], dUpT[i, c:c + cw, 2 * D:])
                     ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
+            elif rp > 128:
+                dq = w.dqkv[:, :3 * D]
+                ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
+                self._dw(w, w.xn1[i][:, D:], dq, dUpT[i])                           # dUp^T = p^T dqkv as ONE tensor-core product
+                if not cfg.dense_delta:
+                    for c in range(0, rp, 64):
+                        cw = min(64, rp - c)
+                        ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
             elif rp:
                 dq = w.dqkv[:, :3 * D]
                 ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
@@ -401,7 +425,7 @@ class VitEngine:
         if m:
             bng = (dWd, dbd16[:, 0], dWuT.transpose(1, 2), dbu16[:, 0], dlg, dlb)
         if r:
-            return dDn[:, :r], dUpT[:, :r], bng
+            return (None if cfg.dense_delta else dDn[:, :r]), dUpT[:, :r], bng
         return None, None, bng
 
 

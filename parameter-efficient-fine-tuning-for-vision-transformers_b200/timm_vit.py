@@ -194,6 +194,8 @@ def lowrank_factors_kron(rule, w_left, w_right):
 def lowrank_operands(attns, kind):
     """Dn [depth, r', D], UpT [depth, r', 3D] from the attention modules' reference-named adapter parameters
     (`phm_rule / W_left{1,2} / W_right{1,2}` or `{q,v}_proj_adapter{1,2}.weight`); shared by both dialects."""
+    if kind == "kron" and kron_is_dense(attns[0]):
+        return dense_kron_operands(attns)
     if kind == "kron":
         rule = torch.stack([a.phm_rule for a in attns])
         dq, uq = lowrank_factors_kron(rule, torch.stack([a.W_left1 for a in attns]), torch.stack([a.W_right1 for a in attns]))
@@ -212,9 +214,36 @@ def lowrank_operands(attns, kind):
     return Dn, UpT
 
 
+DENSE_DELTA_MIN_RANK = 512     # reshape-trick rank 2 n r n above which the dense ("fold") form of the update is used
+
+
+def kron_is_dense(attn):
+    n = attn.phm_rule.shape[0]
+    return 2 * n * attn.phm_rank * n > DENSE_DELTA_MIN_RANK
+
+
+def dense_kron_operands(attns):
+    """Large-n KAdaptation (the committed phm_dim = 768): H = sum_i A_i (x) (u_i v_i^T) is formed as a dense
+    [D, D] matrix per projection by a differentiable contraction over i (it reads phm_rule once: n^3 floats, HBM-bound),
+    and handed to the engine as UpT = [H_q | 0 | H_v] with Dn = I.  dH comes back as ONE tensor-core product per layer and
+    autograd maps it to W_left / W_right (and to phm_rule if it requires grad; the reference freezes it)."""
+    outs = []
+    for a in attns:
+        n, K = a.W_left1.shape[0], a.W_left1.shape[1]
+        D = n * K
+        hs = []
+        for wl, wr in ((a.W_left1, a.W_right1), (a.W_left2, a.W_right2)):
+            B = torch.bmm(wl, wr)                                                   # [n, K, P]
+            hs.append(torch.einsum("iac,ikp->akcp", a.phm_rule, B).reshape(D, D))   # FS/kadaptation.py:104-115
+        outs.append(torch.cat([hs[0], torch.zeros_like(hs[0]), hs[1]], dim=1))      # [D, 3D]
+    return None, torch.stack(outs)
+
+
 def lowrank_rank(attn, kind):
     if kind == "kron":
         n = attn.phm_rule.shape[0]
+        if kron_is_dense(attn):
+            return attn.W_left1.shape[0] * attn.W_left1.shape[1]                    # dense update: rank == width
         return 2 * n * attn.phm_rank * n
     if kind == "lora":
         return 2 * attn.lora_attn_dim
@@ -407,6 +436,8 @@ class VisionTransformer(nn.Module):
 
     def forward_features(self, x):
         extra = dict(rank=self._rank(), **self._bottleneck_cfg())
+        if self.adapter_kind == "kron" and kron_is_dense(self.blocks[0].attn):
+            extra["dense_delta"] = True
         return run_tower(self, x, "timm", self._cfg, extra, self.lowrank_operands, self.bottleneck_operands)
 
     def forward(self, x):

@@ -79,6 +79,9 @@ BACKBONE_CASES = {
     "houlsby_L197": (VitCfg(dialect="timm", adapter="houlsby", img=224, patch=16, depth=2), 2),
     "kron_n4_L197": (VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=224, patch=16, depth=3), 3),
     "lora_L197": (VitCfg(dialect="timm", adapter="lora", img=224, patch=16, depth=2), 2),
+    # large-n KAdaptation (the committed phm_dim is 768): dense "fold" form of the update, dH as one GEMM
+    "kron_n64_dense": (VitCfg(dialect="timm", adapter="kron", phm_dim=64, img=64, patch=32, depth=2), 6),
+    "kron_n192_dense_L50": (VitCfg(dialect="timm", adapter="kron", phm_dim=192, img=224, patch=32, depth=2), 3),
     "kron_n4_L50_d12": (VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=224, patch=32, depth=12), 4),
 }
 
