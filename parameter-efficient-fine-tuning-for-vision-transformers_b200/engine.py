@@ -441,7 +441,7 @@ class VitEngine:
         ops.transpose(X, b[:, :M])
         ops.gemm(a[:, :Mp], b[:, :Mp], out, epilogue=ops.EPI_STORE_F32)
 
-    def backward_full(self, dfeat):
+    def backward_full(self, dfeat, need=None):
         """dL/d(every tower tensor) -> {reference key: fp32 grad}.  Only for cfg.train_all (no adapters): the Fastfood /
         full-fine-tuning configuration C5, where theta is a function of V and autograd needs every dW
         (FL/intrinsic/fastfood.py:61-77).  Same kernels as the PEFT backward plus, per linear layer, one weight-gradient
@@ -460,6 +460,7 @@ class VitEngine:
         dfeat = dfeat.contiguous().float()
         keys = _TIMM_KEYS if cfg.dialect == "timm" else _CLIP_KEYS
         G = {}
+        want = (lambda name: True) if need is None else (lambda name: name in need)   # bias-only / LN-only tuning skip the dW products
         w.g.zero_()
         w.gb.zero_()
         xcls = w.x0[dep].view(B, L * D)[:, :D]
@@ -470,9 +471,10 @@ class VitEngine:
             ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dlnf_w, dlnf_b)
         else:
             dfb = dfeat.to(torch.bfloat16)
-            dproj = e(D, cfg.out_dim)
-            self._dw(w, w.yf, dfb, dproj)                                          # proj [D, E] = yf^T dfeat
-            G["proj"] = dproj
+            if want("proj"):
+                dproj = e(D, cfg.out_dim)
+                self._dw(w, w.yf, dfb, dproj)                                      # proj [D, E] = yf^T dfeat
+                G["proj"] = dproj
             ops.gemm(dfb, self.vproj, w.dyf)
             ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dlnf_w, dlnf_b)
         if cfg.dialect == "timm":
@@ -484,30 +486,46 @@ class VitEngine:
         for i in reversed(range(dep)):
             k = lambda n: keys[n].format(i=i)
             # MLP
-            c16 = z(16, D); self_dw = e(D, F)
-            ops.tn_reduce(w.ones, w.gb, c16)
-            self._dw(w, w.gb, w.act_l[i], self_dw)
-            G[k("fc2_b")], G[k("fc2_w")] = c16[0], self_dw
+            if want(k("fc2_b")):
+                c16 = z(16, D)
+                ops.tn_reduce(w.ones, w.gb, c16)
+                G[k("fc2_b")] = c16[0]
+            if want(k("fc2_w")):
+                dw2 = e(D, F)
+                self._dw(w, w.gb, w.act_l[i], dw2)
+                G[k("fc2_w")] = dw2
             ops.gemm(w.gb, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
-            c16 = z(16, F); dw1 = e(F, D)
-            ops.tn_reduce(w.ones, w.dh, c16)
-            self._dw(w, w.dh, w.xn2_l[i], dw1)
-            G[k("fc1_b")], G[k("fc1_w")] = c16[0], dw1
+            if want(k("fc1_b")):
+                c16 = z(16, F)
+                ops.tn_reduce(w.ones, w.dh, c16)
+                G[k("fc1_b")] = c16[0]
+            if want(k("fc1_w")):
+                dw1 = e(F, D)
+                self._dw(w, w.dh, w.xn2_l[i], dw1)
+                G[k("fc1_w")] = dw1
             ops.gemm(w.dh, self.wfc1T[i], w.dxn)
             dg, db = z(D), z(D)
             ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb, dg, db)
             G[k("ln2_w")], G[k("ln2_b")] = dg, db
             # attention
-            c16 = z(16, D); dwp = e(D, D)
-            ops.tn_reduce(w.ones, w.gb, c16)
-            self._dw(w, w.gb, w.o[i], dwp)
-            G[k("proj_b")], G[k("proj_w")] = c16[0], dwp
+            if want(k("proj_b")):
+                c16 = z(16, D)
+                ops.tn_reduce(w.ones, w.gb, c16)
+                G[k("proj_b")] = c16[0]
+            if want(k("proj_w")):
+                dwp = e(D, D)
+                self._dw(w, w.gb, w.o[i], dwp)
+                G[k("proj_w")] = dwp
             ops.gemm(w.gb, self.wprojT[i], w.d_o)
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
-            c16 = z(16, 3 * D); dwq = e(3 * D, D)
-            ops.tn_reduce(w.ones, dq, c16)
-            self._dw(w, dq, w.xn1[i][:, :D], dwq)
-            G[k("qkv_b")], G[k("qkv_w")] = c16[0], dwq
+            if want(k("qkv_b")):
+                c16 = z(16, 3 * D)
+                ops.tn_reduce(w.ones, dq, c16)
+                G[k("qkv_b")] = c16[0]
+            if want(k("qkv_w")):
+                dwq = e(3 * D, D)
+                self._dw(w, dq, w.xn1[i][:, :D], dwq)
+                G[k("qkv_w")] = dwq
             ops.gemm(dq, self.wqkvT[i][:, :3 * D], w.dxn)
             dg, db = z(D), z(D)
             ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb, dg, db)
@@ -525,7 +543,10 @@ class VitEngine:
         dpe = w.gb.view(B, L, D)[:, 1:, :].reshape(B * P, D)
         kk = 3 * cfg.patch * cfg.patch
         dconv = e(D, kk)
-        self._dw(w, dpe, w.patches[:, :kk], dconv)
+        if want("patch_embed.proj.weight" if cfg.dialect == "timm" else "conv1.weight"):
+            self._dw(w, dpe, w.patches[:, :kk], dconv)
+        else:
+            dconv.zero_()
         if cfg.dialect == "timm":
             c16 = z(16, D)
             ops.tn_reduce(w.ones[:B * P], dpe, c16)
@@ -547,13 +568,14 @@ class _BackboneFullFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, engine, images, names, *tensors):
         ctx.engine, ctx.names = engine, names
+        ctx.need = {n for n, t in zip(names, tensors) if t.requires_grad}
         engine.load_frozen({n: t.detach() for n, t in zip(names, tensors)})
         return engine.forward(images)
 
     @staticmethod
     def backward(ctx, dfeat):
-        G = ctx.engine.backward_full(dfeat)
-        return (None, None, None) + tuple(G.get(n) for n in ctx.names)
+        G = ctx.engine.backward_full(dfeat, ctx.need)
+        return (None, None, None) + tuple(G.get(n) if n in ctx.need else None for n in ctx.names)
 
 
 def backbone_full(engine: VitEngine, images, named_tensors):

@@ -73,8 +73,12 @@ def test_bias_only_tuning_uses_full_engine():
         p.requires_grad_(n.endswith(".bias"))
     images, _ = synth.make_batch(cfg, 4)
     model(images.cuda()).sum().backward()
+    sd_o = {k: v.clone().requires_grad_(k.endswith(".bias")) for k, v in sd.items()}
+    O.visual_forward(images, sd_o, cfg).sum().backward()
     for n, p in model.named_parameters():
         assert (p.grad is not None) == n.endswith(".bias"), n
+        if p.grad is not None:
+            assert rel(p.grad, sd_o[n].grad) < 2 * TOL, (n, rel(p.grad, sd_o[n].grad))
 
 
 def test_fastfood_wrap_vit_end_to_end():
