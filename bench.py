@@ -26,6 +26,10 @@ if ROOT not in sys.path:
 import torch  # noqa: E402
 
 # FLOP per image, fwd + bwd with a frozen backbone (dX only, no dW): SURVEY.md §8d / BASELINE.md §3
+# mean DRAM bytes (read + write) per GEMM launch of one C3 layer (8 products: qkv, proj, fc1, fc2 and their dX) from the
+# `ncu --set full` capture profiles/r01_ncu_top_kernels_v2_summary.txt (263 / 350 / 643 / 628 / 666 / 378 / 115 / 300 MB)
+NCU_GEMM_TRAFFIC_BYTES = {"C3": 417.9e6, "C2": 417.9e6}
+
 CONFIGS = {
     "C3": dict(model="ViT-B/16", dialect="timm", adapter="kron", patch=16, width=768, depth=12, heads=12, batch=256,
                gflop_img=71.45 + 0.17, desc="ViT-B/16 + KAdaptation (n=4, rank 1) on q/v"),
@@ -418,7 +422,9 @@ def main():
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel (all dense products of the step)",
                          "achieved": gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None, "peak": pk["tflops"],
                          "unit": "TFLOP/s", "frac": (gemm_flops / (gemm_ms * 1e-3) / 1e12) / pk["tflops"] if gemm_ms > 0 else None,
-                         "traffic": None, "peak_source": pk["src"] + " bf16_tflops_sustained",
+                         "traffic": NCU_GEMM_TRAFFIC_BYTES.get(args.config) if depth == c["depth"] and Bpg == c["batch"] else None,
+                         "traffic_unit": "bytes per launch (mean over the 8 products of a layer, ncu dram read+write)",
+                         "peak_source": pk["src"] + " bf16_tflops_sustained",
                          "gemm_share_of_step": gemm_ms / eager_ms if eager_ms > 0 else None, "gemm_launches": len(gemm_events),
                          "measured_in": "eager instrumented pass of the same K steps (CUDA events per launch)"},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
