@@ -125,6 +125,13 @@ int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int 
  * a function of V, so autograd needs dL/dW for all of them). */
 int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream);
 
+/* Large-n KAdaptation fold (the committed phm_dim = n = D, K = P = 1).
+ * replaces: kronecker_product_einsum_batched(phm_rule, W).sum(0) of matvec_product (FS/kadaptation.py:81-115) for BOTH
+ * projections in one pass over phm_rule (n^3 fp32, read once; HBM-bound):
+ *   backward == 0:  out[p, j] = sum_i s[p, i] * rule[i, j]      s [2, n] (q, v),  out = H [2, n*n]
+ *   backward == 1:  out[p, i] = sum_j dH[p, j] * rule[i, j]     dH [2, n*n],      out = ds [2, n]      (rule is frozen) */
+int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, int backward, void* stream);
+
 /* Fastfood intrinsic-dimension projection over a SET of wrapped parameter tensors in one call.
  * replaces: FastfoodWrap.forward / fastfood_torched / fast_walsh_hadamard_torched and their autograd backward —
  * FL/intrinsic/fastfood.py:61-77,81-121,151-187.

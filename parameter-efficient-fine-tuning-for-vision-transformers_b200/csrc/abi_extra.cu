@@ -53,6 +53,22 @@ extern "C" int peft_transpose_bf16(const void* in, long long ldin, int rows, int
   return 0;
 }
 
+extern "C" int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, int backward, void* stream) {
+  PEFT_REQUIRE(n > 0 && n <= kFoldMaxN && ((long long)n * n) % 4 == 0, "peft_phm_fold: need n <= %d and n*n %% 4 == 0 (n=%d)", kFoldMaxN, n);
+  PEFT_REQUIRE(rule && s_or_dH && out && al16(rule) && al16(s_or_dH) && al16(out), "peft_phm_fold: null or unaligned pointer");
+  const long long nn = (long long)n * n;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!backward) {
+    const long long threads = nn / 4;
+    phm_fold_fwd_kernel<<<(unsigned)((threads + kFoldThreads - 1) / kFoldThreads), kFoldThreads, 0, st>>>(rule, s_or_dH, out, n, nn);
+  } else {
+    PEFT_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)2 * n * sizeof(float), st));
+    phm_fold_bwd_kernel<<<dim3((n + kFoldRows - 1) / kFoldRows, kFoldSplit), kFoldThreads, 0, st>>>(rule, s_or_dH, out, n, nn);
+  }
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items,
                                  int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign,
                                  const float* theta0, float* theta, float* wu, float* scratch, int* counters, void* stream) {

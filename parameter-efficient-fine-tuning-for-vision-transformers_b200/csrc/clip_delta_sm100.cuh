@@ -118,3 +118,82 @@ __global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16
 }
 
 }  // namespace peft
+
+// ---- large-n KAdaptation "fold" (the committed phm_dim = n = D, K = P = 1) --------------------------
+// H_p[j] = sum_i s_p[i] * A[i, j]   for p in {q, v}, j in [0, n*n):  the weighted sum of the n rule matrices, i.e.
+// kronecker_product_einsum_batched(phm_rule, W).sum(0) of FS/kadaptation.py:81-115 when every W_i is a 1x1 block.
+// HBM-bound: A (= phm_rule, n^3 fp32 = 1.81 GB at n = 768) is read exactly once for BOTH projections.
+namespace peft {
+constexpr int kFoldThreads = 256;
+constexpr int kFoldMaxN = 1024;
+
+__global__ void __launch_bounds__(kFoldThreads) phm_fold_fwd_kernel(const float* __restrict__ A, const float* __restrict__ s,
+                                                                    float* __restrict__ H, int n, long long nn) {
+  __shared__ float sq[kFoldMaxN], sv[kFoldMaxN];
+  for (int i = threadIdx.x; i < n; i += kFoldThreads) { sq[i] = s[i]; sv[i] = s[n + i]; }
+  __syncthreads();
+  const long long j = ((long long)blockIdx.x * kFoldThreads + threadIdx.x) * 4;
+  if (j >= nn) return;
+  const float4* a = reinterpret_cast<const float4*>(A + j);
+  const long long stride = nn / 4;
+  float4 hq = make_float4(0.f, 0.f, 0.f, 0.f), hv = hq;
+#pragma unroll 8
+  for (int i = 0; i < n; ++i) {
+    const float4 v = __ldcs(a + (long long)i * stride);         // streamed once: do not keep in L2
+    const float wq = sq[i], wv = sv[i];
+    hq.x = fmaf(wq, v.x, hq.x); hq.y = fmaf(wq, v.y, hq.y); hq.z = fmaf(wq, v.z, hq.z); hq.w = fmaf(wq, v.w, hq.w);
+    hv.x = fmaf(wv, v.x, hv.x); hv.y = fmaf(wv, v.y, hv.y); hv.z = fmaf(wv, v.z, hv.z); hv.w = fmaf(wv, v.w, hv.w);
+  }
+  *reinterpret_cast<float4*>(H + j) = hq;
+  *reinterpret_cast<float4*>(H + nn + j) = hv;
+}
+
+// ds_p[i] += sum_j dH_p[j] * A[i, j].  A CTA takes kFoldRows rule matrices and one of kFoldSplit slices of j, so every dH
+// vector it pulls from L2 is used kFoldRows times (dH is 2 x n^2 fp32 = 4.7 MB: L2-resident) while A is streamed exactly
+// once from HBM; partial sums go to ds with one atomic per (row, projection) per CTA (ds is zeroed by the host wrapper).
+constexpr int kFoldRows = 4;
+constexpr int kFoldSplit = 4;
+__global__ void __launch_bounds__(kFoldThreads) phm_fold_bwd_kernel(const float* __restrict__ A, const float* __restrict__ dH,
+                                                                    float* __restrict__ ds, int n, long long nn) {
+  const int i0 = blockIdx.x * kFoldRows;
+  const long long n4 = nn / 4;
+  const long long per = (n4 + kFoldSplit - 1) / kFoldSplit;
+  const long long k0 = blockIdx.y * per, k1 = (k0 + per < n4) ? k0 + per : n4;
+  const float4* gq = reinterpret_cast<const float4*>(dH);
+  const float4* gv = reinterpret_cast<const float4*>(dH + nn);
+  const float4* a[kFoldRows];
+#pragma unroll
+  for (int r = 0; r < kFoldRows; ++r) a[r] = reinterpret_cast<const float4*>(A + (long long)((i0 + r) < n ? (i0 + r) : (n - 1)) * nn);
+  float aq[kFoldRows], av[kFoldRows];
+#pragma unroll
+  for (int r = 0; r < kFoldRows; ++r) { aq[r] = 0.f; av[r] = 0.f; }
+#pragma unroll 2
+  for (long long k = k0 + threadIdx.x; k < k1; k += kFoldThreads) {
+    const float4 q = __ldg(gq + k), w = __ldg(gv + k);
+#pragma unroll
+    for (int r = 0; r < kFoldRows; ++r) {
+      const float4 v = __ldcs(a[r] + k);
+      aq[r] = fmaf(v.x, q.x, fmaf(v.y, q.y, fmaf(v.z, q.z, fmaf(v.w, q.w, aq[r]))));
+      av[r] = fmaf(v.x, w.x, fmaf(v.y, w.y, fmaf(v.z, w.z, fmaf(v.w, w.w, av[r]))));
+    }
+  }
+  __shared__ float red[2 * kFoldRows][kFoldThreads / 32];
+#pragma unroll
+  for (int r = 0; r < kFoldRows; ++r) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      aq[r] += __shfl_xor_sync(0xffffffffu, aq[r], o);
+      av[r] += __shfl_xor_sync(0xffffffffu, av[r], o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[2 * r][threadIdx.x >> 5] = aq[r]; red[2 * r + 1][threadIdx.x >> 5] = av[r]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * kFoldRows) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < kFoldThreads / 32; ++k) t += red[threadIdx.x][k];
+    const int r = threadIdx.x >> 1, p = threadIdx.x & 1;
+    if (i0 + r < n) atomicAdd(&ds[p * n + i0 + r], t);
+  }
+}
+}  // namespace peft

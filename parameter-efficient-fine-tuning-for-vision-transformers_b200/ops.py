@@ -178,3 +178,14 @@ def transpose(x, out):
         raise ValueError("transpose: out must be [cols, rows]")
     _lib.check(_lib.load().peft_transpose_bf16(px, ldx, R, Cc, po, ldo, _stream()), "peft_transpose_bf16")
     return out
+
+
+def phm_fold(rule, x, out, backward=False):
+    """forward: out[2, n*n] = x[2, n] @ rule.view(n, n*n); backward: out[2, n] = x[2, n*n] @ rule.view(n, n*n)^T."""
+    n = rule.shape[0]
+    for t in (rule, x, out):
+        if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+            raise RuntimeError("phm_fold: contiguous CUDA fp32 tensors required (no CPU fallback)")
+    _lib.check(_lib.load().peft_phm_fold(rule.data_ptr(), x.data_ptr(), out.data_ptr(), n, int(backward), _stream()),
+               "peft_phm_fold")
+    return out

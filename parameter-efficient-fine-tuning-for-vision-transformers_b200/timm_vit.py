@@ -222,6 +222,29 @@ def kron_is_dense(attn):
     return 2 * n * attn.phm_rank * n > DENSE_DELTA_MIN_RANK
 
 
+class _PhmFoldFn(torch.autograd.Function):
+    """(phm_rule [n,n,n] frozen, s [2,n]) -> H [2, n, n] through peft_phm_fold (K = P = 1 case of the dense update)."""
+
+    @staticmethod
+    def forward(ctx, rule, s):
+        from . import ops
+        if rule.requires_grad:
+            raise NotImplementedError("phm_rule is frozen in the large-n fold path (the reference's 'W' filter freezes it too)")
+        n = rule.shape[0]
+        H = torch.empty(2, n, n, device=rule.device, dtype=torch.float32)
+        ops.phm_fold(rule.detach().contiguous(), s.detach().float().contiguous(), H)
+        ctx.rule = rule
+        return H
+
+    @staticmethod
+    def backward(ctx, dH):
+        from . import ops
+        n = ctx.rule.shape[0]
+        ds = torch.empty(2, n, device=dH.device, dtype=torch.float32)
+        ops.phm_fold(ctx.rule.detach().contiguous(), dH.float().contiguous(), ds, backward=True)
+        return None, ds
+
+
 def dense_kron_operands(attns):
     """Large-n KAdaptation (the committed phm_dim = 768): H = sum_i A_i (x) (u_i v_i^T) is formed as a dense
     [D, D] matrix per projection by a differentiable contraction over i (it reads phm_rule once: n^3 floats, HBM-bound),
@@ -231,10 +254,16 @@ def dense_kron_operands(attns):
     for a in attns:
         n, K = a.W_left1.shape[0], a.W_left1.shape[1]
         D = n * K
-        hs = []
-        for wl, wr in ((a.W_left1, a.W_right1), (a.W_left2, a.W_right2)):
-            B = torch.bmm(wl, wr)                                                   # [n, K, P]
-            hs.append(torch.einsum("iac,ikp->akcp", a.phm_rule, B).reshape(D, D))   # FS/kadaptation.py:104-115
+        if K == 1 and a.phm_rule.is_cuda and not a.phm_rule.requires_grad:
+            # the committed hyper-parameters (n = D): one streaming pass over phm_rule for q and v together
+            s = torch.stack([torch.bmm(a.W_left1, a.W_right1).reshape(n), torch.bmm(a.W_left2, a.W_right2).reshape(n)])
+            H = _PhmFoldFn.apply(a.phm_rule, s)
+            hs = [H[0], H[1]]
+        else:
+            hs = []
+            for wl, wr in ((a.W_left1, a.W_right1), (a.W_left2, a.W_right2)):
+                B = torch.bmm(wl, wr)                                                   # [n, K, P]
+                hs.append(torch.einsum("iac,ikp->akcp", a.phm_rule, B).reshape(D, D))   # FS/kadaptation.py:104-115
         outs.append(torch.cat([hs[0], torch.zeros_like(hs[0]), hs[1]], dim=1))      # [D, 3D]
     return None, torch.stack(outs)
 

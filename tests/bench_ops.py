@@ -93,6 +93,20 @@ def bench_gemm(M=50432, iters=20):
         print(f"gemm {name:24s} M={M} N={N} K={K}: {t:7.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
 
 
+def bench_phm_fold(n=768, peak_gbs=6552.0):
+    """Large-n KAdaptation fold: one streaming pass over phm_rule (n^3 fp32 = 1.81 GB at n = 768) per direction."""
+    rule = torch.randn(n, n, n, device="cuda")
+    s = torch.randn(2, n, device="cuda")
+    H = torch.empty(2, n, n, device="cuda")
+    dH = torch.randn(2, n, n, device="cuda")
+    ds = torch.empty(2, n, device="cuda")
+    byt = 4.0 * n ** 3
+    tf = timeit(lambda: ops.phm_fold(rule, s, H), iters=10, warm=2)
+    tb = timeit(lambda: ops.phm_fold(rule, dH, ds, backward=True), iters=10, warm=2)
+    print(f"phm_fold n={n}: fwd {tf:7.1f} us {byt / tf / 1e3:7.1f} GB/s ({byt / tf / 1e3 / peak_gbs:.2f} of copy peak)  "
+          f"bwd {tb:7.1f} us {byt / tb / 1e3:7.1f} GB/s ({byt / tb / 1e3 / peak_gbs:.2f})", flush=True)
+
+
 def vit_b32_shapes(D=768):
     shapes = [(D, 3, 32, 32), (D,), (50, D), (D,), (D,)]
     for _ in range(12):
@@ -150,6 +164,8 @@ if __name__ == "__main__":
         bench_ln()
         bench_reduce()
         torch.cuda.synchronize()
+    if what in ("fold", "all"):
+        bench_phm_fold()
     if what in ("fastfood", "all"):
         bench_fastfood()
     if what == "prof_fastfood":

@@ -82,6 +82,8 @@ BACKBONE_CASES = {
     # large-n KAdaptation (the committed phm_dim is 768): dense "fold" form of the update, dH as one GEMM
     "kron_n64_dense": (VitCfg(dialect="timm", adapter="kron", phm_dim=64, img=64, patch=32, depth=2), 6),
     "kron_n192_dense_L50": (VitCfg(dialect="timm", adapter="kron", phm_dim=192, img=224, patch=32, depth=2), 3),
+    # the COMMITTED hyper-parameters (phm_dim = 768 = D, K = P = 1): peft_phm_fold path, phm_rule frozen as in few_shot
+    "kron_n768_committed": (VitCfg(dialect="timm", adapter="kron", phm_dim=768, img=64, patch=32, depth=1), 2),
     "kron_n4_L50_d12": (VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=224, patch=32, depth=12), 4),
 }
 
@@ -92,7 +94,11 @@ def test_backbone_grads_match_oracle(name):
     the conditioning of the BatchNorm head."""
     cfg, B = BACKBONE_CASES[name]
     sd = synth.make_state_dict(cfg, seed=0, grad_test=True)
-    names = synth.trainable_names(cfg, sd)
+    names = synth.trainable_names(cfg, sd, train_rule=cfg.phm_dim <= 256)
+    if cfg.phm_dim == 768:
+        for k in sd:                      # n = 768 sums 768 terms per entry: keep |H| in the range of the small-n cases
+            if "W_left" in k or "W_right" in k:
+                sd[k] = sd[k] * 3.0
     model = build_timm(cfg, sd)
     for n, p in model.named_parameters():
         p.requires_grad_(n in names)

@@ -219,3 +219,21 @@ def test_patch_embed_pieces(ops):
     ops.assemble_tokens(pe, cls, pos, x, B, P + 1, D)
     ref_x = torch.cat([cls.expand(B, 1, D), pe.float().reshape(B, P, D)], 1) + pos
     assert rel(x, ref_x) < 1e-6
+
+
+@pytest.mark.parametrize("n", [8, 96, 258])
+def test_phm_fold(n):
+    """peft_phm_fold (large-n KAdaptation, K = P = 1) against the einsum of FS/kadaptation.py:104-115 in float64."""
+    from peft_b200 import ops
+    g = torch.Generator().manual_seed(n)
+    rule = torch.randn(n, n, n, generator=g)
+    s = torch.randn(2, n, generator=g)
+    H = torch.empty(2, n, n, device="cuda")
+    ops.phm_fold(rule.cuda(), s.cuda(), H)
+    ref = torch.einsum("pi,iac->pac", s.double(), rule.double())
+    assert float((H.cpu().double() - ref).norm() / ref.norm()) < 1e-5
+    dH = torch.randn(2, n, n, generator=g)
+    ds = torch.empty(2, n, device="cuda")
+    ops.phm_fold(rule.cuda(), dH.cuda(), ds, backward=True)
+    ref = torch.einsum("pac,iac->pi", dH.double(), rule.double())
+    assert float((ds.cpu().double() - ref).norm() / ref.norm()) < 1e-5
