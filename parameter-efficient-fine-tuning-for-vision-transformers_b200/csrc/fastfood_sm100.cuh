@@ -119,9 +119,11 @@ __device__ __forceinline__ int ff_hi_ioff(int i, int lc) {
   return lc >= 9 ? (((i >> (lc - 9)) << kFfTileBits) + ((i & ((1 << (lc - 9)) - 1)) << 9)) : (i << (22 - lc));
 }
 __device__ __forceinline__ void ff_signal(int* counter) {       // all of this CTA's global writes -> visible, then count
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) atomicAdd(counter, 1);
+  __syncthreads();                                               // bar.sync orders every thread's stores before thread 0's
+  if (threadIdx.x == 0) {                                        // fence (cumulativity): one membar per CTA instead of 512
+    __threadfence();
+    atomicAdd(counter, 1);
+  }
 }
 __device__ __forceinline__ void ff_wait(const int* counter, int target) {
   if (threadIdx.x == 0) {
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_kernel(FfArgs a) {
 // ---- backward --------------------------------------------------------------------------------------------------------
 // low block: x = pad(dtheta), butterflies over bits [0, min(ll,13)); single-pass tensors bin here, others write fp32
 // high tile: butterflies over bits [13, ll), times G, folded through Pi^T into wn bins (shared atomics, then global)
-__global__ void __launch_bounds__(kFfThreads, 2) ff_bwd_kernel(FfArgs a) {
+__global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
   extern __shared__ float ff_smem[];
   float* s = ff_smem;
   float* bins = ff_smem + kFfTile;
