@@ -56,7 +56,7 @@ CONFIGS = {
 
 
 def vit_cfg(c, depth=None):
-    from oracle.synth import VitCfg
+    from peft_b200.synth import VitCfg
     return VitCfg(dialect=c["dialect"], adapter=c["adapter"], img=224, patch=c["patch"], width=c["width"],
                   depth=depth or c["depth"], heads=c["heads"], out_dim=c.get("out_dim", 512), phm_dim=c.get("phm_dim", 4))
 
@@ -229,7 +229,7 @@ def main():
 
     import torch.distributed as dist
     import torch.nn.functional as F
-    from oracle import synth                      # synthetic-weight factory only (not the oracle math)
+    from peft_b200 import synth                   # synthetic weights / inputs (nothing from oracle/ on this arm)
     from peft_b200 import _lib, ops
     from peft_b200.classifier import Classifier
     from peft_b200.dist import GradBucket
