@@ -140,10 +140,13 @@ int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, in
  *   pi_lo [sum LL] uint16 = Pi[j] mod min(LL, wn);  gg [sum LL] fp32 = G;  bsign [T, wn] fp32 = B[:wn] (zero padded);
  *   theta0 / theta / dtheta fp32 indexed by off_dd;  scratch [sum LL] fp32;  wu [T, wn] fp32 scratch;  counters [T] int.
  * wn = power of two >= d, <= 4096.  `items` is a device array of (tensor, tile | kind << 30) int pairs built by the
- * caller and ordered tensor by tensor — kind 1 = "high" tile (tensors with ll > 13: tiles 0 .. LL/8192 - 1), kind 0 =
- * "low" block (blocks 0 .. ceil(DD/8192) - 1).  Forward lists a tensor's high tiles BEFORE its low blocks, backward
- * its low blocks BEFORE its high tiles (the second pass waits for the first through `counters`, which relies on CTAs
- * being dispatched in list order). */
+ * caller — kind 1 = "high" tile (tensors with ll > 13: tiles 0 .. LL/8192 - 1), kind 0 = "low" block (blocks
+ * 0 .. ceil(DD/8192) - 1).  Forward lists a tensor's high tiles BEFORE its low blocks, backward its low blocks BEFORE its
+ * high tiles; items of different tensors may interleave freely (the second pass waits for the first through `counters`;
+ * the kernels are persistent cooperative launches taking items round-robin, so an item only ever waits on lower-numbered
+ * ones).  off_ll and off_dd should be multiples of 64 elements: the DRAM streams are staged with 16-byte cp.async and the
+ * forward drops the intermediate's L2 lines by 128-byte line; other offsets fall back to direct loads.  theta0 / dtheta
+ * must be readable up to the next multiple of 4 elements past DD.  The forward leaves `scratch` undefined. */
 typedef struct {
   long long off_ll;  /* element offset of this tensor in pi_lo / gg / scratch */
   long long off_dd;  /* element offset in theta0 / theta / dtheta */

@@ -1,4 +1,5 @@
 // C-ABI: CLIP-dialect delta placement and the Fastfood projection.
+#include <stdlib.h>
 #include "common.cuh"
 #include "clip_delta_sm100.cuh"
 #include "fastfood_sm100.cuh"
@@ -7,15 +8,42 @@ using namespace peft;
 
 namespace {
 inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
-constexpr int kFfSmemBytes = (kFfTile + kFfMaxWn) * 4;
 
-int ff_configure() {
-  static bool done = false;
-  if (done) return 0;
-  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
-  PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
-  done = true;
+// persistent grid: occupancy x SMs CTAs, launched cooperatively so that every CTA is resident (the in-kernel waits rely on it)
+template <typename K>
+int ff_launch(K kernel, FfArgs a, cudaStream_t s) {
+  static int dev_smem = 0;
+  const int smem = ff_smem_bytes(a.wn);
+  if (dev_smem < smem) {   // raise the opt-in limit once
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ff_smem_bytes(kFfMaxWn)));
+    dev_smem = ff_smem_bytes(kFfMaxWn);
+  }
+  int occ = 0;
+  PEFT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kFfThreads, smem));
+  PEFT_REQUIRE(occ >= 1, "fastfood: kernel does not fit on an SM (smem %d B)", smem);
+  long long grid = (long long)occ * sm_count();
+  if (grid > a.n_items) grid = a.n_items;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kFfThreads);
+  cfg.dynamicSmemBytes = (size_t)smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  PEFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, a));
+  PEFT_LAUNCH_CHECK();
   return 0;
+}
+int ff_discard() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PEFT_FF_DISCARD");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v;
 }
 int ff_check(int d, int wn, int T, int n_items) {
   PEFT_REQUIRE(d > 0 && wn >= d && wn <= kFfMaxWn && (wn & (wn - 1)) == 0, "fastfood: need d <= wn <= %d, wn a power of two (d=%d wn=%d)", kFfMaxWn, d, wn);
@@ -75,18 +103,14 @@ extern "C" int peft_fastfood_fwd(const float* V, int d, int wn, const peft_ff_te
   int rc = ff_check(d, wn, T, n_items);
   if (rc) return rc;
   PEFT_REQUIRE(V && tensors && items && pi_lo && gg && bsign && theta0 && theta && wu && scratch && counters, "peft_fastfood_fwd: null operand");
-  rc = ff_configure();
-  if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   PEFT_CUDA_CHECK(cudaMemsetAsync(counters, 0, (size_t)T * sizeof(int), s));
   ff_small_kernel<0><<<T, 256, wn * 4, s>>>(tensors, bsign, V, wu, nullptr, d, wn);
   PEFT_LAUNCH_CHECK();
   FfArgs a{};
   a.tensors = tensors; a.items = reinterpret_cast<const int2*>(items); a.pi_lo = pi_lo; a.gg = gg; a.wv = wu; a.scratch = scratch;
-  a.theta0 = theta0; a.theta = theta; a.counters = counters; a.wn = wn;
-  ff_fwd_kernel<<<n_items, kFfThreads, (kFfTile + wn) * 4, s>>>(a);
-  PEFT_LAUNCH_CHECK();
-  return 0;
+  a.theta0 = theta0; a.theta = theta; a.counters = counters; a.wn = wn; a.T = T; a.n_items = n_items; a.discard = ff_discard();
+  return ff_launch(ff_fwd_kernel, a, s);
 }
 
 extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* tensors, int T, const int* items,
@@ -95,14 +119,17 @@ extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_
   int rc = ff_check(d, wn, T, n_items);
   if (rc) return rc;
   PEFT_REQUIRE(dtheta && tensors && items && pi_lo && gg && bsign && wu && scratch && counters && dV, "peft_fastfood_bwd: null operand");
-  rc = ff_configure();
-  if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   PEFT_CUDA_CHECK(cudaMemsetAsync(counters, 0, (size_t)T * sizeof(int), s));
   PEFT_CUDA_CHECK(cudaMemsetAsync(wu, 0, (size_t)T * wn * 4, s));
   FfArgs a{};
   a.tensors = tensors; a.items = reinterpret_cast<const int2*>(items); a.pi_lo = pi_lo; a.gg = gg; a.u = wu; a.scratch = scratch;
-  a.dtheta = dtheta; a.counters = counters; a.wn = wn;
+  a.dtheta = dtheta; a.counters = counters; a.wn = wn; a.T = T; a.n_items = n_items;
+  static bool bwd_attr = false;
+  if (!bwd_attr) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (kFfTile + kFfMaxWn) * 4));
+    bwd_attr = true;
+  }
   ff_bwd_kernel<<<n_items, kFfThreads, (kFfTile + wn) * 4, s>>>(a);
   PEFT_LAUNCH_CHECK();
   ff_small_kernel<1><<<T, 256, wn * 4, s>>>(tensors, bsign, nullptr, wu, dV, d, wn);

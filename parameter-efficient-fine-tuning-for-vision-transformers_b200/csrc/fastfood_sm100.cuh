@@ -16,13 +16,20 @@
 //   * both passes of one direction run in ONE launch: the work list is ordered tensor by tensor (forward: high tiles
 //     then low blocks; backward: low blocks then high tiles) and the second pass of a tensor waits on a per-tensor
 //     completion counter, so the fp32 intermediate of a tensor (<= 16 MB) is still in the 126 MB L2 when it is re-read
-//     (read with ld.global.cg).  CTAs are dispatched in blockIdx order, and producers never wait, so the spin is safe.
+//     (read with ld.global.cg).  The forward stores only the intermediate rows below DD and drops their L2 lines after the
+//     read (discard.global.L2), so the intermediate never costs a DRAM write-back.
+//   * the kernels are persistent (one cooperative launch of occupancy x SMs CTAs, items taken round-robin): while a CTA
+//     transforms item k, the Pi / G (or theta0 / dtheta) bytes of its item k + grid are already in flight into a shared-
+//     memory staging buffer (cp.async), so the DRAM latency of a tile is hidden behind the butterflies of the previous one.
+//     Producers never wait and every item only waits on lower-numbered items, so the spin cannot deadlock while all CTAs are
+//     co-resident (guaranteed by the cooperative launch).
 // HBM traffic per step is then the algorithmic minimum: 6 B per LL element (uint16 Pi mod wn + fp32 G) plus 8 B (fwd:
 // theta0 read, theta write) or 4 B (bwd: dtheta read) per DD element.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/peft_b200.h"
+#include "ptx_sm100.cuh"
 
 namespace peft {
 
@@ -30,6 +37,7 @@ constexpr int kFfThreads = 512;
 constexpr int kFfTile = 8192;      // elements per tile = 2^13
 constexpr int kFfTileBits = 13;
 constexpr int kFfMaxWn = 4096;
+constexpr int kFfDescCache = 384;  // tensor descriptors kept in shared memory (the rest is read from global)
 
 __device__ __forceinline__ int ff_swz(int idx) { return idx ^ (((idx >> 5) & 15) << 1); }
 
@@ -97,7 +105,7 @@ __device__ __forceinline__ void ff_tile_fwht(float (&x)[16], float* s, int lc, i
 
 struct FfArgs {
   const peft_ff_tensor* tensors;
-  const int2* items;            // (tensor, tile | kind << 30): kind 0 = low block, 1 = high tile; ordered tensor by tensor
+  const int2* items;            // (tensor, tile | kind << 30): kind 0 = low block, 1 = high tile; producers before consumers
   const uint16_t* pi_lo;        // Pi[j] mod min(LL, wn), concatenated over tensors (off_ll)
   const float* gg;              // G, same layout
   const float* wv;              // [T, wn]: forward w = H (B .* V); unused in backward
@@ -108,7 +116,15 @@ struct FfArgs {
   const float* dtheta;          // backward input
   int* counters;                // [T] completed first-pass CTAs per tensor (zeroed by the host wrapper)
   int wn;
+  int T;
+  int n_items;
+  int discard;                  // forward: drop the intermediate's L2 lines after the low pass has read them
 };
+
+// shared memory of one CTA: tile | w or bins | fp32 staging | uint16 staging | descriptor cache
+__host__ __device__ constexpr int ff_smem_bytes(int wn) {
+  return (kFfTile + wn + kFfTile) * 4 + kFfTile * 2 + kFfDescCache * (int)sizeof(peft_ff_tensor);
+}
 
 // offset of element e = i*512 + tid of a high-pass tile inside its tensor: ((e >> lc) << 13) + (e & (2^lc - 1)), split
 // into a per-thread constant and a term that only depends on (i, lc) and therefore lives on the uniform datapath
@@ -130,88 +146,202 @@ __device__ __forceinline__ void ff_wait(const int* counter, int target) {
     int v;
     do {
       asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-      if (v < target) __nanosleep(200);
+      if (v < target) __nanosleep(100);
     } while (v < target);
   }
   __syncthreads();
 }
+__device__ __forceinline__ peft_ff_tensor ff_desc(const FfArgs& a, const peft_ff_tensor* cache, int idx) {
+  return idx < kFfDescCache ? cache[idx] : a.tensors[idx];
+}
+__device__ __forceinline__ void ff_cp16(void* sdst, const void* g, int bytes) {   // bytes < 16: the rest is zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(ptx::smem_u32(sdst)), "l"(g), "r"(bytes) : "memory");
+}
+
+// ---- staging (cp.async) ----------------------------------------------------------------------------------------------
+// what the NEXT item of this CTA needs from DRAM and can be fetched ahead of its dependencies:
+//   mode 1: a high tile's Pi (uint16) and G (fp32), laid out by tile-local element e (needs 2^lc >= 8 columns per row
+//           segment and 16-byte aligned tensor starts, i.e. off_ll % 8 == 0);
+//   mode 2: a low block's theta0 (forward) / dtheta (backward), zero-filled at and beyond DD (off_dd % 4 == 0);
+//   mode 0: nothing staged (single-pass tensors and the odd layouts): the item loads directly.
+__device__ __forceinline__ int ff_stage_mode(int2 it, const peft_ff_tensor& t) {
+  if (it.y >> 30) return (2 * kFfTileBits - t.ll >= 3 && (t.off_ll & 7) == 0) ? 1 : 0;
+  return (t.ll > kFfTileBits && (t.off_dd & 3) == 0) ? 2 : 0;
+}
+__device__ __forceinline__ void ff_stage(const FfArgs& a, int2 it, const peft_ff_tensor& t, const float* vec, float* sg,
+                                         uint16_t* sp) {
+  const int tid = threadIdx.x, tile = it.y & 0x3fffffff;
+  const int mode = ff_stage_mode(it, t);
+  if (mode == 1) {
+    const int lc = 2 * kFfTileBits - t.ll;
+    const float* gg = a.gg + t.off_ll + (tile << lc);
+    const uint16_t* pi = a.pi_lo + t.off_ll + (tile << lc);
+#pragma unroll
+    for (int q = tid; q < kFfTile / 4; q += kFfThreads) {
+      const int e0 = q << 2;
+      ff_cp16(sg + e0, gg + ((e0 >> lc) << kFfTileBits) + (e0 & ((1 << lc) - 1)), 16);
+    }
+#pragma unroll
+    for (int q = tid; q < kFfTile / 8; q += kFfThreads) {
+      const int e0 = q << 3;
+      ff_cp16(sp + e0, pi + ((e0 >> lc) << kFfTileBits) + (e0 & ((1 << lc) - 1)), 16);
+    }
+  } else if (mode == 2) {
+    const float* src = vec + t.off_dd;
+#pragma unroll
+    for (int q = tid; q < kFfTile / 4; q += kFfThreads) {
+      const int j = (tile << kFfTileBits) + (q << 2);
+      const int rem = t.DD - j;
+      ff_cp16(sg + (q << 2), src + (rem > 0 ? j : 0), rem >= 4 ? 16 : (rem > 0 ? rem * 4 : 0));
+    }
+  }
+  ptx::cp_async_commit();
+}
 
 // ---- forward ---------------------------------------------------------------------------------------------------------
 // high tile: x[j] = w[Pi[j] mod wn] * G[j] generated on the fly, butterflies over bits [13, ll), fp32 intermediate out
+//            (only the rows the low pass will read: row < ceil(DD / 8192))
 // low block: butterflies over bits [0, min(ll, 13)), theta = theta0 + coef * x for j < DD
 __global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_kernel(FfArgs a) {
-  extern __shared__ float ff_smem[];
+  extern __shared__ __align__(16) float ff_smem[];
   float* s = ff_smem;
-  float* w = ff_smem + kFfTile;
-  const int2 it = a.items[blockIdx.x];
-  const peft_ff_tensor t = a.tensors[it.x];
+  float* w = s + kFfTile;
+  float* sg = w + a.wn;
+  uint16_t* sp = reinterpret_cast<uint16_t*>(sg + kFfTile);
+  peft_ff_tensor* cache = reinterpret_cast<peft_ff_tensor*>(sp + kFfTile);
   const int tid = threadIdx.x;
-  const int tile = it.y & 0x3fffffff;
-  const bool high = (it.y >> 30) != 0;
-  const uint16_t* pi = a.pi_lo + t.off_ll;
-  const float* gg = a.gg + t.off_ll;
-  float* scr = a.scratch + t.off_ll;
-  float x[16];
-  const float* wv = a.wv + (long long)it.x * a.wn;
-  if (high) {
-    // all global loads of the tile are issued before the first barrier so that their latencies overlap
-    const int lc = 2 * kFfTileBits - t.ll;               // log2(columns per tile)
-    const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
-    uint16_t pv[16];
+  int k = blockIdx.x;
+  if (k >= a.n_items) return;
+  {
+    const int nc = (a.T < kFfDescCache ? a.T : kFfDescCache) * (int)(sizeof(peft_ff_tensor) / 16);
+    for (int i = tid; i < nc; i += kFfThreads) reinterpret_cast<int4*>(cache)[i] = reinterpret_cast<const int4*>(a.tensors)[i];
+  }
+  __syncthreads();
+  int2 it = a.items[k];
+  ff_stage(a, it, ff_desc(a, cache, it.x), a.theta0, sg, sp);
+  int wcur = -1;                                           // tensor whose w row is in shared memory
+  for (;;) {
+    const int kn = k + gridDim.x;
+    const bool more = kn < a.n_items;
+    int2 itn = make_int2(0, 0);
+    if (more) itn = a.items[kn];                           // needed only after the staging buffers are free again
+    const peft_ff_tensor t = ff_desc(a, cache, it.x);
+    const int tile = it.y & 0x3fffffff;
+    const bool high = (it.y >> 30) != 0;
+    const int mode = ff_stage_mode(it, t);
+    const uint16_t* pi = a.pi_lo + t.off_ll;
+    const float* gg = a.gg + t.off_ll;
+    float* scr = a.scratch + t.off_ll;
+    const float* wv = a.wv + (long long)it.x * a.wn;
+    const int nblk = (t.DD + kFfTile - 1) >> kFfTileBits;
+    float x[16];
+    ptx::cp_async_wait<0>();
+    __syncthreads();                                       // (A) this item's staged bytes have landed
+    if (high) {
+      const int lc = 2 * kFfTileBits - t.ll;               // log2(columns per tile)
+      const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
+      uint16_t pv[16];
+      if (mode == 1) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int j = tc + ff_hi_ioff(i, lc);
-      pv[i] = pi[j];
-      x[i] = gg[j];
+        for (int i = 0; i < 16; ++i) {
+          pv[i] = sp[i * 512 + tid];
+          x[i] = sg[i * 512 + tid];
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int j = tc + ff_hi_ioff(i, lc);
+          pv[i] = pi[j];
+          x[i] = gg[j];
+        }
+      }
+      if (wcur != it.x) {
+        for (int q = tid; q < a.wn; q += kFfThreads) w[q] = wv[q];
+        wcur = it.x;
+      }
+      __syncthreads();                                     // (B) staging consumed, w visible
+      if (more) ff_stage(a, itn, ff_desc(a, cache, itn.x), a.theta0, sg, sp);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) x[i] *= w[pv[i]];
+      ff_tile_fwht(x, s, lc, kFfTileBits);
+      if (lc < 9) {                                        // the large tensors: element i sits i * 2^(22-lc) further on
+        const int S = 1 << (22 - lc), r0 = tc >> kFfTileBits, rs = S >> kFfTileBits;
+        float* p = scr + tc;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (r0 + i * rs < nblk) p[i * S] = x[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int j = tc + ff_hi_ioff(i, lc);
+          if ((j >> kFfTileBits) < nblk) scr[j] = x[i];
+        }
+      }
+      ff_signal(a.counters + it.x);
+    } else {
+      const int j0 = (tile << kFfTileBits) + tid;
+      const float* th0 = a.theta0 + t.off_dd;
+      float* th = a.theta + t.off_dd;
+      float t0v[16];
+      if (mode == 2) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) t0v[i] = sg[i * 512 + tid];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int j = j0 + i * 512;
+          t0v[i] = j < t.DD ? th0[j] : 0.f;
+        }
+      }
+      __syncthreads();                                     // (B)
+      if (more) ff_stage(a, itn, ff_desc(a, cache, itn.x), a.theta0, sg, sp);
+      if (t.ll <= kFfTileBits) {                           // single-pass tensor: generate the input here
+        const int LL = 1 << t.ll;
+        uint16_t pv[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int j = j0 + i * 512;
+          pv[i] = j < LL ? pi[j] : (uint16_t)0;
+          x[i] = j < LL ? gg[j] : 0.f;
+        }
+        if (wcur != it.x) {
+          for (int q = tid; q < a.wn; q += kFfThreads) w[q] = wv[q];
+          wcur = it.x;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] *= w[pv[i]];
+      } else {
+        ff_wait(a.counters + it.x, 1 << (t.ll - kFfTileBits));
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] = __ldcg(scr + j0 + i * 512);
+      }
+      ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int j = j0 + i * 512;
+        if (j < t.DD) th[j] = fmaf(t.coef, x[i], t0v[i]);
+      }
+      if (a.discard && t.ll > kFfTileBits && (tid & 31) == 0 && (t.off_ll & 31) == 0) {
+        // every load of this block has been consumed (the transform went through shared memory); each warp read whole
+        // 128-byte lines that nobody reads again before the next forward overwrites them
+#pragma unroll
+        for (int i = 0; i < 16; ++i) asm volatile("discard.global.L2 [%0], 128;" ::"l"(scr + j0 + i * 512) : "memory");
+      }
     }
-    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = wv[k];
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < 16; ++i) x[i] *= w[pv[i]];
-    ff_tile_fwht(x, s, lc, kFfTileBits);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) scr[tc + ff_hi_ioff(i, lc)] = x[i];
-    ff_signal(a.counters + it.x);
-    return;
-  }
-  const int j0 = (tile << kFfTileBits) + tid;
-  const float* th0 = a.theta0 + t.off_dd;
-  float* th = a.theta + t.off_dd;
-  float t0v[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {                         // theta0 is independent of everything else: fetch it first
-    const int j = j0 + i * 512;
-    t0v[i] = j < t.DD ? th0[j] : 0.f;
-  }
-  if (t.ll <= kFfTileBits) {                             // single-pass tensor: generate the input here
-    const int LL = 1 << t.ll;
-    uint16_t pv[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int j = j0 + i * 512;
-      pv[i] = j < LL ? pi[j] : (uint16_t)0;
-      x[i] = j < LL ? gg[j] : 0.f;
-    }
-    for (int k = tid; k < a.wn; k += kFfThreads) w[k] = wv[k];
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < 16; ++i) x[i] *= w[pv[i]];
-  } else {
-    ff_wait(a.counters + it.x, 1 << (t.ll - kFfTileBits));
-#pragma unroll
-    for (int i = 0; i < 16; ++i) x[i] = __ldcg(scr + j0 + i * 512);
-  }
-  ff_tile_fwht(x, s, 0, t.ll < kFfTileBits ? t.ll : kFfTileBits);
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int j = j0 + i * 512;
-    if (j < t.DD) th[j] = fmaf(t.coef, x[i], t0v[i]);
+    if (!more) break;
+    k = kn;
+    it = itn;
   }
 }
 
 // ---- backward --------------------------------------------------------------------------------------------------------
 // low block: x = pad(dtheta), butterflies over bits [0, min(ll,13)); single-pass tensors bin here, others write fp32
 // high tile: butterflies over bits [13, ll), times G, folded through Pi^T into wn bins (shared atomics, then global)
+// One CTA per item, 3 CTAs per SM.  A persistent cp.async-staged variant (like the forward) was measured SLOWER here
+// (910 vs 850 us on the ViT-B/32 set): the 16 shared-memory float atomics per thread compile to ATOMS.CAST.SPIN loops and
+// are the top stall (ncu: 29 % of samples), which a third resident CTA hides better than the staging does.  The spin on the
+// per-tensor counter relies on CTAs being dispatched in blockIdx order (producers first) and on producers never waiting.
 __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
   extern __shared__ float ff_smem[];
   float* s = ff_smem;
@@ -268,10 +398,17 @@ __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
     gv[i] = gg[j];
   }
   ff_wait(a.counters + it.x, nblk);
+  if (lc < 9) {
+    const int S = 1 << (22 - lc), r0 = tc >> kFfTileBits, rs = S >> kFfTileBits;
+    const float* p = scr + tc;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int j = tc + ff_hi_ioff(i, lc);
-    x[i] = (j >> kFfTileBits) < nblk ? __ldcg(scr + j) : 0.f;
+    for (int i = 0; i < 16; ++i) x[i] = r0 + i * rs < nblk ? __ldcg(p + i * S) : 0.f;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int j = tc + ff_hi_ioff(i, lc);
+      x[i] = (j >> kFfTileBits) < nblk ? __ldcg(scr + j) : 0.f;
+    }
   }
   ff_tile_fwht(x, s, lc, kFfTileBits);
   __syncthreads();

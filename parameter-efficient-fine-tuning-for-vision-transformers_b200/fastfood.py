@@ -17,10 +17,13 @@ import math
 import numpy as np
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import _lib
 
 _TILE = 8192
+_ALIGN = 64      # elements: every tensor starts on a 128-byte line in the uint16 table, 256 bytes in the fp32 ones
+_LAG = 640       # items between the two phases of a tensor (~2 grids of 296 CTAs)
 _FF_DTYPE = np.dtype([("off_ll", "<i8"), ("off_dd", "<i8"), ("DD", "<i4"), ("ll", "<i4"), ("coef", "<f4"), ("reserved", "<i4")])
 
 
@@ -34,6 +37,24 @@ def fastfood_vars(DD, device="cpu"):
     GG = torch.empty(LL, dtype=torch.float32).normal_()
     divisor = torch.sqrt(LL * torch.sum(torch.pow(GG, 2)))
     return [BB, Pi, GG, divisor, LL]
+
+
+def _schedule(phases, lag=_LAG):
+    """Work list of one direction.  The kernels are persistent (occupancy x SMs CTAs take items round-robin) and an item
+    only waits on lower-numbered ones, so any order with producers first is valid; the second phase of a tensor is issued
+    `lag` items (about two full grids) after its first phase, so that a CTA reaching it normally finds the counter already
+    complete instead of spinning through the tail of the first phase.  The intermediate of the tensors in flight
+    (lag x 32 KB + the tensor itself) stays far below the 126 MB L2."""
+    out, pending = [], []
+    for first, second in phases:
+        while pending and pending[0][0] <= len(out):
+            out += pending.pop(0)[1]
+        out += first
+        if second:
+            pending.append((len(out) + lag, second))
+    for _, second in pending:
+        out += second
+    return out
 
 
 class FastfoodPlan:
@@ -53,7 +74,8 @@ class FastfoodPlan:
         desc = np.zeros(T, dtype=_FF_DTYPE)
         off_ll = off_dd = 0
         self.offsets, self.numels, self.shapes = [], [], [tuple(s) for s in shapes]
-        fwd_items, bwd_items = [], []
+        fwd_ph, bwd_ph = [], []          # per tensor: (first-phase items, second-phase items that wait for them)
+        sum_ll = 0
         bsign = torch.zeros(T, self.wn, dtype=torch.float32)
         pi_parts, gg_parts = [], []
         for t, (shape, (BB, Pi, GG, divisor, LL)) in enumerate(zip(shapes, params)):
@@ -69,17 +91,20 @@ class FastfoodPlan:
             coef = 1.0 / (float(divisor) * math.sqrt(float(DD) / LL))
             desc[t] = (off_ll, off_dd, DD, ll, coef, 0)
             bsign[t, :n1] = BB[:n1]
-            pi_parts.append((Pi & (n1 - 1)).to(torch.int16))     # n1 <= 4096 fits; reinterpret as uint16 on device
-            gg_parts.append(GG.float())
+            pad = (-LL) % _ALIGN                                  # tensor starts stay 256-byte aligned (cp.async staging)
+            pi_parts.append(F.pad((Pi & (n1 - 1)).to(torch.int16), (0, pad)))   # n1 <= 4096 fits; uint16 on device
+            gg_parts.append(F.pad(GG.float(), (0, pad)))
             hi = [(t, k | (1 << 30)) for k in range(LL // _TILE)] if ll > 13 else []
             lo = [(t, k) for k in range((DD + _TILE - 1) // _TILE)]
-            fwd_items += hi + lo           # forward: high tiles, then the low blocks that wait for them
-            bwd_items += lo + hi           # backward: the other way round
+            fwd_ph.append((hi, lo) if hi else (lo, []))   # forward: high tiles, then the low blocks that wait for them
+            bwd_ph.append((lo, hi) if hi else (lo, []))   # backward: the other way round
             self.offsets.append(off_dd)
             self.numels.append(DD)
-            off_ll += LL
-            off_dd += (DD + 63) // 64 * 64
-        self.total_ll, self.total_dd = off_ll, off_dd
+            off_ll += LL + pad
+            sum_ll += LL
+            off_dd += (DD + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.total_ll, self.total_dd, self.sum_ll = off_ll, off_dd, sum_ll
+        fwd_items, bwd_items = _schedule(fwd_ph), _schedule(bwd_ph)
         dev = self.device
         self.desc = torch.from_numpy(desc.view(np.uint8).copy()).to(dev)
         self.pi_lo = torch.cat(pi_parts).to(dev)
@@ -97,7 +122,7 @@ class FastfoodPlan:
     # algorithmic HBM bytes of one forward / backward: 6 B per LL element + 8 / 4 B per DD element
     def algorithmic_bytes(self):
         dd = sum(self.numels)
-        return 6 * self.total_ll + 8 * dd, 6 * self.total_ll + 4 * dd
+        return 6 * self.sum_ll + 8 * dd, 6 * self.sum_ll + 4 * dd
 
     def set_theta0(self, tensors):
         for off, n, t in zip(self.offsets, self.numels, tensors):

@@ -134,7 +134,7 @@ def bench_fastfood(d=1000, iters=10, peak_gbs=6552.0):
     bf, bb = plan.algorithmic_bytes()
     tf = timeit(lambda: plan.project(V), iters=iters, warm=2)
     tb = timeit(lambda: plan.project_backward(plan.dtheta), iters=iters, warm=2)
-    print(f"fastfood ViT-B/32 T={plan.T} sumLL={plan.total_ll / 1e6:.1f}M sumDD={sum(plan.numels) / 1e6:.2f}M d={d}: "
+    print(f"fastfood ViT-B/32 T={plan.T} sumLL={plan.sum_ll / 1e6:.1f}M sumDD={sum(plan.numels) / 1e6:.2f}M d={d}: "
           f"fwd {tf:8.1f} us  {bf / tf / 1e3:7.1f} GB/s algorithmic ({bf / 1e9:.2f} GB, {bf / tf / 1e3 / peak_gbs:.2f} of copy peak)  "
           f"bwd {tb:8.1f} us  {bb / tb / 1e3:7.1f} GB/s ({bb / 1e9:.2f} GB, {bb / tb / 1e3 / peak_gbs:.2f})", flush=True)
     return plan, V
