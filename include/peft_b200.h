@@ -164,6 +164,31 @@ int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* 
                       int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign, float* wu, float* scratch,
                       int* counters, float* dV, void* stream);
 
+/* ---- fp32 verification mode ("within 1e-5 relative for fp32 mode", BASELINE.json north_star) -------------------------
+ * Plain CUDA-core fp32 counterparts of the entry points above: same operand layouts (row pitches in elements), same
+ * epilogue semantics with every bf16 tensor replaced by fp32, IEEE expf/erff/tanhf.  The Python engine selects them
+ * through the dtype of its buffers (EngineCfg.precision = "fp32"); peft_layernorm_fwd / _bwd_f32g already take fp32 on
+ * both sides.  They replace the same reference lines as their bf16 twins and are not the throughput path. */
+int peft_gemm_f32(const float* a, long long lda, const float* b, long long ldb, int M, int N, int K, const float* bias,
+                  float* out, long long ldo, float* out2, long long ldo2, const float* aux, long long ldaux, int epilogue,
+                  void* stream);
+/* out[I, J] += x[M, I]^T y[M, J], any I, J (split over M, fp32 atomics) */
+int peft_tn_reduce_f32(const float* x, long long ldx, int I, const float* y, long long ldy, int J, float* out,
+                       long long ldout, int M, void* stream);
+/* lse[B*H*L] = rowmax + ln(rowsum) of the scaled scores (private to the fp32 kernels) */
+int peft_attention_fwd_f32(const float* qkv, long long ldqkv, float* o, long long ldo, float* lse, int B, int H, int L,
+                           float scale, void* stream);
+int peft_attention_bwd_f32(const float* qkv, long long ldqkv, const float* o, long long ldo, const float* d_o, long long lddo,
+                           const float* lse, float* delta, float* dqkv, long long lddqkv, int B, int H, int L, float scale,
+                           void* stream);
+int peft_clip_delta_f32(float* qkv, long long ldqkv, float* delta, long long ldd, int B, int H, int L, float mult_q,
+                        float mult_v, int backward, void* stream);
+int peft_im2col_patches_f32(const float* images, float* patches, long long ldp, int B, int img, int patch, void* stream);
+int peft_assemble_tokens_f32(const float* patch_embed, const float* cls, const float* pos, float* x, int B, int L, int D,
+                             void* stream);
+/* out[i] = a[i] + b[i] (the residual add the bf16 path fuses into peft_layernorm_fwd_add) */
+int peft_add_f32(const float* a, const float* b, float* out, long long n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,15 @@ SIGNATURES = {
     "peft_phm_fold": [_vp, _vp, _vp, C.c_int, C.c_int, _vp],
     "peft_fastfood_fwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "peft_fastfood_bwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    # fp32 verification mode
+    "peft_gemm_f32": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
+    "peft_tn_reduce_f32": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp],
+    "peft_attention_fwd_f32": [_vp, _c_ll, _vp, _c_ll, _vp, C.c_int, C.c_int, C.c_int, C.c_float, _vp],
+    "peft_attention_bwd_f32": [_vp, _c_ll, _vp, _c_ll, _vp, _c_ll, _vp, _vp, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, _vp],
+    "peft_clip_delta_f32": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, _vp],
+    "peft_im2col_patches_f32": [_vp, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp],
+    "peft_assemble_tokens_f32": [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp],
+    "peft_add_f32": [_vp, _vp, _vp, _c_ll, _vp],
 }
 _RESTYPES = {"peft_last_error": None, "peft_launch_count": C.c_ulonglong}
 

@@ -43,6 +43,12 @@ class EngineCfg:
     dense_delta: bool = False  # q/v update given as dense H_q, H_v [D, D] (large-n KAdaptation "fold" variant):
                                # rank == width, Dn is the identity (not trainable) and UpT = [H_q | 0 | H_v]
     train_all: bool = False  # full fine-tuning / intrinsic-dimension mode: backward also emits dL/dW for EVERY tower tensor
+    precision: str = "bf16"  # "bf16": tensor-core path | "fp32": verification mode — every buffer fp32, plain CUDA-core kernels
+                             # (csrc/f32_sm100.cuh), same engine code; gate 1e-5 relative vs the fp32 oracle
+
+    @property
+    def cdt(self):
+        return torch.float32 if self.precision == "fp32" else torch.bfloat16
 
     @property
     def seq(self):
@@ -79,7 +85,8 @@ class _Workspace:
     def __init__(self, cfg: EngineCfg, B: int, dev):
         D, L, H, F, dep, rp = cfg.width, cfg.seq, cfg.heads, cfg.mlp, cfg.depth, cfg.rank_pad
         M = B * L
-        bf, f32 = torch.bfloat16, torch.float32
+        bf, f32 = cfg.cdt, torch.float32          # "bf" = the compute dtype of the GEMM / attention operands
+        fp32_mode = bf == f32
         e = lambda *s, dt=bf: torch.empty(*s, device=dev, dtype=dt)
         self.B, self.M = B, M
         P = L - 1
@@ -107,7 +114,7 @@ class _Workspace:
         # CLIP dialect with a q/v adapter: the update cannot ride in the K extension (raw-reshape placement)
         self.dlt = e(M, 2 * D) if (cfg.dialect == "clip" and rp) else None
         self.g = e(M, D, dt=f32)                                 # residual-gradient stream (fp32, like the forward stream)
-        self.gb = e(M, D)                                        # its bf16 copy: A operand of the dX products
+        self.gb = self.g if fp32_mode else e(M, D)               # its bf16 copy: A operand of the dX products
         # final LayerNorm on the cls rows
         self.meanf = e(B, dt=f32); self.rstdf = e(B, dt=f32)
         self.yf = e(B, D)                                        # clip: ln_post output (bf16 operand of the projection)
@@ -126,8 +133,8 @@ class _Workspace:
             self.upre = [e(M, m) for _ in range(dep)] if cfg.bn_act != "relu" else None   # pre-activation (gelu_new)
             self.dz = e(M, m)
             self.gh = e(M, D, dt=f32)                                # gradient w.r.t. h (fp32) and its bf16 copy
-            self.ghb = e(M, D)
-        if cfg.rank > 128 and not cfg.train_all:
+            self.ghb = self.gh if fp32_mode else e(M, D)
+        if cfg.rank > 128 and not cfg.train_all and not fp32_mode:
             Mp = (M + 7) // 8 * 8
             self.tA = torch.zeros(rp, Mp, device=dev, dtype=bf)           # p^T      [r', tokens]
             self.tB = torch.zeros(3 * D, Mp, device=dev, dtype=bf)        # dqkv^T   [3D, tokens]
@@ -148,6 +155,10 @@ class VitEngine:
     def __init__(self, cfg: EngineCfg, device="cuda"):
         if not torch.cuda.is_available():
             raise RuntimeError("peft_b200.VitEngine needs a CUDA device (sm_100a); there is no CPU fallback")
+        if cfg.precision not in ("bf16", "fp32"):
+            raise ValueError(f"EngineCfg.precision must be 'bf16' or 'fp32', got {cfg.precision!r}")
+        if cfg.precision == "fp32" and cfg.train_all:
+            raise NotImplementedError("the fp32 verification mode covers the PEFT engine (frozen tower + adapters), not train_all")
         self.cfg = cfg
         self.dev = torch.device(device)
         self.ws = {}
@@ -159,7 +170,7 @@ class VitEngine:
         """sd: reference-named fp32 state dict of the visual tower (any device)."""
         cfg, dev = self.cfg, self.dev
         D, F, dep, rp = cfg.width, cfg.mlp, cfg.depth, cfg.rank_pad
-        bf, f32 = torch.bfloat16, torch.float32
+        bf, f32 = cfg.cdt, torch.float32
         keys = _TIMM_KEYS if cfg.dialect == "timm" else _CLIP_KEYS
         g = lambda k: sd[k].detach().to(dev, f32)
         if keys["qkv_b"].format(i=0) not in sd:           # timm qkv_bias=False
@@ -248,7 +259,7 @@ class VitEngine:
     def _refresh_bottleneck(self, bn):
         """bn = (Wd [dep,m,D], bd [dep,m], Wu [dep,D,m], bu [dep,D], ln_g [dep,D], ln_b [dep,D]) fp32."""
         Wd, bd, Wu, bu, lg, lb = bn
-        bf = torch.bfloat16
+        bf = self.cfg.cdt
         with torch.no_grad():
             self.wd_bf = Wd.detach().to(bf).contiguous()                        # down: B [N=m, K=D]
             self.wdT_bf = Wd.detach().transpose(1, 2).to(bf).contiguous()       # dza : B [N=D, K=m]
@@ -351,7 +362,7 @@ class VitEngine:
         if self.vproj is None:
             ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
         else:
-            ops.gemm(dfeat.to(torch.bfloat16), self.vproj, w.dyf)                # dy = dfeat proj^T
+            ops.gemm(dfeat.to(cfg.cdt), self.vproj, w.dyf)                       # dy = dfeat proj^T
             ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
         dDn = dUpT = None
         if r:
@@ -399,7 +410,7 @@ class VitEngine:
                     ops.tn_reduce(pc, w.dlt[:, :D], dUpT[i, c:c + cw, :D])
                     ops.tn_reduce(pc, w.dlt[:, D:], dUpT[i, c:c + cw, 2 * D:])
                     ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
-            elif rp > 128:
+            elif rp > 128 and cfg.precision != "fp32":
                 dq = w.dqkv[:, :3 * D]
                 ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
                 self._dw(w, w.xn1[i][:, D:], dq, dUpT[i])                           # dUp^T = p^T dqkv as ONE tensor-core product
@@ -413,7 +424,8 @@ class VitEngine:
                 for c in range(0, rp, 64):                                          # adapter-gradient token reductions
                     cw = min(64, rp - c)
                     ops.tn_reduce(w.xn1[i][:, D + c:D + c + cw], dq, dUpT[i, c:c + cw])            # dUp^T = p^T dqkv
-                    ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])  # dDn = dp^T x
+                    if not cfg.dense_delta:
+                        ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])  # dDn = dp^T x
             if i == 0:
                 break       # block 0's input gradient feeds only the frozen patch embedding: no dX product, no LN1'
             if rp:

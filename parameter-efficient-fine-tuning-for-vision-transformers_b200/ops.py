@@ -33,7 +33,10 @@ def _mat(t: torch.Tensor, dtype=None, name="tensor"):
 
 
 def gemm(a, b, out, bias=None, epilogue=EPI_STORE, out2=None, aux=None):
-    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T (+ bias)); bf16 operands, see peft_gemm_bf16."""
+    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T (+ bias)); bf16 operands, see peft_gemm_bf16.  fp32 operands select the fp32
+    verification kernels (peft_gemm_f32: every tensor fp32, same epilogue semantics)."""
+    if a.dtype == torch.float32:
+        return _gemm_f32(a, b, out, bias, epilogue, out2, aux)
     pa, lda = _mat(a, torch.bfloat16, "a")
     pb, ldb = _mat(b, torch.bfloat16, "b")
     M, K = a.shape
@@ -57,6 +60,33 @@ def gemm(a, b, out, bias=None, epilogue=EPI_STORE, out2=None, aux=None):
     return out
 
 
+def _gemm_f32(a, b, out, bias, epilogue, out2, aux):
+    f32 = torch.float32
+    pa, lda = _mat(a, f32, "a")
+    pb, ldb = _mat(b, f32, "b")
+    M, K = a.shape
+    N = b.shape[0]
+    if b.shape[1] != K or tuple(out.shape) != (M, N):
+        raise ValueError(f"gemm(fp32): shape mismatch {tuple(a.shape)} x {tuple(b.shape)} -> {tuple(out.shape)}")
+    po, ldo = _mat(out, f32, "out")
+    po2, ldo2 = _mat(out2, f32, "out2") if out2 is not None else (0, 0)
+    pax, ldax = _mat(aux, f32, "aux") if aux is not None else (0, 0)
+    if bias is not None and (bias.dtype != f32 or bias.numel() != N or not bias.is_contiguous()):
+        raise ValueError("gemm: bias must be contiguous fp32 [N]")
+    _lib.check(_lib.load().peft_gemm_f32(pa, lda, pb, ldb, M, N, K, _p(bias), po, ldo, po2, ldo2, pax, ldax, epilogue,
+                                         _stream()), "peft_gemm_f32")
+    return out
+
+
+def add(a, b, out):
+    """out = a + b, contiguous fp32 (fp32 mode only: the bf16 path fuses this add into layernorm_fwd_add)."""
+    for t in (a, b, out):
+        if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != out.numel():
+            raise ValueError("add: contiguous CUDA fp32 tensors of one size required")
+    _lib.check(_lib.load().peft_add_f32(a.data_ptr(), b.data_ptr(), out.data_ptr(), out.numel(), _stream()), "peft_add_f32")
+    return out
+
+
 def layernorm_fwd(x, gamma, beta, y, mean=None, rstd=None, eps=1e-6):
     px, ldx = _mat(x, None, "x")
     py, ldy = _mat(y, None, "y")
@@ -68,7 +98,11 @@ def layernorm_fwd(x, gamma, beta, y, mean=None, rstd=None, eps=1e-6):
 
 
 def layernorm_fwd_add(x, gamma, beta, y, mean, rstd, add_in, add_out, eps=1e-5):
-    """y(bf16) = LN(x fp32); add_out(fp32) = x + add_in(fp32)."""
+    """y(bf16) = LN(x fp32); add_out(fp32) = x + add_in(fp32).  fp32 y (verification mode): two unfused launches."""
+    if y.dtype == torch.float32:
+        layernorm_fwd(x, gamma, beta, y, mean, rstd, eps)
+        add(x, add_in, add_out)
+        return y
     px, ldx = _mat(x, torch.float32, "x")
     py, ldy = _mat(y, torch.bfloat16, "y")
     pai, ldai = _mat(add_in, torch.float32, "add_in")
@@ -102,6 +136,10 @@ def layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g_in, g_out, g_copy=None, dgamm
     if g_in is not None:
         pgi, ldgi = _mat(g_in, torch.float32, "g_in")
     pgc = ldgc = 0
+    if g_copy is not None and g_copy.dtype == torch.float32:
+        if g_copy.data_ptr() != g_out.data_ptr():      # fp32 mode: the "copy" IS the fp32 stream
+            raise ValueError("layernorm_bwd_f32g: an fp32 g_copy must alias g_out")
+        g_copy = None
     if g_copy is not None:
         pgc, ldgc = _mat(g_copy, torch.bfloat16, "g_copy")
     M, D = x.shape
@@ -113,6 +151,12 @@ def layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g_in, g_out, g_copy=None, dgamm
 
 
 def attention_fwd(qkv, o, lse2, B, H, L, scale):
+    if qkv.dtype == torch.float32:
+        pq, ldq = _mat(qkv, torch.float32, "qkv")
+        po, ldo = _mat(o, torch.float32, "o")
+        _lib.check(_lib.load().peft_attention_fwd_f32(pq, ldq, po, ldo, _p(lse2), B, H, L, float(scale), _stream()),
+                   "peft_attention_fwd_f32")
+        return o
     pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
     po, ldo = _mat(o, torch.bfloat16, "o")
     _lib.check(_lib.load().peft_attention_fwd(pq, ldq, po, ldo, _p(lse2), B, H, L, float(scale), _stream()),
@@ -121,6 +165,12 @@ def attention_fwd(qkv, o, lse2, B, H, L, scale):
 
 
 def attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, scale):
+    if qkv.dtype == torch.float32:
+        f32 = torch.float32
+        (pq, ldq), (po, ldo), (pg, ldg), (pd, ldd) = _mat(qkv, f32, "qkv"), _mat(o, f32, "o"), _mat(d_o, f32, "d_o"), _mat(dqkv, f32, "dqkv")
+        _lib.check(_lib.load().peft_attention_bwd_f32(pq, ldq, po, ldo, pg, ldg, _p(lse2), _p(delta), pd, ldd, B, H, L,
+                                                      float(scale), _stream()), "peft_attention_bwd_f32")
+        return dqkv
     pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
     po, ldo = _mat(o, torch.bfloat16, "o")
     pg, ldg = _mat(d_o, torch.bfloat16, "d_o")
@@ -134,19 +184,26 @@ def im2col_patches(images, patches, patch):
     B, C, Hh, Ww = images.shape
     if C != 3 or Hh != Ww or images.dtype != torch.float32 or not images.is_contiguous() or not images.is_cuda:
         raise ValueError("im2col_patches: images must be contiguous CUDA fp32 [B,3,S,S]")
-    _lib.check(_lib.load().peft_im2col_patches(images.data_ptr(), patches.data_ptr(), patches.stride(0), B, Hh, patch, _stream()),
-               "peft_im2col_patches")
+    fn = _lib.load().peft_im2col_patches_f32 if patches.dtype == torch.float32 else _lib.load().peft_im2col_patches
+    _lib.check(fn(images.data_ptr(), patches.data_ptr(), patches.stride(0), B, Hh, patch, _stream()), "peft_im2col_patches")
     return patches
 
 
 def assemble_tokens(patch_embed, cls, pos, x, B, L, D):
-    _lib.check(_lib.load().peft_assemble_tokens(patch_embed.data_ptr(), cls.data_ptr(), pos.data_ptr(), x.data_ptr(), B,
-                                                L, D, _stream()), "peft_assemble_tokens")
+    fn = _lib.load().peft_assemble_tokens_f32 if patch_embed.dtype == torch.float32 else _lib.load().peft_assemble_tokens
+    _lib.check(fn(patch_embed.data_ptr(), cls.data_ptr(), pos.data_ptr(), x.data_ptr(), B, L, D, _stream()), "peft_assemble_tokens")
     return x
 
 
 def tn_reduce(x, y, out):
-    """out[I,J] += x[M,I]^T @ y[M,J]  (fp32 out, bf16 x / y)."""
+    """out[I,J] += x[M,I]^T @ y[M,J]  (fp32 out, bf16 x / y; fp32 x / y select the verification kernel, any I, J)."""
+    if x.dtype == torch.float32:
+        (px, ldx), (py, ldy), (po, ldo) = _mat(x, torch.float32, "x"), _mat(y, torch.float32, "y"), _mat(out, torch.float32, "out")
+        if tuple(out.shape) != (x.shape[1], y.shape[1]) or y.shape[0] != x.shape[0]:
+            raise ValueError("tn_reduce: shape mismatch")
+        _lib.check(_lib.load().peft_tn_reduce_f32(px, ldx, x.shape[1], py, ldy, y.shape[1], po, ldo, x.shape[0], _stream()),
+                   "peft_tn_reduce_f32")
+        return out
     px, ldx = _mat(x, torch.bfloat16, "x")
     py, ldy = _mat(y, torch.bfloat16, "y")
     po, ldo = _mat(out, torch.float32, "out")
@@ -160,12 +217,13 @@ def tn_reduce(x, y, out):
 
 def clip_delta(qkv, delta, B, H, L, mult_q, mult_v, backward=False):
     """CLIP-dialect raw-reshape placement of the q/v update, see peft_clip_delta."""
-    pq, ldq = _mat(qkv, torch.bfloat16, "qkv")
-    pd, ldd = _mat(delta, torch.bfloat16, "delta")
+    dt = qkv.dtype if qkv.dtype == torch.float32 else torch.bfloat16
+    pq, ldq = _mat(qkv, dt, "qkv")
+    pd, ldd = _mat(delta, dt, "delta")
     if qkv.shape[0] != B * L or delta.shape[0] != B * L or delta.shape[1] != 2 * H * 64:
         raise ValueError("clip_delta: shape mismatch")
-    _lib.check(_lib.load().peft_clip_delta(pq, ldq, pd, ldd, B, H, L, float(mult_q), float(mult_v), int(backward),
-                                           _stream()), "peft_clip_delta")
+    fn = _lib.load().peft_clip_delta_f32 if dt == torch.float32 else _lib.load().peft_clip_delta
+    _lib.check(fn(pq, ldq, pd, ldd, B, H, L, float(mult_q), float(mult_v), int(backward), _stream()), "peft_clip_delta")
     return delta if backward else qkv
 
 

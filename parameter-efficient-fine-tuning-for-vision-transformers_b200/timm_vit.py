@@ -359,8 +359,9 @@ def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck):
                                   "(PEFT) or build the model with adapter='none' (full fine-tuning / Fastfood)")
     slot = "_engine_full" if full else "_engine"
     eng = getattr(model, slot, None)
-    if eng is None or eng.dev != x.device:
-        eng = VitEngine(EngineCfg(dialect=dialect, train_all=full, **extra_cfg, **geom), x.device)
+    precision = getattr(model, "precision", "bf16")      # "fp32": verification mode (plain fp32 kernels, 1e-5 gate)
+    if eng is None or eng.dev != x.device or eng.cfg.precision != precision:
+        eng = VitEngine(EngineCfg(dialect=dialect, train_all=full, precision=precision, **extra_cfg, **geom), x.device)
         setattr(model, slot, eng)
         model._frozen_sig = None
     if full:
