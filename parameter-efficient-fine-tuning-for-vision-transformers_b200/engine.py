@@ -145,8 +145,9 @@ class _Workspace:
             self.ones = torch.zeros(M, 16, device=dev, dtype=bf)
             self.ones[:, 0] = 1.0
             Mp = (M + 7) // 8 * 8
-            self.tA = torch.zeros(max(F, 3 * D), Mp, device=dev, dtype=bf)            # dY^T  [N, tokens]
-            self.tB = torch.zeros(max(F, D, cfg.patch_k), Mp, device=dev, dtype=bf)   # X^T   [K, tokens]
+            if not fp32_mode:
+                self.tA = torch.zeros(max(F, 3 * D), Mp, device=dev, dtype=bf)            # dY^T  [N, tokens]
+                self.tB = torch.zeros(max(F, D, cfg.patch_k), Mp, device=dev, dtype=bf)   # X^T   [K, tokens]
             self.mean_pre = e(M, dt=f32); self.rstd_pre = e(M, dt=f32)
         self.generation = 0
 
@@ -157,8 +158,6 @@ class VitEngine:
             raise RuntimeError("peft_b200.VitEngine needs a CUDA device (sm_100a); there is no CPU fallback")
         if cfg.precision not in ("bf16", "fp32"):
             raise ValueError(f"EngineCfg.precision must be 'bf16' or 'fp32', got {cfg.precision!r}")
-        if cfg.precision == "fp32" and cfg.train_all:
-            raise NotImplementedError("the fp32 verification mode covers the PEFT engine (frozen tower + adapters), not train_all")
         self.cfg = cfg
         self.dev = torch.device(device)
         self.ws = {}
@@ -445,6 +444,10 @@ class VitEngine:
     # ------------------------------------------------------------------ backward, full fine-tuning mode
     def _dw(self, w, dY, X, out):
         """out[N, K] (fp32) = dY[M, N]^T X[M, K]: both operands transposed to K-major, then the tcgen05 GEMM."""
+        if self.cfg.precision == "fp32":           # verification mode: one fp32 token reduction (any shape)
+            out.zero_()
+            ops.tn_reduce(dY, X, out)
+            return
         M = dY.shape[0]
         Mp = (M + 7) // 8 * 8                      # contraction length padded to the GEMM's K granularity; the pad
         a = w.tA[:dY.shape[1]]                     # columns [M, Mp) of tA / tB are never written and stay zero
@@ -482,7 +485,7 @@ class VitEngine:
         if self.vproj is None:
             ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dlnf_w, dlnf_b)
         else:
-            dfb = dfeat.to(torch.bfloat16)
+            dfb = dfeat.to(cfg.cdt)
             if want("proj"):
                 dproj = e(D, cfg.out_dim)
                 self._dw(w, w.yf, dfb, dproj)                                      # proj [D, E] = yf^T dfeat
@@ -545,14 +548,18 @@ class VitEngine:
         # embedding: w.g = dL/dx0 (fp32 [B, L, D])
         if cfg.dialect == "clip":
             dg, db = z(D), z(D)
-            ops.layernorm_bwd_f32g(w.g, w.tokens, w.mean_pre, w.rstd_pre, self.lnpre_w, None, w.x1[0], w.gb, dg, db)
+            fp32_mode = cfg.precision == "fp32"
+            ops.layernorm_bwd_f32g(w.g, w.tokens, w.mean_pre, w.rstd_pre, self.lnpre_w, None, w.x1[0],
+                                   None if fp32_mode else w.gb, dg, db)
             G["ln_pre.weight"], G["ln_pre.bias"] = dg, db
             g3 = w.x1[0].view(B, L, D)          # x1[0] is dead by now: reuse it for dL/d(tokens before ln_pre)
+            gop = g3 if fp32_mode else w.gb.view(B, L, D)    # operand copy of it in the compute dtype
         else:
             g3 = w.g.view(B, L, D)
+            gop = w.gb.view(B, L, D)            # (fp32 mode: gb aliases g)
         dpos = g3.sum(0)                                     # [L, D] batch reduction of the token gradient (glue)
         P = L - 1
-        dpe = w.gb.view(B, L, D)[:, 1:, :].reshape(B * P, D)
+        dpe = gop[:, 1:, :].reshape(B * P, D)
         kk = 3 * cfg.patch * cfg.patch
         dconv = e(D, kk)
         if want("patch_embed.proj.weight" if cfg.dialect == "timm" else "conv1.weight"):

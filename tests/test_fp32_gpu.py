@@ -88,6 +88,38 @@ def test_fp32_mode_matches_oracle(name):
         assert r < 5 * TOL, (k, r)
 
 
+FULL_CASES = {
+    "timm_L5": (VitCfg(dialect="timm", adapter="none", img=64, patch=32, depth=2), 8),
+    "timm_L50": (VitCfg(dialect="timm", adapter="none", img=224, patch=32, depth=2), 6),
+    "clip_L50": (VitCfg(dialect="clip", adapter="none", img=224, patch=32, depth=2), 5),
+}
+
+
+@pytest.mark.parametrize("name", list(FULL_CASES))
+def test_fp32_full_mode_all_tower_gradients(name):
+    """train_all (full fine-tuning / Fastfood C5 backward): dL/dW of every tower tensor in fp32 mode vs the oracle."""
+    from tests.test_full_gpu import build
+    cfg, B = FULL_CASES[name]
+    sd = synth.make_state_dict(cfg, seed=0, grad_test=True)
+    model = build(cfg, sd)
+    model.precision = "fp32"
+    images, _ = synth.make_batch(cfg, B)
+    w = torch.randn(B, cfg.feat_dim, generator=torch.Generator().manual_seed(3))
+    feat = model(images.cuda())
+    (feat * w.cuda()).sum().backward()
+    assert model._engine_full.cfg.precision == "fp32"
+    sd_o = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    rfeat = O.visual_forward(images, sd_o, cfg)
+    (rfeat * w).sum().backward()
+    assert rel(feat, rfeat) < TOL, rel(feat, rfeat)
+    params = dict(model.named_parameters())
+    got = torch.cat([params[k].grad.float().cpu().reshape(-1) for k in sd])
+    ref = torch.cat([sd_o[k].grad.reshape(-1) for k in sd])
+    assert rel(got, ref) < TOL, rel(got, ref)
+    worst = max((rel(params[k].grad, sd_o[k].grad), k) for k in sd)
+    assert worst[0] < 5 * TOL, worst
+
+
 def test_fp32_and_bf16_engines_coexist():
     """Switching `precision` rebuilds the engine; the bf16 result stays within its own gate of the fp32 one."""
     cfg = VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=64, patch=32, depth=2)
