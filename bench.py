@@ -217,6 +217,8 @@ def main():
     ap.add_argument("--depth", type=int, default=0, help="debug only: override depth (marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="fp32 = the verification mode (plain CUDA-core kernels behind the same engine); reported, not the headline")
     ap.add_argument("--graph", type=int, default=1, help="1: replay the whole step from one CUDA graph (default), 0: eager launches")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -257,6 +259,7 @@ def main():
         from peft_b200.clip_model import VisionTransformer
         vit = VisionTransformer(224, c["patch"], c["width"], depth, c["heads"], c["out_dim"], adapter=c["adapter"], **kw)
     vit.load_state_dict(sd, strict=False)
+    vit.precision = args.precision
     if c.get("fastfood_d"):
         from peft_b200.fastfood import FastfoodWrap
         import numpy as np
@@ -432,6 +435,11 @@ def main():
         }
         if args.depth and args.depth != c["depth"]:
             line["invalid"] = "debug run with reduced depth"
+        if args.precision == "fp32":
+            line["dtype"] = "f32"
+            line["note"] = "fp32 verification mode: plain CUDA-core kernels (csrc/f32_sm100.cuh), no tensor cores; not the headline path"
+            line["roofline"]["kernel"] = "f32::gemm_kernel (CUDA-core SGEMM; fraction is against the bf16 tensor peak and only shows the gap)"
+            line["roofline"]["traffic"] = None
         if world == 1 and not args.no_cpu_baseline:
             base, _, _ = cpu_reference_rate(args.config, budget_s=20.0, steps=2, warmup=1)
             line["cpu_baseline"] = base
