@@ -345,12 +345,14 @@ class VitEngine:
         return feat
 
     # ------------------------------------------------------------------ backward
-    def backward(self, dfeat):
+    def backward(self, dfeat, generation=None):
+        """`generation` = the engine's `_fwd_generation` right after the forward this backward belongs to (the autograd
+        node records it); a later forward at the same batch size has overwritten the saved activations."""
         cfg = self.cfg
         D, L, H, dep, r, rp = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.rank, cfg.rank_pad
         B = dfeat.shape[0]
         w = self._workspace(B)
-        if self._fwd_generation != (B, w.generation):
+        if (generation or self._fwd_generation) != (B, w.generation):
             raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
         dfeat = dfeat.contiguous().float()
         w.g.zero_()
@@ -456,7 +458,7 @@ class VitEngine:
         ops.transpose(X, b[:, :M])
         ops.gemm(a[:, :Mp], b[:, :Mp], out, epilogue=ops.EPI_STORE_F32)
 
-    def backward_full(self, dfeat, need=None):
+    def backward_full(self, dfeat, need=None, generation=None):
         """dL/d(every tower tensor) -> {reference key: fp32 grad}.  Only for cfg.train_all (no adapters): the Fastfood /
         full-fine-tuning configuration C5, where theta is a function of V and autograd needs every dW
         (FL/intrinsic/fastfood.py:61-77).  Same kernels as the PEFT backward plus, per linear layer, one weight-gradient
@@ -467,7 +469,7 @@ class VitEngine:
         D, L, H, dep, F = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.mlp
         B = dfeat.shape[0]
         w = self._workspace(B)
-        if self._fwd_generation != (B, w.generation):
+        if (generation or self._fwd_generation) != (B, w.generation):
             raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
         dev, f32 = self.dev, torch.float32
         z = lambda *sh: torch.zeros(*sh, device=dev, dtype=f32)
@@ -589,11 +591,13 @@ class _BackboneFullFn(torch.autograd.Function):
         ctx.engine, ctx.names = engine, names
         ctx.need = {n for n, t in zip(names, tensors) if t.requires_grad}
         engine.load_frozen({n: t.detach() for n, t in zip(names, tensors)})
-        return engine.forward(images)
+        out = engine.forward(images)
+        ctx.generation = engine._fwd_generation
+        return out
 
     @staticmethod
     def backward(ctx, dfeat):
-        G = ctx.engine.backward_full(dfeat, ctx.need)
+        G = ctx.engine.backward_full(dfeat, ctx.need, ctx.generation)
         return (None, None, None) + tuple(G.get(n) if n in ctx.need else None for n in ctx.names)
 
 
@@ -608,11 +612,13 @@ class _BackboneFn(torch.autograd.Function):
     def forward(ctx, engine, images, Dn, UpT, *bn):
         ctx.engine = engine
         ctx.nbn = len(bn)
-        return engine.forward(images, Dn, UpT, bn if bn else None)
+        out = engine.forward(images, Dn, UpT, bn if bn else None)
+        ctx.generation = engine._fwd_generation
+        return out
 
     @staticmethod
     def backward(ctx, dfeat):
-        dDn, dUpT, bng = ctx.engine.backward(dfeat)
+        dDn, dUpT, bng = ctx.engine.backward(dfeat, ctx.generation)
         extra = tuple(bng) if bng is not None else (None,) * ctx.nbn
         return (None, None, dDn, dUpT) + extra
 
