@@ -74,9 +74,15 @@ extern "C" int peft_transpose_bf16(const void* in, long long ldin, int rows, int
   PEFT_REQUIRE(ldin % 2 == 0 && ldout % 2 == 0 && ldin >= cols && ldout >= rows && (reinterpret_cast<uintptr_t>(in) & 3) == 0 &&
                    (reinterpret_cast<uintptr_t>(out) & 3) == 0,
                "peft_transpose_bf16: pitches must be even and pointers 4-byte aligned");
-  dim3 grid((cols + 63) / 64, (rows + 63) / 64);
-  transpose_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows, cols,
-                                                                                 (__nv_bfloat16*)out, ldout);
+  if (al16(in) && al16(out) && ldin % 8 == 0 && ldout % 8 == 0) {
+    dim3 grid((cols + 255) / 256, (rows + 63) / 64);
+    transpose_bf16_vec_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows, cols,
+                                                                                        (__nv_bfloat16*)out, ldout);
+  } else {
+    dim3 grid((cols + 63) / 64, (rows + 63) / 64);
+    transpose_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows, cols,
+                                                                                   (__nv_bfloat16*)out, ldout);
+  }
   PEFT_LAUNCH_CHECK();
   return 0;
 }

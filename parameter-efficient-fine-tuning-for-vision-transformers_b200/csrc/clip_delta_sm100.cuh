@@ -117,6 +117,39 @@ __global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16
   }
 }
 
+// 16-byte-aligned fast path: no shared memory.  Each thread moves one 8 x 8 bf16 block: 8 row vectors (16 B, 8 columns)
+// in, an in-register transpose with byte permutes, 8 column vectors (16 B, 8 rows) out.  Lanes are laid out 4 (column
+// groups) x 8 (row groups), so a warp reads 64-byte and writes 128-byte contiguous runs: whole 32-byte sectors both ways.
+// CTA = 8 warps side by side: 64 rows x 256 columns.  Blocks crossing the matrix edge take the guarded scalar path.
+__global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows,
+                                                                int cols, __nv_bfloat16* __restrict__ out, long long ldout) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cg = lane & 3, rg = lane >> 2;
+  const int r0 = blockIdx.y * 64 + rg * 8;
+  const int c0 = blockIdx.x * 256 + warp * 32 + cg * 8;
+  if (r0 >= rows || c0 >= cols) return;
+  if (r0 + 8 <= rows && c0 + 8 <= cols) {
+    uint4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const uint4*>(in + (long long)(r0 + j) * ldin + c0);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t sel = (c & 1) ? 0x7632u : 0x5410u;      // high / low bf16 of both source registers
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t a = reinterpret_cast<const uint32_t*>(&v[2 * k])[c >> 1];
+        const uint32_t b = reinterpret_cast<const uint32_t*>(&v[2 * k + 1])[c >> 1];
+        w[k] = __byte_perm(a, b, sel);
+      }
+      *reinterpret_cast<uint4*>(out + (long long)(c0 + c) * ldout + r0) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  } else {
+    for (int j = 0; j < 8 && r0 + j < rows; ++j)
+      for (int c = 0; c < 8 && c0 + c < cols; ++c) out[(long long)(c0 + c) * ldout + r0 + j] = in[(long long)(r0 + j) * ldin + c0 + c];
+  }
+}
+
 }  // namespace peft
 
 // ---- large-n KAdaptation "fold" (the committed phm_dim = n = D, K = P = 1) --------------------------

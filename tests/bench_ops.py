@@ -93,6 +93,20 @@ def bench_gemm(M=50432, iters=20):
         print(f"gemm {name:24s} M={M} N={N} K={K}: {t:7.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
 
 
+def bench_gemm_dw(tokens=12800, iters=20):
+    """Weight-gradient products of the full mode (C5): out[N_out, K_in] = dY^T X, contraction over the tokens."""
+    for name, No, Ki in [("dW qkv", 2304, 768), ("dW proj", 768, 768), ("dW fc1", 3072, 768), ("dW fc2", 768, 3072)]:
+        a = torch.randn(No, tokens, device="cuda").to(torch.bfloat16)
+        b = torch.randn(Ki, tokens, device="cuda").to(torch.bfloat16)
+        out = torch.empty(No, Ki, device="cuda")
+        t = timeit(lambda: ops.gemm(a, b, out, epilogue=ops.EPI_STORE_F32), iters=iters, warm=2)
+        print(f"gemm {name:10s} M={No} N={Ki} K={tokens}: {t:7.1f} us  {2.0 * No * Ki * tokens / t / 1e6:7.1f} TFLOP/s", flush=True)
+        x = torch.randn(tokens, No, device="cuda").to(torch.bfloat16)
+        xt = torch.empty(No, tokens, device="cuda", dtype=torch.bfloat16)
+        t = timeit(lambda: ops.transpose(x, xt), iters=iters, warm=2)
+        print(f"     transpose [{tokens} x {No}] bf16: {t:7.1f} us  {4.0 * tokens * No / t / 1e3:7.1f} GB/s", flush=True)
+
+
 def bench_phm_fold(n=768, peak_gbs=6552.0):
     """Large-n KAdaptation fold: one streaming pass over phm_rule (n^3 fp32 = 1.81 GB at n = 768) per direction."""
     rule = torch.randn(n, n, n, device="cuda")
@@ -168,6 +182,9 @@ if __name__ == "__main__":
         bench_phm_fold()
     if what in ("fastfood", "all"):
         bench_fastfood()
+    if what == "gemm_c5":
+        bench_gemm(12800)
+        bench_gemm_dw(12800)
     if what == "prof_fastfood":
         bench_fastfood(iters=1)
         torch.cuda.synchronize()

@@ -237,3 +237,19 @@ def test_phm_fold(n):
     ops.phm_fold(rule.cuda(), dH.cuda(), ds, backward=True)
     ref = torch.einsum("pac,iac->pi", dH.double(), rule.double())
     assert float((ds.cpu().double() - ref).norm() / ref.norm()) < 1e-5
+
+
+@pytest.mark.parametrize("R,C,cpad,rpad", [(12800, 2304, 0, 0), (1001, 260, 4, 7), (198, 72, 0, 0), (130, 50, 0, 0),
+                                            (64, 8, 0, 0), (6, 4, 0, 2)])
+def test_transpose(ops, R, C, cpad, rpad):
+    """bf16 transpose: the 16-byte fast path (register 8x8 transposes) incl. ragged edges (1001 x 260 inside pitches 264 /
+    1008), and the fallback for pitches that are not multiples of 8; bit-exact (pure data movement).  Pads make the
+    operands column slices of wider buffers; nothing may be written outside the view."""
+    g = torch.Generator().manual_seed(R + C)
+    src = torch.randn(R, C + cpad, generator=g).to(torch.bfloat16).cuda()
+    dst = torch.full((C, R + rpad), 7.0, device="cuda", dtype=torch.bfloat16)
+    x, out = src[:, :C], dst[:, :R]
+    ops.transpose(x, out)
+    assert torch.equal(out, x.t())
+    if rpad:
+        assert bool((dst[:, R:] == 7.0).all())
