@@ -55,7 +55,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2SmemBytes));
     configured = true;
   }
-  const int num_tiles = ((p.M + 2 * kBM - 1) / (2 * kBM)) * ((p.N + kG2BN - 1) / kG2BN);
+  const int num_tiles = ((p.M + 2 * kBM - 1) / (2 * kBM)) * ((p.N + kG2BN - 1) / kG2BN) * (p.ksplit > 1 ? p.ksplit : 1);
   const int max_clusters = sm_count() / 2;
   const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
   cudaLaunchConfig_t cfg = {};
@@ -104,6 +104,28 @@ static bool use_gemm2(int M, int N) {
   return tiles >= sm_count() / 2;
 }
 
+// Split-K for weight-gradient-shaped products (fp32 output with few 256 x 256 tiles and a long contraction): the smallest
+// number of K ranges (<= 8, each >= 16 k-blocks) that fills >= 90 % of the waves over the 74 SM pairs; 1 = do not split.
+static int pick_ksplit(int M, int N, int K, int epilogue, const float* bias, long long ldo) {
+  if (epilogue != EPI_STORE_F32 || bias != nullptr || gemm_algo().load(std::memory_order_relaxed) == 1) return 1;
+  if (N < 256 || ldo != N) return 1;                      // contiguous output: one memset zeroes it
+  const long long tiles = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  const int pairs = sm_count() / 2;
+  const int num_kb = (K + kBK - 1) / kBK;
+  if (tiles >= pairs || num_kb < 32) return 1;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int sp = 2; sp <= 8; ++sp) {
+    const int per = (num_kb + sp - 1) / sp;
+    if (per < 16 || (long long)per * (sp - 1) >= num_kb) continue;      // no empty range
+    const long long t = tiles * sp;
+    const double eff = (double)t / (double)(((t + pairs - 1) / pairs) * pairs);
+    if (eff > best_eff + 0.02) { best_eff = eff; best = sp; }
+    if (best_eff >= 0.9) break;
+  }
+  return best;
+}
+
 // Tile-width heuristic: widest tile that still gives >= ~2 waves over the SMs; narrow outputs get BN=32.
 static int pick_bn(int M, int N) {
   if (N <= 64) return 32;
@@ -145,7 +167,9 @@ extern "C" int peft_gemm_bf16(const void* a, long long lda, const void* b, long 
   GemmParams p;
   p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
   p.aux = aux; p.ldaux = ldaux;
-  if (use_gemm2(M, N)) {
+  p.ksplit = pick_ksplit(M, N, K, epilogue, bias, ldo);
+  if (p.ksplit > 1) PEFT_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)M * N * sizeof(float), s));
+  if (p.ksplit > 1 || use_gemm2(M, N)) {
     CUtensorMap ta, tb, to, to2, tx;
     int rc = make_tmap_2d(&ta, a, false, (unsigned long long)M, (unsigned long long)K, (unsigned long long)lda, kBM, 64);
     if (rc) return rc;

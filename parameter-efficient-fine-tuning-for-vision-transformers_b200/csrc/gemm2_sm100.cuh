@@ -77,6 +77,13 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* 
                "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
                : "memory");
 }
+// same box, but added into global memory (fp32 tensor map): split-K partial sums
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
@@ -228,8 +235,10 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 
   const int num_mp = (p.M + 2 * kBM - 1) / (2 * kBM);     // 256-row pair tiles
   const int num_n = (p.N + kG2BN - 1) / kG2BN;
-  const int num_tiles = num_mp * num_n;
+  const int ksplit = p.ksplit > 1 ? p.ksplit : 1;
+  const int num_tiles = num_mp * num_n * ksplit;            // tile = (mp * num_n + n_blk) * ksplit + ks
   const int num_kb = (p.K + kBK - 1) / kBK;
+  const int kb_per = (num_kb + ksplit - 1) / ksplit;        // k-blocks per split (the host guarantees none is empty)
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
 
@@ -239,10 +248,12 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        const int mp = tile / num_n, n_blk = tile % num_n;
+        const int ks = tile % ksplit, mn = tile / ksplit;
+        const int mp = mn / num_n, n_blk = mn % num_n;
         const int row_a = mp * 2 * kBM + (int)cta_rank * kBM;
         const int row_b = n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = ks * kb_per, kb1 = min(num_kb, kb0 + kb_per);
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = tiles + stage * kG2StageBytes;
           uint8_t* sb = sa + kBM * kBK * 2;
@@ -266,7 +277,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
         ptx::tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kG2BN);
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = (tile % ksplit) * kb_per, kb1 = min(num_kb, kb0 + kb_per);
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait_cluster(&full_bar[stage], phase);
           ptx::tcgen05_fence_after();
           const uint32_t sa = ptx::smem_u32(tiles + stage * kG2StageBytes);
@@ -276,7 +288,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           const int ksteps = krem >= kBK ? (kBK / 16) : ((krem + 15) / 16);
           for (int k = 0; k < ksteps; ++k)
             ptx::umma_bf16_2sm(tmem_d, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k), idesc,
-                               (kb | k) != 0 ? 1u : 0u);
+                               (kb != kb0 || k != 0) ? 1u : 0u);
           ptx::umma_commit_2sm(&empty_bar[stage], 3);       // frees this smem slot in both CTAs
           if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
         }
@@ -299,7 +311,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-      const int mp = tile / num_n, n_blk = tile % num_n;
+      const int mn = tile / ksplit;
+      const int mp = mn / num_n, n_blk = mn % num_n;
       const int row0 = mp * 2 * kBM + (int)cta_rank * kBM + quarter * 32;   // first row of this warp's 32-row slab
       const int col0 = n_blk * kG2BN + half * 128;                          // first of this warp's 128 columns
       if constexpr (T::kAux) {
@@ -431,6 +444,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           if constexpr (T::kDual) {
             ptx::tma_store_2d(&tmap_out, slot_ptr(0), colu, row0);
             ptx::tma_store_2d(&tmap_out2, slot_ptr(1), colu, row0);
+          } else if (EPI == EPI_STORE_F32 && ksplit > 1) {
+            ptx::tma_reduce_add_2d(&tmap_out, slot_ptr(s), colu, row0);
           } else {
             ptx::tma_store_2d(&tmap_out, slot_ptr(s), colu, row0);
           }

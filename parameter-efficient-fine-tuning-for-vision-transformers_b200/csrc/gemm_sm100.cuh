@@ -46,6 +46,8 @@ struct GemmParams {
   long long ldo2;
   const void* aux;    // residual (fp32) / pre-activation (bf16) or nullptr
   long long ldaux;
+  int ksplit = 1;     // 2-CTA kernel, EPI_STORE_F32 only: K is cut into `ksplit` ranges that are separate tiles and are
+                      // summed into a pre-zeroed `out` by TMA reduce-add (weight-gradient products: small output, long K)
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }

@@ -253,3 +253,18 @@ def test_transpose(ops, R, C, cpad, rpad):
     assert torch.equal(out, x.t())
     if rpad:
         assert bool((dst[:, R:] == 7.0).all())
+
+
+@pytest.mark.parametrize("M,N,K", [(768, 768, 12800), (2304, 768, 12800), (3072, 768, 4096), (768, 600, 2048), (300, 520, 2304)])
+def test_gemm_splitk_f32(ops, M, N, K):
+    """Weight-gradient-shaped products (small fp32 output, long contraction) take the split-K route of the 2-CTA kernel:
+    K ranges as separate tiles, summed into the zeroed output by TMA reduce-add.  The output is pre-filled with NaN to
+    prove the library zeroes it; ragged M / N check the clipped reduce boxes."""
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g).to(torch.bfloat16).cuda()
+    b = torch.randn(N, K, generator=g).to(torch.bfloat16).cuda()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(a, b, out, epilogue=ops.EPI_STORE_F32)
+    ref = a.double() @ b.double().T
+    err = float((out.double() - ref).norm() / ref.norm())
+    assert err < 1e-5, err
