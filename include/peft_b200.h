@@ -124,6 +124,11 @@ int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int 
  * full-fine-tuning / intrinsic-dimension mode computes dW (FL/intrinsic/fastfood.py:61-77 makes every wrapped weight
  * a function of V, so autograd needs dL/dW for all of them). */
 int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream);
+/* same, and colsum[c] += sum_r in[r, c] (fp32, caller zeroes it) in the same pass: the bias gradient of a linear layer
+ * (autograd of `+ bias`, FS/kadaptation.py:72-78,133,236) is the column sum of the dY being transposed for its dW product.
+ * Requires 16-byte aligned operands and pitches % 8 == 0. */
+int peft_transpose_colsum_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, float* colsum,
+                               void* stream);
 
 /* Large-n KAdaptation fold (the committed phm_dim = n = D, K = P = 1).
  * replaces: kronecker_product_einsum_batched(phm_rule, W).sum(0) of matvec_product (FS/kadaptation.py:81-115) for BOTH

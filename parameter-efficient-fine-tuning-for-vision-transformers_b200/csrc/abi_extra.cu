@@ -69,22 +69,37 @@ extern "C" int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long lon
   return 0;
 }
 
-extern "C" int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream) {
+static int transpose_impl(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, float* colsum,
+                          void* stream) {
   PEFT_REQUIRE(rows > 0 && cols > 0 && in && out, "peft_transpose_bf16: bad shape rows=%d cols=%d", rows, cols);
   PEFT_REQUIRE(ldin % 2 == 0 && ldout % 2 == 0 && ldin >= cols && ldout >= rows && (reinterpret_cast<uintptr_t>(in) & 3) == 0 &&
                    (reinterpret_cast<uintptr_t>(out) & 3) == 0,
                "peft_transpose_bf16: pitches must be even and pointers 4-byte aligned");
-  if (al16(in) && al16(out) && ldin % 8 == 0 && ldout % 8 == 0) {
+  const bool vec = al16(in) && al16(out) && ldin % 8 == 0 && ldout % 8 == 0;
+  PEFT_REQUIRE(colsum == nullptr || vec, "peft_transpose_colsum_bf16: needs 16-byte aligned operands and pitches %% 8 == 0");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (vec) {
     dim3 grid((cols + 255) / 256, (rows + 63) / 64);
-    transpose_bf16_vec_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows, cols,
-                                                                                        (__nv_bfloat16*)out, ldout);
+    if (colsum)
+      transpose_bf16_vec_kernel<true><<<grid, 256, 0, s>>>((const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout, colsum);
+    else
+      transpose_bf16_vec_kernel<false><<<grid, 256, 0, s>>>((const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout, nullptr);
   } else {
     dim3 grid((cols + 63) / 64, (rows + 63) / 64);
-    transpose_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows, cols,
-                                                                                   (__nv_bfloat16*)out, ldout);
+    transpose_bf16_kernel<<<grid, 256, 0, s>>>((const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout);
   }
   PEFT_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream) {
+  return transpose_impl(in, ldin, rows, cols, out, ldout, nullptr, stream);
+}
+
+extern "C" int peft_transpose_colsum_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout,
+                                          float* colsum, void* stream) {
+  PEFT_REQUIRE(colsum != nullptr, "peft_transpose_colsum_bf16: null colsum");
+  return transpose_impl(in, ldin, rows, cols, out, ldout, colsum, stream);
 }
 
 extern "C" int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, int backward, void* stream) {

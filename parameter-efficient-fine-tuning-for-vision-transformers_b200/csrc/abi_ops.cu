@@ -10,9 +10,10 @@ using namespace peft;
 
 namespace {
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
-inline int ln_grid(int M) {
+inline int ln_grid(int M, bool param_grad = false) {
   const int blocks = (M + 7) / 8;
-  const int cap = sm_count() * 8;
+  // with dgamma / dbeta every CTA ends in 2*D global atomics: keep the grid at 4 CTAs per SM so that they stay negligible
+  const int cap = sm_count() * (param_grad ? 4 : 8);
   return blocks < cap ? (blocks > 0 ? blocks : 1) : cap;
 }
 }  // namespace
@@ -81,8 +82,8 @@ extern "C" int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32,
   PEFT_REQUIRE(lddy % 4 == 0 && ldx % 4 == 0 && ldgo % 4 == 0 && ldgi % 4 == 0, "peft_layernorm_bwd: pitches must be multiples of 4");
   PEFT_REQUIRE((dgamma == nullptr) == (dbeta == nullptr), "peft_layernorm_bwd: dgamma and dbeta go together");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  const int grid = ln_grid(M);
   const bool pg = dgamma != nullptr;
+  const int grid = ln_grid(M, pg);
   using bf = __nv_bfloat16;
 #define LN_BWD_LAUNCH(DYT, XT, PG) \
   ln_bwd_kernel<NV, DYT, XT, bf, PG><<<grid, 256, 0, s>>>((const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, (const bf*)g_in, ldgi, (bf*)g_out, ldgo, dgamma, dbeta, M)
@@ -114,8 +115,8 @@ extern "C" int peft_layernorm_bwd_f32g(const void* dy, long long lddy, int dy_is
                "peft_layernorm_bwd_f32g: pitches must be multiples of 4");
   PEFT_REQUIRE((dgamma == nullptr) == (dbeta == nullptr), "peft_layernorm_bwd_f32g: dgamma and dbeta go together");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  const int grid = ln_grid(M);
   const bool pg = dgamma != nullptr;
+  const int grid = ln_grid(M, pg);
   using bf = __nv_bfloat16;
 #define LN_BWD_LAUNCH32(DYT, XT, PG) \
   ln_bwd_kernel<NV, DYT, XT, float, PG><<<grid, 256, 0, s>>>((const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, g_in, ldgi, g_out, ldgo, dgamma, dbeta, M, (bf*)g_copy, ldgc)

@@ -121,17 +121,38 @@ __global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16
 // in, an in-register transpose with byte permutes, 8 column vectors (16 B, 8 rows) out.  Lanes are laid out 4 (column
 // groups) x 8 (row groups), so a warp reads 64-byte and writes 128-byte contiguous runs: whole 32-byte sectors both ways.
 // CTA = 8 warps side by side: 64 rows x 256 columns.  Blocks crossing the matrix edge take the guarded scalar path.
+// COLSUM: also colsum[c] += sum_r in[r, c] (fp32): the bias gradient of a linear layer is the column sum of the same dY
+// that is being transposed for the weight-gradient product, so it rides along (8 lanes share a column group: three
+// shuffles, then one global atomic per column per warp) instead of costing another pass over dY.
+template <bool COLSUM>
 __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows,
-                                                                int cols, __nv_bfloat16* __restrict__ out, long long ldout) {
+                                                                int cols, __nv_bfloat16* __restrict__ out, long long ldout,
+                                                                float* __restrict__ colsum) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cg = lane & 3, rg = lane >> 2;
   const int r0 = blockIdx.y * 64 + rg * 8;
   const int c0 = blockIdx.x * 256 + warp * 32 + cg * 8;
-  if (r0 >= rows || c0 >= cols) return;
-  if (r0 + 8 <= rows && c0 + 8 <= cols) {
+  float cs[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) cs[c] = 0.f;
+  if (r0 >= rows || c0 >= cols) {
+    if (!COLSUM) return;
+  } else if (r0 + 8 <= rows && c0 + 8 <= cols) {
     uint4 v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const uint4*>(in + (long long)(r0 + j) * ldin + c0);
+    if (COLSUM) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[j]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 f = __bfloat1622float2(h[q]);
+          cs[2 * q] += f.x;
+          cs[2 * q + 1] += f.y;
+        }
+      }
+    }
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
       const uint32_t sel = (c & 1) ? 0x7632u : 0x5410u;      // high / low bf16 of both source registers
@@ -146,7 +167,24 @@ __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bflo
     }
   } else {
     for (int j = 0; j < 8 && r0 + j < rows; ++j)
-      for (int c = 0; c < 8 && c0 + c < cols; ++c) out[(long long)(c0 + c) * ldout + r0 + j] = in[(long long)(r0 + j) * ldin + c0 + c];
+      for (int c = 0; c < 8 && c0 + c < cols; ++c) {
+        const __nv_bfloat16 e = in[(long long)(r0 + j) * ldin + c0 + c];
+        out[(long long)(c0 + c) * ldout + r0 + j] = e;
+        if (COLSUM) cs[c] += __bfloat162float(e);
+      }
+  }
+  if (COLSUM) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {                       // lanes with equal (lane & 3) hold the same 8 columns
+      cs[c] += __shfl_xor_sync(0xffffffffu, cs[c], 4);
+      cs[c] += __shfl_xor_sync(0xffffffffu, cs[c], 8);
+      cs[c] += __shfl_xor_sync(0xffffffffu, cs[c], 16);
+    }
+    if (rg == 0) {
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if (c0 + c < cols) atomicAdd(colsum + c0 + c, cs[c]);
+    }
   }
 }
 

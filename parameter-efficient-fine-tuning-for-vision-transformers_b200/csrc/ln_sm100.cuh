@@ -99,7 +99,7 @@ ln_fwd_kernel(const InT* __restrict__ x, long long ldx, const float* __restrict_
 
 // dx = rstd * (gamma*dy - mean(gamma*dy) - xhat * mean(gamma*dy*xhat)),  xhat = (x - mean) * rstd
 // g_out = (g_in ? g_in : 0) + dx.   With kParamGrad: dgamma += sum_rows dy*xhat, dbeta += sum_rows dy (fp32 atomics,
-// one per column per CTA after an in-CTA shared-memory reduction).
+// one per column per CTA after an in-CTA shared-memory reduction; the host launches this variant with few CTAs).
 template <int NV, typename DyT, typename XT, typename GT, bool kParamGrad>
 __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__ x, long long ldx,
@@ -159,14 +159,19 @@ ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__
     __shared__ float red[2][NV * 128];
     for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) (&red[0][0])[c] = 0.f;
     __syncthreads();
+    // warp by warp, each lane adding into its own columns: no shared-memory float atomics (they compile to CAS loops)
+    for (int wsel = 0; wsel < warps_per_block; ++wsel) {
+      if (warp == wsel) {
 #pragma unroll
-    for (int i = 0; i < NV; ++i)
+        for (int i = 0; i < NV; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        atomicAdd(&red[0][(i * 32 + lane) * 4 + j], ag[i][j]);
-        atomicAdd(&red[1][(i * 32 + lane) * 4 + j], ab[i][j]);
+          for (int j = 0; j < 4; ++j) {
+            red[0][(i * 32 + lane) * 4 + j] += ag[i][j];
+            red[1][(i * 32 + lane) * 4 + j] += ab[i][j];
+          }
       }
-    __syncthreads();
+      __syncthreads();
+    }
     for (int c = threadIdx.x; c < D; c += blockDim.x) {
       atomicAdd(dgamma + c, red[0][c]);
       atomicAdd(dbeta + c, red[1][c]);

@@ -444,9 +444,12 @@ class VitEngine:
 
 
     # ------------------------------------------------------------------ backward, full fine-tuning mode
-    def _dw(self, w, dY, X, out):
-        """out[N, K] (fp32) = dY[M, N]^T X[M, K]: both operands transposed to K-major, then the tcgen05 GEMM."""
+    def _dw(self, w, dY, X, out, colsum=None):
+        """out[N, K] (fp32) = dY[M, N]^T X[M, K]: both operands transposed to K-major, then the tcgen05 GEMM (split-K).
+        `colsum` (fp32 [N], zeroed) additionally receives the column sums of dY — the bias gradient — from the same
+        transpose pass (bf16 mode only)."""
         if self.cfg.precision == "fp32":           # verification mode: one fp32 token reduction (any shape)
+            assert colsum is None
             out.zero_()
             ops.tn_reduce(dY, X, out)
             return
@@ -454,9 +457,27 @@ class VitEngine:
         Mp = (M + 7) // 8 * 8                      # contraction length padded to the GEMM's K granularity; the pad
         a = w.tA[:dY.shape[1]]                     # columns [M, Mp) of tA / tB are never written and stay zero
         b = w.tB[:X.shape[1]]
-        ops.transpose(dY, a[:, :M])
+        ops.transpose(dY, a[:, :M], colsum=colsum)
         ops.transpose(X, b[:, :M])
         ops.gemm(a[:, :Mp], b[:, :Mp], out, epilogue=ops.EPI_STORE_F32)
+
+    def _dw_db(self, w, G, want, kw, kb, dY, X):
+        """Weight and bias gradient of one linear layer (either may be unwanted): G[kw] = dY^T X, G[kb] = colsum(dY)."""
+        ww, wb = want(kw), want(kb)
+        N, K = dY.shape[1], X.shape[1]
+        fused = ww and wb and self.cfg.precision != "fp32"
+        bsum = None
+        if wb and fused:
+            bsum = torch.zeros(N, device=self.dev, dtype=torch.float32)
+            G[kb] = bsum
+        elif wb:
+            c16 = torch.zeros(16, N, device=self.dev, dtype=torch.float32)
+            ops.tn_reduce(w.ones[:dY.shape[0]], dY, c16)
+            G[kb] = c16[0]
+        if ww:
+            dw = torch.empty(N, K, device=self.dev, dtype=torch.float32)
+            self._dw(w, dY, X, dw, colsum=bsum)
+            G[kw] = dw
 
     def backward_full(self, dfeat, need=None, generation=None):
         """dL/d(every tower tensor) -> {reference key: fp32 grad}.  Only for cfg.train_all (no adapters): the Fastfood /
@@ -503,46 +524,18 @@ class VitEngine:
         for i in reversed(range(dep)):
             k = lambda n: keys[n].format(i=i)
             # MLP
-            if want(k("fc2_b")):
-                c16 = z(16, D)
-                ops.tn_reduce(w.ones, w.gb, c16)
-                G[k("fc2_b")] = c16[0]
-            if want(k("fc2_w")):
-                dw2 = e(D, F)
-                self._dw(w, w.gb, w.act_l[i], dw2)
-                G[k("fc2_w")] = dw2
+            self._dw_db(w, G, want, k("fc2_w"), k("fc2_b"), w.gb, w.act_l[i])
             ops.gemm(w.gb, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
-            if want(k("fc1_b")):
-                c16 = z(16, F)
-                ops.tn_reduce(w.ones, w.dh, c16)
-                G[k("fc1_b")] = c16[0]
-            if want(k("fc1_w")):
-                dw1 = e(F, D)
-                self._dw(w, w.dh, w.xn2_l[i], dw1)
-                G[k("fc1_w")] = dw1
+            self._dw_db(w, G, want, k("fc1_w"), k("fc1_b"), w.dh, w.xn2_l[i])
             ops.gemm(w.dh, self.wfc1T[i], w.dxn)
             dg, db = z(D), z(D)
             ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb, dg, db)
             G[k("ln2_w")], G[k("ln2_b")] = dg, db
             # attention
-            if want(k("proj_b")):
-                c16 = z(16, D)
-                ops.tn_reduce(w.ones, w.gb, c16)
-                G[k("proj_b")] = c16[0]
-            if want(k("proj_w")):
-                dwp = e(D, D)
-                self._dw(w, w.gb, w.o[i], dwp)
-                G[k("proj_w")] = dwp
+            self._dw_db(w, G, want, k("proj_w"), k("proj_b"), w.gb, w.o[i])
             ops.gemm(w.gb, self.wprojT[i], w.d_o)
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
-            if want(k("qkv_b")):
-                c16 = z(16, 3 * D)
-                ops.tn_reduce(w.ones, dq, c16)
-                G[k("qkv_b")] = c16[0]
-            if want(k("qkv_w")):
-                dwq = e(3 * D, D)
-                self._dw(w, dq, w.xn1[i][:, :D], dwq)
-                G[k("qkv_w")] = dwq
+            self._dw_db(w, G, want, k("qkv_w"), k("qkv_b"), dq, w.xn1[i][:, :D])
             ops.gemm(dq, self.wqkvT[i][:, :3 * D], w.dxn)
             dg, db = z(D), z(D)
             ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb, dg, db)

@@ -227,14 +227,20 @@ def clip_delta(qkv, delta, B, H, L, mult_q, mult_v, backward=False):
     return delta if backward else qkv
 
 
-def transpose(x, out):
-    """out[c, r] = x[r, c] (bf16)."""
+def transpose(x, out, colsum=None):
+    """out[c, r] = x[r, c] (bf16); with `colsum` (fp32 [cols], caller-zeroed) also colsum[c] += sum_r x[r, c]."""
     px, ldx = _mat(x, torch.bfloat16, "x")
     po, ldo = _mat(out, torch.bfloat16, "out")
     R, Cc = x.shape
     if tuple(out.shape) != (Cc, R):
         raise ValueError("transpose: out must be [cols, rows]")
-    _lib.check(_lib.load().peft_transpose_bf16(px, ldx, R, Cc, po, ldo, _stream()), "peft_transpose_bf16")
+    if colsum is None:
+        _lib.check(_lib.load().peft_transpose_bf16(px, ldx, R, Cc, po, ldo, _stream()), "peft_transpose_bf16")
+    else:
+        if colsum.dtype != torch.float32 or colsum.numel() != Cc or not colsum.is_contiguous() or not colsum.is_cuda:
+            raise ValueError("transpose: colsum must be a contiguous CUDA fp32 vector of length cols")
+        _lib.check(_lib.load().peft_transpose_colsum_bf16(px, ldx, R, Cc, po, ldo, colsum.data_ptr(), _stream()),
+                   "peft_transpose_colsum_bf16")
     return out
 
 

@@ -268,3 +268,18 @@ def test_gemm_splitk_f32(ops, M, N, K):
     ref = a.double() @ b.double().T
     err = float((out.double() - ref).norm() / ref.norm())
     assert err < 1e-5, err
+
+
+@pytest.mark.parametrize("R,C", [(12800, 768), (1001, 264), (64, 8), (70, 520)])
+def test_transpose_colsum(ops, R, C):
+    """Transpose with the fused column sum (bias gradient riding on the dY transpose): data movement bit-exact, sums
+    within fp32 round-off of a float64 reference, accumulated ON TOP of the caller's buffer."""
+    g = torch.Generator().manual_seed(R * 7 + C)
+    Rp = (R + 7) // 8 * 8
+    x = torch.randn(R, C, generator=g).to(torch.bfloat16).cuda()
+    dst = torch.zeros(C, Rp, device="cuda", dtype=torch.bfloat16)
+    cs = torch.full((C,), 2.0, device="cuda")
+    ops.transpose(x, dst[:, :R], colsum=cs)
+    assert torch.equal(dst[:, :R], x.t())
+    ref = 2.0 + x.double().sum(0)
+    assert float((cs.double() - ref).abs().max()) < 1e-3 * (1.0 + float(ref.abs().max())) * 1e-2
