@@ -182,6 +182,8 @@ if __name__ == "__main__":
         bench_phm_fold()
     if what in ("fastfood", "all"):
         bench_fastfood()
+    if what == "prof_c5":     # one pass of the full-mode (C5) products and transposes, for ncu
+        bench_gemm_dw(12800, iters=1)
     if what == "gemm_c5":
         bench_gemm(12800)
         bench_gemm_dw(12800)
