@@ -177,16 +177,30 @@ class VitEngine:
             for i in range(dep):
                 sd[keys["qkv_b"].format(i=i)] = torch.zeros(3 * D)
         L = {k: [g(v.format(i=i)) for i in range(dep)] for k, v in keys.items()}
-        # forward operands: W [N, K]; the qkv weight carries rp extra K columns for scale*Up (refreshed every step)
-        self.wqkv = torch.zeros(dep, 3 * D, D + rp, device=dev, dtype=bf)
-        self.wqkvT = torch.zeros(dep, D, 3 * D + rp, device=dev, dtype=bf)   # [W^T | Dn^T] for dX
-        for i in range(dep):
-            self.wqkv[i, :, :D] = L["qkv_w"][i]
-            self.wqkvT[i, :, :3 * D] = L["qkv_w"][i].T
-        stack = lambda k, t=False: torch.stack([(w.T if t else w) for w in L[k]]).to(bf).contiguous()
-        self.wproj, self.wprojT = stack("proj_w"), stack("proj_w", True)
-        self.wfc1, self.wfc1T = stack("fc1_w"), stack("fc1_w", True)
-        self.wfc2, self.wfc2T = stack("fc2_w"), stack("fc2_w", True)
+        # forward operands: W [N, K]; the qkv weight carries rp extra K columns for scale*Up (refreshed every step).
+        # The buffers persist across calls (full mode re-packs every step: theta changes with V) and each layer is
+        # converted straight into its slot: one fp32 -> bf16 pass, then W^T from the bf16 copy with the transpose kernel.
+        def slot(name, *shape):
+            t = getattr(self, name, None)
+            if t is None or tuple(t.shape) != shape or t.dtype != bf or t.device != dev:
+                t = torch.zeros(*shape, device=dev, dtype=bf)
+                setattr(self, name, t)
+            return t
+
+        def pack(wname, tname, key, n_pad=0, k_pad=0):
+            N, K = L[key][0].shape
+            W, WT = slot(wname, dep, N, K + k_pad), slot(tname, dep, K, N + n_pad)
+            for i in range(dep):
+                W[i, :, :K].copy_(L[key][i])
+                if bf == torch.bfloat16 and N % 8 == 0 and K % 8 == 0:
+                    ops.transpose(W[i, :, :K], WT[i, :, :N])
+                else:
+                    WT[i, :, :N].copy_(L[key][i].T)
+
+        pack("wqkv", "wqkvT", "qkv_w", n_pad=rp, k_pad=rp)      # [W | Up^T-columns], [W^T | Dn^T] for dX
+        pack("wproj", "wprojT", "proj_w")
+        pack("wfc1", "wfc1T", "fc1_w")
+        pack("wfc2", "wfc2T", "fc2_w")
         vec = lambda k: torch.stack(L[k]).contiguous()
         self.bqkv, self.bproj, self.bfc1, self.bfc2 = vec("qkv_b"), vec("proj_b"), vec("fc1_b"), vec("fc2_b")
         self.ln1_w, self.ln1_b, self.ln2_w, self.ln2_b = vec("ln1_w"), vec("ln1_b"), vec("ln2_w"), vec("ln2_b")
