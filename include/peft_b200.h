@@ -123,6 +123,12 @@ int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int 
  * weight-gradient product dW = dY^T X (contraction over tokens) into the K-major form peft_gemm_bf16 consumes; only the
  * full-fine-tuning / intrinsic-dimension mode computes dW (FL/intrinsic/fastfood.py:61-77 makes every wrapped weight
  * a function of V, so autograd needs dL/dW for all of them). */
+/* out[M, N] (fp32, contiguous) = x[T, M]^T y[T, N]: the weight-gradient product dW = dY^T X taken straight from the
+ * token-major activations (MN-major tcgen05 operands, no transposes), contraction over the T tokens split across tiles
+ * when the output is small.  replaces: the autograd dW of nn.Linear in full fine-tuning / Fastfood mode
+ * (FL/intrinsic/fastfood.py:61-77 makes every weight a function of V). */
+int peft_gemm_tn_bf16(const void* x, long long ldx, const void* y, long long ldy, int M, int N, int T, float* out,
+                      long long ldo, void* stream);
 int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream);
 /* same, and colsum[c] += sum_r in[r, c] (fp32, caller zeroes it) in the same pass: the bias gradient of a linear layer
  * (autograd of `+ bias`, FS/kadaptation.py:72-78,133,236) is the column sum of the dY being transposed for its dW product.

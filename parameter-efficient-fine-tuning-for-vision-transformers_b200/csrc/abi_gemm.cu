@@ -46,10 +46,10 @@ static std::atomic<int>& gemm_algo() {
   return a;
 }
 
-template <int EPI>
+template <int EPI, bool TN = false>
 static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& to2,
                         const CUtensorMap& tx, const GemmParams& p, cudaStream_t stream) {
-  auto kern = gemm2_bf16_tcgen05_kernel<EPI>;
+  auto kern = gemm2_bf16_tcgen05_kernel<EPI, TN>;
   static bool configured = false;
   if (!configured) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2SmemBytes));
@@ -206,4 +206,27 @@ extern "C" int peft_set_gemm_algo(int algo) {
   PEFT_REQUIRE(algo >= 0 && algo <= 2, "peft_set_gemm_algo: algo must be 0 (auto), 1 (1-CTA) or 2 (2-CTA)");
   gemm_algo().store(algo);
   return 0;
+}
+
+extern "C" int peft_gemm_tn_bf16(const void* x, long long ldx, const void* y, long long ldy, int M, int N, int T, float* out,
+                                 long long ldo, void* stream) {
+  PEFT_REQUIRE(M > 0 && N > 0 && T > 0 && x && y && out, "peft_gemm_tn_bf16: bad shape M=%d N=%d T=%d or null operand", M, N, T);
+  PEFT_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 && ldx % 8 == 0 &&
+                   ldy % 8 == 0 && ldx >= M && ldy >= N,
+               "peft_gemm_tn_bf16: operands must be 16-byte aligned with pitches %% 8 == 0");
+  PEFT_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0 && ldo == N && N % 4 == 0,
+               "peft_gemm_tn_bf16: out must be contiguous [M, N], 16-byte aligned, N %% 4 == 0");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = T; p.bias = nullptr; p.out = out; p.ldo = ldo;
+  p.ksplit = pick_ksplit(M, N, T, EPI_STORE_F32, nullptr, ldo);
+  if (p.ksplit > 1) PEFT_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)M * N * sizeof(float), s));
+  CUtensorMap ta, tb, to;
+  int rc = make_tmap_2d(&ta, x, false, (unsigned long long)T, (unsigned long long)M, (unsigned long long)ldx, 64, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tb, y, false, (unsigned long long)T, (unsigned long long)N, (unsigned long long)ldy, 64, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d(&to, out, true, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldo, 32, 32);
+  if (rc) return rc;
+  return launch_gemm2<EPI_STORE_F32, true>(ta, tb, to, to, to, p, s);
 }

@@ -77,6 +77,16 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* 
                "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
                : "memory");
 }
+// MN-major SWIZZLE_128B operand, 128 MN-elements wide: two 64-wide atoms columns 8 KB apart (LBO), 8-row groups 1 KB apart (SBO)
+__device__ __forceinline__ uint64_t make_smem_desc_sw128_mn128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(8192 >> 4) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
 // same box, but added into global memory (fp32 tensor map): split-K partial sums
 __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, const void* smem_src, int c0, int c1) {
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
@@ -185,7 +195,12 @@ struct EpiTraits {
 // 16-byte chunk j of row `lane` inside a 128B-swizzled [32 x 128 B] slot (the layout TMA expects for SWIZZLE_128B).
 __device__ __forceinline__ uint32_t slot_off(int lane, int j) { return (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4)); }
 
-template <int EPI>
+// TN = true: both operands are given token-major — A(m, k) = a[k, m], B(n, k) = b[k, n] (the weight-gradient product
+// dW = dY^T X straight from the row-major activations, no transposes).  The smem tiles are then MN-major: a TMA box is
+// [64 k-rows x 64 MN-elements (128 B)], two boxes side by side give the 128-wide operand half of a CTA (second box at
+// +8 KB = the descriptor's leading-dimension byte offset), 8-row groups stay 1 KB apart, and one UMMA K-step (16 rows)
+// advances the start address by 2 KB.  p.K is the number of tokens; rows past it are zero-filled by TMA.
+template <int EPI, bool TN = false>
 __global__ void __launch_bounds__(kG2Threads, 1)
 gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
@@ -259,8 +274,15 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           uint8_t* sb = sa + kBM * kBK * 2;
           const uint32_t bar = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
           if (leader) ptx::mbar_expect_tx(&full_bar[stage], 2 * kG2StageBytes);
-          ptx::tma_load_2d_2sm(sa, &tmap_a, bar, kb * kBK, row_a);
-          ptx::tma_load_2d_2sm(sb, &tmap_b, bar, kb * kBK, row_b);
+          if constexpr (TN) {
+            ptx::tma_load_2d_2sm(sa, &tmap_a, bar, row_a, kb * kBK);
+            ptx::tma_load_2d_2sm(sa + 8192, &tmap_a, bar, row_a + 64, kb * kBK);
+            ptx::tma_load_2d_2sm(sb, &tmap_b, bar, row_b, kb * kBK);
+            ptx::tma_load_2d_2sm(sb + 8192, &tmap_b, bar, row_b + 64, kb * kBK);
+          } else {
+            ptx::tma_load_2d_2sm(sa, &tmap_a, bar, kb * kBK, row_a);
+            ptx::tma_load_2d_2sm(sb, &tmap_b, bar, kb * kBK, row_b);
+          }
           if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -268,7 +290,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   } else if (warp == 1) {
     // ===================== MMA issuer (one lane of the leader CTA) =====================
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kG2BN);
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kG2BN) | (TN ? ((1u << 15) | (1u << 16)) : 0u);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -282,12 +304,13 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           ptx::mbar_wait_cluster(&full_bar[stage], phase);
           ptx::tcgen05_fence_after();
           const uint32_t sa = ptx::smem_u32(tiles + stage * kG2StageBytes);
-          const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
-          const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + kBM * kBK * 2);
+          const uint64_t adesc = TN ? ptx::make_smem_desc_sw128_mn128(sa) : ptx::make_smem_desc_sw128(sa);
+          const uint64_t bdesc = TN ? ptx::make_smem_desc_sw128_mn128(sa + kBM * kBK * 2) : ptx::make_smem_desc_sw128(sa + kBM * kBK * 2);
           const int krem = p.K - kb * kBK;
           const int ksteps = krem >= kBK ? (kBK / 16) : ((krem + 15) / 16);
+          constexpr uint64_t kstep = TN ? (2048 >> 4) : (32 >> 4);     // descriptor start-address units per UMMA K-step
           for (int k = 0; k < ksteps; ++k)
-            ptx::umma_bf16_2sm(tmem_d, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k), idesc,
+            ptx::umma_bf16_2sm(tmem_d, adesc + kstep * static_cast<uint64_t>(k), bdesc + kstep * static_cast<uint64_t>(k), idesc,
                                (kb != kb0 || k != 0) ? 1u : 0u);
           ptx::umma_commit_2sm(&empty_bar[stage], 3);       // frees this smem slot in both CTAs
           if (++stage == kG2Stages) { stage = 0; phase ^= 1; }

@@ -227,6 +227,19 @@ def clip_delta(qkv, delta, B, H, L, mult_q, mult_v, backward=False):
     return delta if backward else qkv
 
 
+def gemm_tn(x, y, out):
+    """out[M, N] (fp32, contiguous) = x[T, M]^T @ y[T, N] (bf16 token-major operands), see peft_gemm_tn_bf16."""
+    px, ldx = _mat(x, torch.bfloat16, "x")
+    py, ldy = _mat(y, torch.bfloat16, "y")
+    po, ldo = _mat(out, torch.float32, "out")
+    T, M = x.shape
+    N = y.shape[1]
+    if y.shape[0] != T or tuple(out.shape) != (M, N):
+        raise ValueError(f"gemm_tn: shape mismatch {tuple(x.shape)}^T x {tuple(y.shape)} -> {tuple(out.shape)}")
+    _lib.check(_lib.load().peft_gemm_tn_bf16(px, ldx, py, ldy, M, N, T, po, ldo, _stream()), "peft_gemm_tn_bf16")
+    return out
+
+
 def transpose(x, out, colsum=None):
     """out[c, r] = x[r, c] (bf16); with `colsum` (fp32 [cols], caller-zeroed) also colsum[c] += sum_r x[r, c]."""
     px, ldx = _mat(x, torch.bfloat16, "x")

@@ -101,6 +101,10 @@ def bench_gemm_dw(tokens=12800, iters=20):
         out = torch.empty(No, Ki, device="cuda")
         t = timeit(lambda: ops.gemm(a, b, out, epilogue=ops.EPI_STORE_F32), iters=iters, warm=2)
         print(f"gemm {name:10s} M={No} N={Ki} K={tokens}: {t:7.1f} us  {2.0 * No * Ki * tokens / t / 1e6:7.1f} TFLOP/s", flush=True)
+        dy = torch.randn(tokens, No, device="cuda").to(torch.bfloat16)
+        xx = torch.randn(tokens, Ki, device="cuda").to(torch.bfloat16)
+        t = timeit(lambda: ops.gemm_tn(dy, xx, out), iters=iters, warm=2)
+        print(f"gemm_tn {name:7s} M={No} N={Ki} T={tokens}: {t:7.1f} us  {2.0 * No * Ki * tokens / t / 1e6:7.1f} TFLOP/s  (no transposes)", flush=True)
         x = torch.randn(tokens, No, device="cuda").to(torch.bfloat16)
         xt = torch.empty(No, tokens, device="cuda", dtype=torch.bfloat16)
         t = timeit(lambda: ops.transpose(x, xt), iters=iters, warm=2)

@@ -283,3 +283,18 @@ def test_transpose_colsum(ops, R, C):
     assert torch.equal(dst[:, :R], x.t())
     ref = 2.0 + x.double().sum(0)
     assert float((cs.double() - ref).abs().max()) < 1e-3 * (1.0 + float(ref.abs().max())) * 1e-2
+
+
+@pytest.mark.parametrize("T,M,N", [(256, 256, 256), (12800, 768, 768), (12800, 2304, 768), (4096, 768, 3072), (1000, 300, 588),
+                                   (50, 128, 264)])
+def test_gemm_tn(ops, T, M, N):
+    """dW-style product straight from token-major operands (MN-major tcgen05 descriptors): out = x^T y."""
+    g = torch.Generator().manual_seed(T + M + N)
+    ld_x, ld_y = (M + 15) // 8 * 8, (N + 23) // 8 * 8     # column slices of wider buffers (pitch % 8 == 0)
+    x = torch.randn(T, ld_x, generator=g).to(torch.bfloat16).cuda()[:, :M]
+    y = torch.randn(T, ld_y, generator=g).to(torch.bfloat16).cuda()[:, :N]
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm_tn(x, y, out)
+    ref = x.double().t() @ y.double()
+    err = float((out.double() - ref).norm() / ref.norm())
+    assert err < 1e-5, err
