@@ -135,6 +135,8 @@ int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void
  * Requires 16-byte aligned operands and pitches % 8 == 0. */
 int peft_transpose_colsum_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, float* colsum,
                                void* stream);
+/* colsum[c] += sum_r in[r, c] only (bf16 in, fp32 out, caller zeroes): the bias gradient when dW comes from peft_gemm_tn_bf16 */
+int peft_colsum_bf16(const void* in, long long ldin, int rows, int cols, float* colsum, void* stream);
 
 /* Large-n KAdaptation fold (the committed phm_dim = n = D, K = P = 1).
  * replaces: kronecker_product_einsum_batched(phm_rule, W).sum(0) of matvec_product (FS/kadaptation.py:81-115) for BOTH

@@ -34,6 +34,7 @@ SIGNATURES = {
     "peft_tn_reduce": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp],
     "peft_clip_delta": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, _vp],
     "peft_gemm_tn_bf16": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _c_ll, _vp],
+    "peft_colsum_bf16": [_vp, _c_ll, C.c_int, C.c_int, _vp, _vp],
     "peft_transpose_bf16": [_vp, _c_ll, C.c_int, C.c_int, _vp, _c_ll, _vp],
     "peft_transpose_colsum_bf16": [_vp, _c_ll, C.c_int, C.c_int, _vp, _c_ll, _vp, _vp],
     "peft_phm_fold": [_vp, _vp, _vp, C.c_int, C.c_int, _vp],

@@ -102,6 +102,16 @@ extern "C" int peft_transpose_colsum_bf16(const void* in, long long ldin, int ro
   return transpose_impl(in, ldin, rows, cols, out, ldout, colsum, stream);
 }
 
+extern "C" int peft_colsum_bf16(const void* in, long long ldin, int rows, int cols, float* colsum, void* stream) {
+  PEFT_REQUIRE(rows > 0 && cols > 0 && in && colsum, "peft_colsum_bf16: bad shape rows=%d cols=%d or null operand", rows, cols);
+  PEFT_REQUIRE(al16(in) && ldin % 8 == 0 && ldin >= cols, "peft_colsum_bf16: needs a 16-byte aligned operand and pitch %% 8 == 0");
+  dim3 grid((cols + 255) / 256, (rows + 63) / 64);
+  transpose_bf16_vec_kernel<true, false><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      (const __nv_bfloat16*)in, ldin, rows, cols, nullptr, 0, colsum);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, int backward, void* stream) {
   PEFT_REQUIRE(n > 0 && n <= kFoldMaxN && ((long long)n * n) % 4 == 0, "peft_phm_fold: need n <= %d and n*n %% 4 == 0 (n=%d)", kFoldMaxN, n);
   PEFT_REQUIRE(rule && s_or_dH && out && al16(rule) && al16(s_or_dH) && al16(out), "peft_phm_fold: null or unaligned pointer");

@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16
 // COLSUM: also colsum[c] += sum_r in[r, c] (fp32): the bias gradient of a linear layer is the column sum of the same dY
 // that is being transposed for the weight-gradient product, so it rides along (8 lanes share a column group: three
 // shuffles, then one global atomic per column per warp) instead of costing another pass over dY.
-template <bool COLSUM>
+// STORE = false: column sums only (nothing is written to `out`): the bias gradient when dW comes from peft_gemm_tn_bf16.
+template <bool COLSUM, bool STORE = true>
 __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows,
                                                                 int cols, __nv_bfloat16* __restrict__ out, long long ldout,
                                                                 float* __restrict__ colsum) {
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bflo
       }
     }
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
+    for (int c = 0; c < (STORE ? 8 : 0); ++c) {
       const uint32_t sel = (c & 1) ? 0x7632u : 0x5410u;      // high / low bf16 of both source registers
       uint32_t w[4];
 #pragma unroll
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bflo
     for (int j = 0; j < 8 && r0 + j < rows; ++j)
       for (int c = 0; c < 8 && c0 + c < cols; ++c) {
         const __nv_bfloat16 e = in[(long long)(r0 + j) * ldin + c0 + c];
-        out[(long long)(c0 + c) * ldout + r0 + j] = e;
+        if (STORE) out[(long long)(c0 + c) * ldout + r0 + j] = e;
         if (COLSUM) cs[c] += __bfloat162float(e);
       }
   }

@@ -134,10 +134,6 @@ class _Workspace:
             self.dz = e(M, m)
             self.gh = e(M, D, dt=f32)                                # gradient w.r.t. h (fp32) and its bf16 copy
             self.ghb = self.gh if fp32_mode else e(M, D)
-        if cfg.rank > 128 and not cfg.train_all and not fp32_mode:
-            Mp = (M + 7) // 8 * 8
-            self.tA = torch.zeros(rp, Mp, device=dev, dtype=bf)           # p^T      [r', tokens]
-            self.tB = torch.zeros(3 * D, Mp, device=dev, dtype=bf)        # dqkv^T   [3D, tokens]
         if cfg.train_all:
             # everything a weight-gradient product needs that the PEFT path recomputes or never keeps
             self.xn2_l = [e(M, D) for _ in range(dep)]
@@ -145,9 +141,6 @@ class _Workspace:
             self.ones = torch.zeros(M, 16, device=dev, dtype=bf)
             self.ones[:, 0] = 1.0
             Mp = (M + 7) // 8 * 8
-            if not fp32_mode:
-                self.tA = torch.zeros(max(F, 3 * D), Mp, device=dev, dtype=bf)            # dY^T  [N, tokens]
-                self.tB = torch.zeros(max(F, D, cfg.patch_k), Mp, device=dev, dtype=bf)   # X^T   [K, tokens]
             self.mean_pre = e(M, dt=f32); self.rstd_pre = e(M, dt=f32)
         self.generation = 0
 
@@ -398,10 +391,11 @@ class VitEngine:
             if m:
                 # bottleneck adapter backward; g = dL/dx_{i+1} is also dL/dx1 (residual) and part of dL/dh
                 z, ones = w.zext[i][:, :m], w.zext[i][:, m:m + 16]
-                ops.tn_reduce(ones, w.gb, dbu16[i])                                   # dbu  = colsum(g)       (row 0)
+                bsum = (lambda x, o16: ops.tn_reduce(ones, x, o16)) if cfg.precision == "fp32" else (lambda x, o16: ops.colsum(x, o16[0]))
+                bsum(w.gb, dbu16[i])                                                  # dbu  = colsum(g)       (row 0)
                 ops.tn_reduce(z, w.gb, dWuT[i])                                       # dWu^T = z^T g
                 ops.gemm(w.gb, self.wuT_bf[i], w.dz, epilogue=bn_dact, aux=(z if cfg.bn_act == "relu" else w.upre[i]))
-                ops.tn_reduce(ones, w.dz, dbd16[i])                                   # dbd  = colsum(dz)
+                bsum(w.dz, dbd16[i])                                                  # dbd  = colsum(dz)
                 ops.tn_reduce(w.dz, w.za[i], dWd[i])                                  # dWd  = dz^T LN_a(h)
                 ops.gemm(w.dz, self.wdT_bf[i], w.dxn)                                 # dza  = dz Wd
                 ops.layernorm_bwd_f32g(w.dxn, w.hf[i], w.mean_a[i], w.rstd_a[i], self.lga[i], w.g, w.gh, w.ghb, dlg[i], dlb[i])
@@ -458,39 +452,28 @@ class VitEngine:
 
 
     # ------------------------------------------------------------------ backward, full fine-tuning mode
-    def _dw(self, w, dY, X, out, colsum=None):
-        """out[N, K] (fp32) = dY[M, N]^T X[M, K]: both operands transposed to K-major, then the tcgen05 GEMM (split-K).
-        `colsum` (fp32 [N], zeroed) additionally receives the column sums of dY — the bias gradient — from the same
-        transpose pass (bf16 mode only)."""
+    def _dw(self, w, dY, X, out):
+        """out[N, K] (fp32) = dY[M, N]^T X[M, K], contraction over the M tokens: one tcgen05 product straight from the
+        token-major activations (MN-major operands, split-K when the output has few tiles) — no transposes."""
         if self.cfg.precision == "fp32":           # verification mode: one fp32 token reduction (any shape)
-            assert colsum is None
             out.zero_()
             ops.tn_reduce(dY, X, out)
             return
-        M = dY.shape[0]
-        Mp = (M + 7) // 8 * 8                      # contraction length padded to the GEMM's K granularity; the pad
-        a = w.tA[:dY.shape[1]]                     # columns [M, Mp) of tA / tB are never written and stay zero
-        b = w.tB[:X.shape[1]]
-        ops.transpose(dY, a[:, :M], colsum=colsum)
-        ops.transpose(X, b[:, :M])
-        ops.gemm(a[:, :Mp], b[:, :Mp], out, epilogue=ops.EPI_STORE_F32)
+        ops.gemm_tn(dY, X, out)
 
     def _dw_db(self, w, G, want, kw, kb, dY, X):
         """Weight and bias gradient of one linear layer (either may be unwanted): G[kw] = dY^T X, G[kb] = colsum(dY)."""
-        ww, wb = want(kw), want(kb)
         N, K = dY.shape[1], X.shape[1]
-        fused = ww and wb and self.cfg.precision != "fp32"
-        bsum = None
-        if wb and fused:
-            bsum = torch.zeros(N, device=self.dev, dtype=torch.float32)
-            G[kb] = bsum
-        elif wb:
-            c16 = torch.zeros(16, N, device=self.dev, dtype=torch.float32)
-            ops.tn_reduce(w.ones[:dY.shape[0]], dY, c16)
-            G[kb] = c16[0]
-        if ww:
+        if want(kb):
+            if self.cfg.precision == "fp32":
+                c16 = torch.zeros(16, N, device=self.dev, dtype=torch.float32)
+                ops.tn_reduce(w.ones[:dY.shape[0]], dY, c16)
+                G[kb] = c16[0]
+            else:
+                G[kb] = ops.colsum(dY, torch.zeros(N, device=self.dev, dtype=torch.float32))
+        if want(kw):
             dw = torch.empty(N, K, device=self.dev, dtype=torch.float32)
-            self._dw(w, dY, X, dw, colsum=bsum)
+            self._dw(w, dY, X, dw)
             G[kw] = dw
 
     def backward_full(self, dfeat, need=None, generation=None):

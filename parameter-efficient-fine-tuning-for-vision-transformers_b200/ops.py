@@ -240,6 +240,15 @@ def gemm_tn(x, y, out):
     return out
 
 
+def colsum(x, out):
+    """out[c] += sum_r x[r, c] (bf16 x, fp32 out [cols], caller-zeroed)."""
+    px, ldx = _mat(x, torch.bfloat16, "x")
+    if out.dtype != torch.float32 or out.numel() != x.shape[1] or not out.is_contiguous() or not out.is_cuda:
+        raise ValueError("colsum: out must be a contiguous CUDA fp32 vector of length cols")
+    _lib.check(_lib.load().peft_colsum_bf16(px, ldx, x.shape[0], x.shape[1], out.data_ptr(), _stream()), "peft_colsum_bf16")
+    return out
+
+
 def transpose(x, out, colsum=None):
     """out[c, r] = x[r, c] (bf16); with `colsum` (fp32 [cols], caller-zeroed) also colsum[c] += sum_r x[r, c]."""
     px, ldx = _mat(x, torch.bfloat16, "x")

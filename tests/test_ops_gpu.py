@@ -298,3 +298,13 @@ def test_gemm_tn(ops, T, M, N):
     ref = x.double().t() @ y.double()
     err = float((out.double() - ref).norm() / ref.norm())
     assert err < 1e-5, err
+
+
+@pytest.mark.parametrize("R,C", [(12800, 2304), (1001, 264), (70, 64)])
+def test_colsum(ops, R, C):
+    g = torch.Generator().manual_seed(R + 3 * C)
+    x = torch.randn(R, C + 8, generator=g).to(torch.bfloat16).cuda()[:, :C]
+    out = torch.full((C,), -1.0, device="cuda")
+    ops.colsum(x, out)
+    ref = -1.0 + x.double().sum(0)
+    assert float((out.double() - ref).abs().max()) < 1e-4 * (1.0 + float(ref.abs().max()))
