@@ -196,7 +196,9 @@ def run_reference(args, rank):
     steps = max(1, args.steps)
     base, dt, b = cpu_reference_rate(args.config, budget_s=150.0, steps=steps, warmup=max(1, min(args.warmup, 2)))
     line = {
-        "impl": "reference", "metric": "fine-tune step images/s (fwd+bwd+SGD)", "value": base["value"], "unit": "images/s",
+        "impl": "reference",
+        "metric": "fine-tune step images/s (fwd+bwd) ViT-B/16 KAdaptation" if args.config == "C3" else f"fine-tune step images/s (fwd+bwd) {c['desc']}",
+        "value": base["value"], "unit": "images/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.config}: {c['desc']}, 224x224 synthetic, CPU sample batch {b}"},
