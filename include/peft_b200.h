@@ -119,24 +119,25 @@ int peft_tn_reduce(const void* x, long long ldx, int I, const void* y, long long
 int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long long ldd, int B, int H, int L, float mult_q,
                     float mult_v, int backward, void* stream);
 
-/* out[c, r] = in[r, c], bf16 [rows, cols] (pitch ldin) -> [cols, rows] (pitch ldout).  Brings the operands of a
- * weight-gradient product dW = dY^T X (contraction over tokens) into the K-major form peft_gemm_bf16 consumes; only the
- * full-fine-tuning / intrinsic-dimension mode computes dW (FL/intrinsic/fastfood.py:61-77 makes every wrapped weight
- * a function of V, so autograd needs dL/dW for all of them). */
 /* out[M, N] (fp32, contiguous) = x[T, M]^T y[T, N]: the weight-gradient product dW = dY^T X taken straight from the
  * token-major activations (MN-major tcgen05 operands, no transposes), contraction over the T tokens split across tiles
- * when the output is small.  replaces: the autograd dW of nn.Linear in full fine-tuning / Fastfood mode
- * (FL/intrinsic/fastfood.py:61-77 makes every weight a function of V). */
+ * when the output is small.  x, y: bf16, 16-byte aligned, pitches % 8 == 0; N % 4 == 0.
+ * replaces: the autograd dW of nn.Linear in full fine-tuning / Fastfood mode (FL/intrinsic/fastfood.py:61-77 makes every
+ * wrapped weight a function of V, so autograd needs dL/dW for all of them; FL/tools/finetune_{bias,attention}.py select
+ * subsets), and dUp^T of the dense large-n KAdaptation update. */
 int peft_gemm_tn_bf16(const void* x, long long ldx, const void* y, long long ldy, int M, int N, int T, float* out,
                       long long ldo, void* stream);
+/* colsum[c] += sum_r in[r, c] (bf16 in, fp32 out, caller zeroes it): the bias gradient of a linear layer (autograd of
+ * `+ bias`, FS/kadaptation.py:72-78,133,236) is the column sum of its dY.  16-byte aligned operand, pitch % 8 == 0. */
+int peft_colsum_bf16(const void* in, long long ldin, int rows, int cols, float* colsum, void* stream);
+
+/* out[c, r] = in[r, c], bf16 [rows, cols] (pitch ldin) -> [cols, rows] (pitch ldout).  Used by the per-step weight
+ * re-pack of the full mode (W^T operands of the dX products from the bf16 copy of W); 16-byte aligned operands with
+ * pitches % 8 == 0 take the shared-memory-free fast path, anything else (even pitches, 4-byte alignment) a tiled one. */
 int peft_transpose_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, void* stream);
-/* same, and colsum[c] += sum_r in[r, c] (fp32, caller zeroes it) in the same pass: the bias gradient of a linear layer
- * (autograd of `+ bias`, FS/kadaptation.py:72-78,133,236) is the column sum of the dY being transposed for its dW product.
- * Requires 16-byte aligned operands and pitches % 8 == 0. */
+/* same, and colsum[c] += sum_r in[r, c] in the same pass (fast path only) */
 int peft_transpose_colsum_bf16(const void* in, long long ldin, int rows, int cols, void* out, long long ldout, float* colsum,
                                void* stream);
-/* colsum[c] += sum_r in[r, c] only (bf16 in, fp32 out, caller zeroes): the bias gradient when dW comes from peft_gemm_tn_bf16 */
-int peft_colsum_bf16(const void* in, long long ldin, int rows, int cols, float* colsum, void* stream);
 
 /* Large-n KAdaptation fold (the committed phm_dim = n = D, K = P = 1).
  * replaces: kronecker_product_einsum_batched(phm_rule, W).sum(0) of matvec_product (FS/kadaptation.py:81-115) for BOTH

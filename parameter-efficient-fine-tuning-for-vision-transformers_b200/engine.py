@@ -139,8 +139,7 @@ class _Workspace:
             self.xn2_l = [e(M, D) for _ in range(dep)]
             self.act_l = [e(M, F) for _ in range(dep)]
             self.ones = torch.zeros(M, 16, device=dev, dtype=bf)
-            self.ones[:, 0] = 1.0
-            Mp = (M + 7) // 8 * 8
+            self.ones[:, 0] = 1.0                  # bias sums of the fp32 mode and the (tiny) patch-embed bias
             self.mean_pre = e(M, dt=f32); self.rstd_pre = e(M, dt=f32)
         self.generation = 0
 
