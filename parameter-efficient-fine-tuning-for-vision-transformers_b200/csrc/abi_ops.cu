@@ -1,4 +1,5 @@
 // C-ABI: LayerNorm, attention, patch-embedding helpers and the skinny adapter-gradient reductions.
+#include <stdlib.h>
 #include "common.cuh"
 #include "ln_sm100.cuh"
 #include "attention_sm100.cuh"
@@ -12,8 +13,14 @@ namespace {
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 inline int ln_grid(int M, bool param_grad = false) {
   const int blocks = (M + 7) / 8;
-  // with dgamma / dbeta every CTA ends in 2*D global atomics: keep the grid at 4 CTAs per SM so that they stay negligible
-  const int cap = sm_count() * (param_grad ? 4 : 8);
+  // with dgamma / dbeta every CTA ends in a shared-memory reduction and 2*D global atomics: measured on B200 the kernel
+  // gets monotonically faster with fewer CTAs (M = 12800: 62.6 us at 8 per SM, 48.1 at 4, 35.9 at 1), so one per SM
+  static int pg_cap = 0;                       // tuning knob (tests/bench_ops.py ln_pg): PEFT_LN_PG_CAP CTAs per SM
+  if (pg_cap == 0) {
+    const char* e = getenv("PEFT_LN_PG_CAP");
+    pg_cap = (e && atoi(e) > 0) ? atoi(e) : 1;
+  }
+  const int cap = sm_count() * (param_grad ? pg_cap : 8);
   return blocks < cap ? (blocks > 0 ? blocks : 1) : cap;
 }
 }  // namespace

@@ -61,6 +61,21 @@ def bench_ln(M=50432, D=768):
     print(f"ln_bwd  M={M} D={D}: {t:7.1f} us  {(M * D * 10) / t / 1e3:7.1f} GB/s")
 
 
+def bench_ln_pg(D=768):
+    """LayerNorm backward with dgamma / dbeta (full mode, Houlsby adapter norm) at the C5 and C4 row counts."""
+    for M in (12800, 32896):
+        x = torch.randn(M, D, device="cuda")
+        dy = torch.randn(M, D, device="cuda").to(torch.bfloat16)
+        g = torch.randn(M, D, device="cuda")
+        gb = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+        gamma = torch.randn(D, device="cuda")
+        mean, rstd = x.mean(1), 1.0 / x.std(1)
+        dg, db = torch.zeros(D, device="cuda"), torch.zeros(D, device="cuda")
+        t = timeit(lambda: ops.layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g, g, gb, dg, db), iters=20, warm=3)
+        byt = M * D * (2 + 4 + 4 + 4 + 2)
+        print(f"ln_bwd +dgamma/dbeta M={M} D={D}: {t:7.1f} us  {byt / t / 1e3:7.1f} GB/s", flush=True)
+
+
 def bench_reduce(M=50432):
     wide = torch.randn(M, 800, device="cuda").to(torch.bfloat16)
     y = torch.randn(M, 2304, device="cuda").to(torch.bfloat16)
@@ -186,6 +201,8 @@ if __name__ == "__main__":
         bench_phm_fold()
     if what in ("fastfood", "all"):
         bench_fastfood()
+    if what == "ln_pg":
+        bench_ln_pg()
     if what == "prof_c5":     # one pass of the full-mode (C5) products and transposes, for ncu
         bench_gemm_dw(12800, iters=1)
     if what == "gemm_c5":
