@@ -105,9 +105,12 @@ extern "C" int peft_transpose_colsum_bf16(const void* in, long long ldin, int ro
 extern "C" int peft_colsum_bf16(const void* in, long long ldin, int rows, int cols, float* colsum, void* stream) {
   PEFT_REQUIRE(rows > 0 && cols > 0 && in && colsum, "peft_colsum_bf16: bad shape rows=%d cols=%d or null operand", rows, cols);
   PEFT_REQUIRE(al16(in) && ldin % 8 == 0 && ldin >= cols, "peft_colsum_bf16: needs a 16-byte aligned operand and pitch %% 8 == 0");
-  dim3 grid((cols + 255) / 256, (rows + 63) / 64);
-  transpose_bf16_vec_kernel<true, false><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      (const __nv_bfloat16*)in, ldin, rows, cols, nullptr, 0, colsum);
+  const int colblocks = (cols + 255) / 256, nrb = (rows + 63) / 64;
+  int gy = (2 * sm_count() + colblocks - 1) / colblocks;       // ~2 CTAs per SM in total; each walks nrb / gy row blocks
+  if (gy > nrb) gy = nrb;
+  if (gy < 1) gy = 1;
+  colsum_bf16_kernel<<<dim3(colblocks, gy), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows,
+                                                                                             cols, colsum);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

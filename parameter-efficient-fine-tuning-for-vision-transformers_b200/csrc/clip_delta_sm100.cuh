@@ -189,6 +189,56 @@ __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bflo
   }
 }
 
+// colsum[c] += sum_r in[r, c]: streaming column sums (bias gradients).  Same lane layout as the transpose (4 column groups
+// x 8 row groups per warp, 16-byte loads, 64-byte runs per row); each CTA walks several 64-row blocks and accumulates in
+// registers, so a column receives gridDim.y atomics in total instead of one per 64 rows (the one-block-per-CTA version
+// spent more time serialising same-address atomics in L2 than streaming: 23 us for [12800, 3072]).
+__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows, int cols,
+                                                         float* __restrict__ colsum) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cg = lane & 3, rg = lane >> 2;
+  const int c0 = blockIdx.x * 256 + warp * 32 + cg * 8;
+  float cs[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) cs[c] = 0.f;
+  if (c0 < cols) {
+    const bool full = c0 + 8 <= cols;
+    for (int rb = blockIdx.y; rb * 64 < rows; rb += gridDim.y) {
+      const int r0 = rb * 64 + rg * 8;
+      if (full) {
+        uint4 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          v[j] = (r0 + j < rows) ? *reinterpret_cast<const uint4*>(in + (long long)(r0 + j) * ldin + c0) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[j]);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 f = __bfloat1622float2(h[q]);
+            cs[2 * q] += f.x;
+            cs[2 * q + 1] += f.y;
+          }
+        }
+      } else {
+        for (int j = 0; j < 8 && r0 + j < rows; ++j)
+          for (int c = 0; c < 8 && c0 + c < cols; ++c) cs[c] += __bfloat162float(in[(long long)(r0 + j) * ldin + c0 + c]);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {                         // lanes with equal (lane & 3) hold the same 8 columns
+    cs[c] += __shfl_xor_sync(0xffffffffu, cs[c], 4);
+    cs[c] += __shfl_xor_sync(0xffffffffu, cs[c], 8);
+    cs[c] += __shfl_xor_sync(0xffffffffu, cs[c], 16);
+  }
+  if (rg == 0) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+      if (c0 + c < cols) atomicAdd(colsum + c0 + c, cs[c]);
+  }
+}
+
 }  // namespace peft
 
 // ---- large-n KAdaptation "fold" (the committed phm_dim = n = D, K = P = 1) --------------------------

@@ -120,6 +120,9 @@ def bench_gemm_dw(tokens=12800, iters=20):
         xx = torch.randn(tokens, Ki, device="cuda").to(torch.bfloat16)
         t = timeit(lambda: ops.gemm_tn(dy, xx, out), iters=iters, warm=2)
         print(f"gemm_tn {name:7s} M={No} N={Ki} T={tokens}: {t:7.1f} us  {2.0 * No * Ki * tokens / t / 1e6:7.1f} TFLOP/s  (no transposes)", flush=True)
+        cs = torch.zeros(No, device="cuda")
+        t = timeit(lambda: ops.colsum(dy, cs), iters=iters, warm=2)
+        print(f"     colsum [{tokens} x {No}] bf16: {t:7.1f} us  {2.0 * tokens * No / t / 1e3:7.1f} GB/s", flush=True)
         x = torch.randn(tokens, No, device="cuda").to(torch.bfloat16)
         xt = torch.empty(No, tokens, device="cuda", dtype=torch.bfloat16)
         t = timeit(lambda: ops.transpose(x, xt), iters=iters, warm=2)
