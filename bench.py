@@ -6,7 +6,8 @@
 
 Workload (BASELINE.json configs[2], the one the metric is quoted on): ViT-B/16 (L=197, D=768, 12 layers) +
 KAdaptation (Kronecker q/v update, n=4, rank 1) + BatchNorm/Linear head, synthetic 224x224 images, bf16 compute,
-per-GPU batch 256 (weak scaling: global batch = 256 x N), SGD momentum 0.9.  One "step" = zero grads -> forward ->
+GLOBAL batch 256 split over the N ranks (per-GPU batch 256 / N: the fixed-global-batch partitioning of SURVEY 8e,
+"scaling": "strong"; `--scaling weak` keeps per-GPU batch 256), SGD momentum 0.9.  One "step" = zero grads -> forward ->
 CrossEntropy -> backward -> adapter-gradient all-reduce (N > 1) -> optimizer step.
 Rank 0 prints ONE JSON line.  `--impl reference` times the CPU oracle (the restatement of the reference's PyTorch path,
 pinned to the reference by tests/golden) on the host cores for the same model/metric on a bounded sample.
@@ -26,9 +27,34 @@ if ROOT not in sys.path:
 import torch  # noqa: E402
 
 # FLOP per image, fwd + bwd with a frozen backbone (dX only, no dW): SURVEY.md §8d / BASELINE.md §3
-# mean DRAM bytes (read + write) per GEMM launch of one C3 layer (8 products: qkv, proj, fc1, fc2 and their dX) from the
-# `ncu --set full` capture profiles/r01_ncu_top_kernels_v2_summary.txt (263 / 350 / 643 / 628 / 666 / 378 / 115 / 300 MB)
-NCU_GEMM_TRAFFIC_BYTES = {"C3": 417.9e6, "C2": 417.9e6}
+
+
+def kernel_source_hash():
+    """sha256 over the CUDA sources: ties a committed ncu traffic figure to the build it was captured from."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    csrc = os.path.join(ROOT, "parameter-efficient-fine-tuning-for-vision-transformers_b200", "csrc")
+    for f in sorted(glob.glob(os.path.join(csrc, "*.cu")) + glob.glob(os.path.join(csrc, "*.cuh"))):
+        if os.path.basename(f).startswith("test_"):
+            continue
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_gemm_traffic(cfg_name):
+    """Mean DRAM bytes (read + write) per GEMM launch from the committed `ncu --set full` summary of THIS build
+    (profiles/gemm_traffic.json, written by tools/ncu_traffic.py); None when the sources changed since the capture."""
+    p = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+    except Exception:
+        return None
+    if d.get("source_hash") != kernel_source_hash():
+        return None
+    return d.get("bytes_per_launch", {}).get(cfg_name)
 
 CONFIGS = {
     "C3": dict(model="ViT-B/16", dialect="timm", adapter="kron", patch=16, width=768, depth=12, heads=12, batch=256,
@@ -215,7 +241,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--config", default="C3", choices=list(CONFIGS))
-    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the config's 256)")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: global batch / N, or the global batch with --scaling weak)")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default): the config's GLOBAL batch is fixed and split over the ranks (SURVEY 8e); weak: per-GPU batch fixed")
     ap.add_argument("--depth", type=int, default=0, help="debug only: override depth (marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -248,7 +276,14 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     c = dict(CONFIGS[args.config])
     depth = args.depth or c["depth"]
-    Bpg = args.batch or c["batch"]
+    if args.batch:
+        Bpg = args.batch
+    elif args.scaling == "strong":
+        if c["batch"] % world:
+            raise SystemExit(f"global batch {c['batch']} is not divisible by {world} ranks")
+        Bpg = c["batch"] // world
+    else:
+        Bpg = c["batch"]
     cfg = vit_cfg(c, depth)
     sd = synth.make_state_dict(cfg, seed=0, grad_test=False)
     names = set(synth.trainable_names(cfg, sd, train_rule=c.get("phm_dim", 4) <= 64))   # few_shot freezes phm_rule ('W' filter)
@@ -415,20 +450,24 @@ def main():
         line = {
             "metric": "fine-tune step images/s (fwd+bwd) ViT-B/16 KAdaptation" if args.config == "C3" else f"fine-tune step images/s (fwd+bwd) {c['desc']}",
             "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": f"{args.config}: {c['desc']}, 224x224 synthetic images, per-GPU batch {Bpg}, SGD m=0.9, 10-class BN+Linear head",
+            "config": {"workload": f"{args.config}: {c['desc']}, 224x224 synthetic images, global batch {Bpg * world} = {world} x {Bpg} per GPU, SGD m=0.9, 10-class BN+Linear head",
                        "global_batch": Bpg * world, "seq_len": cfg.seq, "parallelism": f"dp{world}",
                        "l2": "per-step working set (GBs of saved activations) >> 126 MB L2; no flush needed",
                        "allreduce_bytes": bucket.nbytes},
-            "step_frac_of_bf16_peak": value * flop_img / (pk["tflops"] * 1e12 * world),
+            "step_frac_of_bf16_peak": value * flop_img / (pk["tflops_burst"] * 1e12 * world),
+            "step_frac_of_bf16_peak_sustained": value * flop_img / (pk["tflops"] * 1e12 * world),
+            "peaks": {"bf16_tflops_burst": pk["tflops_burst"], "bf16_tflops_sustained": pk["tflops"], "hbm_gbs": pk["hbm"],
+                      "source": "MEASURED_PEAKS.json" if pk["src"] == "measured" else "fallback (B200_PROFILING.md)"},
             "launch_mode": "cuda-graph replay (1 graph launch per step)" if graphed is not None else "eager",
             "eager_ms_per_step": eager_ms / args.steps,
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel (all dense products of the step)",
                          "achieved": gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None, "peak": pk["tflops"],
                          "unit": "TFLOP/s", "frac": (gemm_flops / (gemm_ms * 1e-3) / 1e12) / pk["tflops"] if gemm_ms > 0 else None,
-                         "traffic": NCU_GEMM_TRAFFIC_BYTES.get(args.config) if depth == c["depth"] and Bpg == c["batch"] else None,
-                         "traffic_unit": "bytes per launch (mean over the 8 products of a layer, ncu dram read+write)",
+                         "traffic": ncu_gemm_traffic(args.config) if depth == c["depth"] and Bpg == c["batch"] else None,
+                         "traffic_unit": "bytes per launch (mean over the 8 products of a layer, ncu dram read+write; profiles/gemm_traffic.json, null if the kernels changed since the capture)",
+                         "frac_of_burst": (gemm_flops / (gemm_ms * 1e-3) / 1e12) / pk["tflops_burst"] if gemm_ms > 0 else None,
                          "peak_source": pk["src"] + " bf16_tflops_sustained",
                          "gemm_share_of_step": gemm_ms / eager_ms if eager_ms > 0 else None, "gemm_launches": len(gemm_events),
                          "measured_in": "eager instrumented pass of the same K steps (CUDA events per launch)"},
@@ -445,15 +484,27 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             base, _, _ = cpu_reference_rate(args.config, budget_s=20.0, steps=2, warmup=1)
             line["cpu_baseline"] = base
+            if args.config != "C1":
+                # SURVEY 8d's stated CPU configuration, exactly: BASELINE.json configs[0] (CLIP ViT-B/32 + KAdaptation, batch 32)
+                c1, _, _ = cpu_reference_rate("C1", budget_s=12.0, steps=2, warmup=1)
+                line["cpu_baseline_c1"] = c1
         print(json.dumps(line), flush=True)
     if world > 1:
-        # A process group whose NCCL kernels were captured into a live CUDA graph can hang in destroy_process_group();
-        # every rank has its result by now, so synchronise, flush and leave without the teardown.
+        # NCCL kernels captured into a live CUDA graph keep the communicator busy: destroy the graph first, then the
+        # group.  A watchdog leaves the process if the teardown still blocks (every rank has its result by now).
         dist.barrier()
         torch.cuda.synchronize()
         sys.stdout.flush()
         sys.stderr.flush()
-        os._exit(0)
+        wd = threading.Timer(20.0, lambda: os._exit(0))
+        wd.daemon = True
+        wd.start()
+        if graphed is not None:
+            graphed.release()
+        del graphed
+        torch.cuda.synchronize()
+        dist.destroy_process_group()
+        wd.cancel()
 
 
 if __name__ == "__main__":

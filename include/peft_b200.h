@@ -40,6 +40,10 @@ int peft_version(void);
 void peft_last_error(char* buf, size_t n);
 /* number of kernels this library has launched since load (all threads) — bench.py reports it as gpu_launches */
 unsigned long long peft_launch_count(void);
+/* launches per kernel family since load — 0: 1-CTA tcgen05 GEMM, 1: 2-CTA (cta_group::2) GEMM, 2: tcgen05 attention forward,
+ * 3: tcgen05 attention backward, 4: legacy mma.sync attention, 5: token-major (TN) tcgen05 GEMM, 6: 4-CTA multicast GEMM.
+ * Test hook: the parity suite asserts that the benchmarked shapes really ran on the kernels the bench times. */
+unsigned long long peft_kernel_count(int kind);
 /* tuning / test knob: which tensor-core GEMM kernel peft_gemm_bf16 uses — 0 = automatic (2-CTA cta_group::2 kernel when
  * the problem fills the 74 SM pairs, else the 1-CTA kernel), 1 = always 1-CTA, 2 = always 2-CTA. */
 int peft_set_gemm_algo(int algo);

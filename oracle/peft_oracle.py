@@ -78,11 +78,23 @@ def gelu_new(x):
 # --------------------------------------------------------------------------------------------------------------------
 # bottleneck adapters
 # --------------------------------------------------------------------------------------------------------------------
+# Test hooks for the discontinuous ReLU gate of the Houlsby bottleneck (tests/houlsby_gate.py).  GATE_RECORD, when a dict,
+# receives {adapter prefix: pre-activation}; GATE_OVERRIDE maps an adapter prefix to a 0/1 mask that REPLACES the sign
+# test of the ReLU (z = pre * mask): the oracle then differentiates the linear region the CUDA engine selected, which
+# separates "the kernels compute the wrong gradient" from "a pre-activation within bf16 noise of 0 flipped its gate".
+GATE_RECORD = None
+GATE_OVERRIDE = {}
+
+
 def houlsby_adapter(h, sd, pfx, eps=1e-5):
     """FS/adapter_model.py:204-295 — up(relu(down(LN(h)))) + h  (residual_input = h at the call site :330-334)."""
     D = h.shape[-1]
     z = F.layer_norm(h, (D,), sd[pfx + "adapter_norm_before.weight"], sd[pfx + "adapter_norm_before.bias"], eps)
-    z = F.relu(F.linear(z, sd[pfx + "adapter_down.1.weight"], sd[pfx + "adapter_down.1.bias"]))
+    pre = F.linear(z, sd[pfx + "adapter_down.1.weight"], sd[pfx + "adapter_down.1.bias"])
+    if GATE_RECORD is not None:
+        GATE_RECORD[pfx] = pre.detach()
+    gate = GATE_OVERRIDE.get(pfx)
+    z = F.relu(pre) if gate is None else pre * gate.to(pre.dtype)
     z = F.linear(z, sd[pfx + "adapter_up.weight"], sd[pfx + "adapter_up.bias"])
     return z + h
 

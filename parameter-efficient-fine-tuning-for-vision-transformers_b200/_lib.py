@@ -20,6 +20,7 @@ SIGNATURES = {
     "peft_version": [],
     "peft_last_error": [C.c_char_p, C.c_size_t],
     "peft_launch_count": [],
+    "peft_kernel_count": [C.c_int],
     "peft_set_gemm_algo": [C.c_int],
     "peft_set_attention_algo": [C.c_int],
     "peft_gemm_bf16": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
@@ -50,7 +51,7 @@ SIGNATURES = {
     "peft_assemble_tokens_f32": [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp],
     "peft_add_f32": [_vp, _vp, _vp, _c_ll, _vp],
 }
-_RESTYPES = {"peft_last_error": None, "peft_launch_count": C.c_ulonglong}
+_RESTYPES = {"peft_last_error": None, "peft_launch_count": C.c_ulonglong, "peft_kernel_count": C.c_ulonglong}
 
 _lib = None
 
@@ -87,3 +88,11 @@ def check(rc: int, what: str = ""):
 
 def launch_count() -> int:
     return int(load().peft_launch_count())
+
+
+KIND_GEMM_1CTA, KIND_GEMM_2CTA, KIND_ATTN_TC_FWD, KIND_ATTN_TC_BWD, KIND_ATTN_LEGACY, KIND_GEMM_TN, KIND_GEMM_4CTA = range(7)
+
+
+def kernel_count(kind: int) -> int:
+    """Launches of one kernel family since load (see peft_kernel_count)."""
+    return int(load().peft_kernel_count(kind))

@@ -10,3 +10,6 @@ extern "C" void peft_last_error(char* buf, size_t n) {
 }
 
 extern "C" unsigned long long peft_launch_count(void) { return peft::launch_counter().load(); }
+extern "C" unsigned long long peft_kernel_count(int kind) {
+  return (kind >= 0 && kind < peft::KIND_COUNT) ? peft::kind_counter(kind).load() : 0ull;
+}

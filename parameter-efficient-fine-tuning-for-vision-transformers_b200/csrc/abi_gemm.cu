@@ -1,4 +1,5 @@
 // C-ABI: peft_gemm_bf16 — host launcher of the tcgen05/TMA GEMM (gemm_sm100.cuh).
+#include <stdlib.h>
 #include "common.cuh"
 #include "gemm_sm100.cuh"
 #include "gemm2_sm100.cuh"
@@ -17,7 +18,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
   const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
   kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, p);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_GEMM_1CTA);
   return 0;
 }
 
@@ -71,7 +72,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   PEFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, to, to2, tx, p));
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(TN ? KIND_GEMM_TN : KIND_GEMM_2CTA);
   return 0;
 }
 
@@ -168,6 +169,10 @@ extern "C" int peft_gemm_bf16(const void* a, long long lda, const void* b, long 
   p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
   p.aux = aux; p.ldaux = ldaux;
   p.ksplit = pick_ksplit(M, N, K, epilogue, bias, ldo);
+  {
+    static const int dbg = [] { const char* e = getenv("PEFT_GEMM_DBG"); return e ? atoi(e) : 0; }();
+    p.dbg = dbg;
+  }
   if (p.ksplit > 1) PEFT_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)M * N * sizeof(float), s));
   if (p.ksplit > 1 || use_gemm2(M, N)) {
     CUtensorMap ta, tb, to, to2, tx;

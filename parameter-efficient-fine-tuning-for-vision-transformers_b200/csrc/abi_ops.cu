@@ -182,7 +182,7 @@ static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long
   p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
   const int grid = B * H < sm_count() ? B * H : sm_count();
   kern<<<grid, kA2Threads, C::kSmemBytes, s>>>(tq, tkv, to, p);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_FWD);
   return 0;
 }
 
@@ -209,7 +209,7 @@ extern "C" int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, lon
   }
   dim3 grid((L + 63) / 64, B * H);
   attn_fwd_kernel<<<grid, kAttnThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(p, Lp);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_LEGACY);
   return 0;
 }
 
@@ -239,9 +239,9 @@ static int launch_attn2_bwd(const void* qkv, long long ldqkv, const void* o, lon
   p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale;
   const int grid = B * H < sm_count() ? B * H : sm_count();
   kdq<<<grid, kA2Threads, C::kDqSmemBytes, s>>>(t128, tchunk, tdo128, to128, tout, p);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
   kdkv<<<grid, kA2Threads, C::kDkvSmemBytes, s>>>(t128, tchunk, tdochunk, tout, p);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
   return 0;
 }
 
@@ -279,9 +279,9 @@ extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   dim3 grid((L + 63) / 64, B * H);
   attn_bwd_dq_kernel<<<grid, kAttnThreads, smem_dq, s>>>(p, Lp);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_LEGACY);
   attn_bwd_dkv_kernel<<<grid, kAttnThreads, smem_dkv, s>>>(p, Lp);
-  PEFT_LAUNCH_CHECK();
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_LEGACY);
   return 0;
 }
 

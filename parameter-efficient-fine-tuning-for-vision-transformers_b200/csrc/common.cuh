@@ -29,6 +29,13 @@ inline std::atomic<unsigned long long>& launch_counter() {
   static std::atomic<unsigned long long> c{0};
   return c;
 }
+// per-kernel-family launch counters (peft_kernel_count): lets the tests assert WHICH kernel served a call
+enum KernelKind { KIND_GEMM_1CTA = 0, KIND_GEMM_2CTA = 1, KIND_ATTN_TC_FWD = 2, KIND_ATTN_TC_BWD = 3, KIND_ATTN_LEGACY = 4,
+                  KIND_GEMM_TN = 5, KIND_GEMM_4CTA = 6, KIND_COUNT = 16 };
+inline std::atomic<unsigned long long>& kind_counter(int k) {
+  static std::atomic<unsigned long long> c[KIND_COUNT];
+  return c[(k >= 0 && k < KIND_COUNT) ? k : KIND_COUNT - 1];
+}
 
 #define PEFT_CUDA_CHECK(expr)                                                                         \
   do {                                                                                                \
@@ -43,6 +50,12 @@ inline std::atomic<unsigned long long>& launch_counter() {
     cudaError_t _e = cudaGetLastError();                                                              \
     if (_e != cudaSuccess)                                                                            \
       return ::peft::fail(PEFT_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define PEFT_LAUNCH_CHECK_KIND(kind)                                                                  \
+  do {                                                                                                \
+    ::peft::kind_counter(kind).fetch_add(1, std::memory_order_relaxed);                               \
+    PEFT_LAUNCH_CHECK();                                                                              \
   } while (0)
 
 #define PEFT_REQUIRE(cond, ...)                                   \

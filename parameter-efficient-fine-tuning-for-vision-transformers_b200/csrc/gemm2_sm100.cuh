@@ -265,14 +265,20 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         const int ks = tile % ksplit, mn = tile / ksplit;
         const int mp = mn / num_n, n_blk = mn % num_n;
-        const int row_a = mp * 2 * kBM + (int)cta_rank * kBM;
-        const int row_b = n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
+        const int row_a = (p.dbg & 2) ? (int)cta_rank * kBM : mp * 2 * kBM + (int)cta_rank * kBM;
+        const int row_b = (p.dbg & 2) ? (int)cta_rank * (kG2BN / 2) : n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
         const int kb0 = ks * kb_per, kb1 = min(num_kb, kb0 + kb_per);
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = tiles + stage * kG2StageBytes;
           uint8_t* sb = sa + kBM * kBK * 2;
           const uint32_t bar = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+          if (!TN && (p.dbg & 1)) {          // diagnostic: A operand only (the B slot keeps stale data)
+            if (leader) ptx::mbar_expect_tx(&full_bar[stage], kG2StageBytes);
+            ptx::tma_load_2d_2sm(sa, &tmap_a, bar, kb * kBK, row_a);
+            if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           if (leader) ptx::mbar_expect_tx(&full_bar[stage], 2 * kG2StageBytes);
           if constexpr (TN) {
             ptx::tma_load_2d_2sm(sa, &tmap_a, bar, row_a, kb * kBK);
@@ -379,6 +385,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive_cluster(acc ? tmem_empty_remote1 : tmem_empty_remote0);
         }
+        if constexpr (!T::kAux) { if (p.dbg & 4) continue; }   // diagnostic: drain TMEM only
         if (p.bias != nullptr) {
           if (colu + T::kUnitCols <= p.N) {
 #pragma unroll

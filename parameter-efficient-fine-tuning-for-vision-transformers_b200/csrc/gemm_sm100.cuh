@@ -48,6 +48,8 @@ struct GemmParams {
   long long ldaux;
   int ksplit = 1;     // 2-CTA kernel, EPI_STORE_F32 only: K is cut into `ksplit` ranges that are separate tiles and are
                       // summed into a pre-zeroed `out` by TMA reduce-add (weight-gradient products: small output, long K)
+  int dbg = 0;        // diagnostics (env PEFT_GEMM_DBG, results are WRONG when set; bench_ops.py gemm_dbg): bit 0 = no B-operand
+                      // loads, bit 1 = every tile loads the operands of tile 0, bit 2 = epilogue only drains TMEM (no math / stores)
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }

@@ -60,6 +60,13 @@ class GraphedTrainStep:
         self.optimizer.step()
         return loss.detach(), out.detach()
 
+    def release(self):
+        """Destroys the captured graph (and the NCCL kernels recorded in it).  Call before
+        torch.distributed.destroy_process_group(): a live graph holding collective nodes can block the teardown."""
+        if self.graph is not None:
+            self.graph.reset()
+            self.graph = None
+
     def __call__(self, images=None, labels=None):
         """Copies the batch into the static buffers (device-to-device or host-to-device, on the current stream) and replays
         the step.  Returns the static loss tensor (read it with .item() only when needed)."""

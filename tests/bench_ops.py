@@ -87,11 +87,13 @@ def bench_reduce(M=50432):
     print(f"tn_reduce I=32 J=768  M={M}: {t:7.1f} us  {(M * (768 + 32) * 2) / t / 1e3:7.1f} GB/s")
 
 
-def bench_gemm(M=50432, iters=20):
+def bench_gemm(M=50432, iters=20, only=None):
     cases = [("qkv   [x|p][W|Up]^T+b", 2304, 800, ops.EPI_STORE), ("proj  +resid f32", 768, 768, ops.EPI_RESID_F32),
              ("fc1   +GELU (h, act)", 3072, 768, ops.EPI_GELU), ("fc2   +resid f32", 768, 3072, ops.EPI_RESID_F32),
              ("fc2^T *gelu'(h)", 3072, 768, ops.EPI_DGELU), ("fc1^T store", 768, 3072, ops.EPI_STORE),
              ("proj^T store", 768, 768, ops.EPI_STORE), ("qkv^T [dqkv|dp]", 768, 2336, ops.EPI_STORE)]
+    if only is not None:
+        cases = [cases[i] for i in only]
     for name, N, K, epi in cases:
         a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
         b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
@@ -184,6 +186,14 @@ if __name__ == "__main__":
         bench_attn(256, 12, 50)
     if what in ("gemm", "all"):
         bench_gemm()
+    if what == "small":       # per-GPU batch 32 of the fixed-global-batch split at 8 GPUs (M = 6304)
+        bench_gemm(6304, iters=50)
+        bench_attn(32, 12, 197)
+        bench_ln(6304)
+        bench_reduce(6304)
+    if what == "gemm_dbg":    # PEFT_GEMM_DBG diagnostics: plain-store and GELU products only (results are wrong by design)
+        print("PEFT_GEMM_DBG =", os.environ.get("PEFT_GEMM_DBG", "0"), flush=True)
+        bench_gemm(50432, iters=10, only=(0, 2, 5))
     if what == "prof":      # one pass of each hot kernel, for ncu captures
         bench_gemm(iters=1)
         B, H, L = 256, 12, 197

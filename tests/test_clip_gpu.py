@@ -91,23 +91,24 @@ def test_backbone_grads_match_oracle(name):
     sd_o = {k: v.clone() for k, v in sd.items()}
     for k in names:
         sd_o[k].requires_grad_(True)
-    rfeat = O.visual_forward(images, sd_o, cfg)
-    if names:
-        (rfeat * w).sum().backward()
+    if cfg.adapter == "houlsby":
+        # discontinuous ReLU gate: see tests/houlsby_gate.py — gate decisions may differ from the oracle's only within bf16
+        # noise of 0, and on the linear region the engine selected every tensor (adapter_down included) holds 2e-2
+        from tests.houlsby_gate import engine_gate_masks, oracle_with_engine_gates
+        rfeat, st = oracle_with_engine_gates(images, sd_o, cfg, engine_gate_masks(model, cfg, B), w)
+        assert st["flip_frac"] < 1e-2 and st["worst_flip_sigma"] < 0.1, st
+    else:
+        rfeat = O.visual_forward(images, sd_o, cfg)
+        if names:
+            (rfeat * w).sum().backward()
     assert rel(feat, rfeat) < TOL, rel(feat, rfeat)
-    gated = (lambda k: cfg.adapter == "houlsby" and ("adapter_down" in k or "adapter_norm_before" in k))
     if names:
-        # north_star gate on the adapter gradient taken as one vector.  Houlsby: tensors BELOW the discontinuous ReLU gate
-        # (adapter_down, its LayerNorm) are excluded here and bounded per tensor below — a pre-activation within the bf16
-        # forward error of 0 flips its derivative (see tests/test_model_gpu.py); tensors above the gate keep 2e-2.
-        cat = [k for k in names if not gated(k)]
-        got = torch.cat([params[k].grad.detach().float().cpu().reshape(-1) for k in cat])
-        ref = torch.cat([sd_o[k].grad.detach().float().reshape(-1) for k in cat])
+        got = torch.cat([params[k].grad.detach().float().cpu().reshape(-1) for k in names])
+        ref = torch.cat([sd_o[k].grad.detach().float().reshape(-1) for k in names])
         assert rel(got, ref) < TOL, rel(got, ref)
     per_tensor = TOL if cfg.depth <= 3 else 1.5 * TOL
     for k in names:
-        bound = 0.12 if gated(k) else per_tensor
-        assert rel(params[k].grad, sd_o[k].grad) < bound, (k, rel(params[k].grad, sd_o[k].grad))
+        assert rel(params[k].grad, sd_o[k].grad) < per_tensor, (k, rel(params[k].grad, sd_o[k].grad))
 
 
 def test_build_model_from_state_dict():

@@ -114,25 +114,27 @@ def test_backbone_grads_match_oracle(name):
     sd_o = {k: v.clone() for k, v in sd.items()}
     for k in names:
         sd_o[k].requires_grad_(True)
-    rfeat = O.visual_forward(images, sd_o, cfg)
-    if names:
-        (rfeat * w).sum().backward()
+    if cfg.adapter == "houlsby":
+        # discontinuous ReLU gate: the oracle differentiates the linear region the engine selected, and the gate decisions
+        # themselves may differ only within bf16 noise of 0 (tests/houlsby_gate.py) — then EVERY tensor holds 2e-2
+        from tests.houlsby_gate import engine_gate_masks, oracle_with_engine_gates
+        rfeat, st = oracle_with_engine_gates(images, sd_o, cfg, engine_gate_masks(model, cfg, B), w)
+        assert st["flip_frac"] < 1e-2 and st["worst_flip_sigma"] < 0.1, st
+    else:
+        rfeat = O.visual_forward(images, sd_o, cfg)
+        if names:
+            (rfeat * w).sum().backward()
     assert rel(feat, rfeat) < TOL
-    # Houlsby's ReLU gate is discontinuous: a pre-activation within the bf16 forward error of 0 (~0.3 % of the units) flips
-    # its derivative between 0 and 1, which moves the gradient of everything BELOW the gate (adapter_down, its LayerNorm)
-    # by sqrt(flipped / active) ~ 5-8 % however large the batch is; tensors above the gate keep the 2e-2 bound.
-    gated = (lambda k: cfg.adapter == "houlsby" and ("adapter_down" in k or "adapter_norm_before" in k))
     if names:
         # north_star gate: <= 2e-2 relative on the adapter gradient (all trainable tensors taken as one vector) ...
         got = torch.cat([params[k].grad.detach().float().cpu().reshape(-1) for k in names])
         ref = torch.cat([sd_o[k].grad.detach().float().reshape(-1) for k in names])
-        assert rel(got, ref) < (1.5 * TOL if cfg.adapter == "houlsby" else TOL), rel(got, ref)
+        assert rel(got, ref) < TOL, rel(got, ref)
     # ... and per tensor: 2e-2 for the shallow towers; at depth 12 the bf16 operand rounding of the forward (feature
     # error ~8e-3) shows up as 1-2e-2 on the smallest-norm factors (|grad| ~ 1e-2), so the per-tensor bound is 3e-2 there
     per_tensor = TOL if cfg.depth <= 3 else 1.5 * TOL
     for k in names:
-        bound = 0.1 if gated(k) else per_tensor
-        assert rel(params[k].grad, sd_o[k].grad) < bound, (k, rel(params[k].grad, sd_o[k].grad))
+        assert rel(params[k].grad, sd_o[k].grad) < per_tensor, (k, rel(params[k].grad, sd_o[k].grad))
 
 
 @pytest.mark.parametrize("adapter", ["kron", "lora"])
