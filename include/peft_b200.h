@@ -61,6 +61,13 @@ int peft_set_attention_algo(int algo);
 int peft_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
                    const float* bias, void* out, long long ldo, void* out2, long long ldo2,
                    const void* aux, long long ldaux, int epilogue, void* stream);
+/* same, with (acc + bias) multiplied by rowscale[row] (fp32 [M], NULL = none) before the rest of the epilogue:
+ * the per-sample stochastic-depth factor keep/keep_prob of `x + self.drop_path(branch)` (timm DropPath; FS/kadaptation.py:263,
+ * 276-277, full_shot yaml DROP_PATH_RATE 0.1) folded into the residual epilogue (forward) and into the first dX product
+ * of the branch (backward). */
+int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
+                      const float* bias, void* out, long long ldo, void* out2, long long ldo2,
+                      const void* aux, long long ldaux, int epilogue, const float* rowscale, void* stream);
 
 /* LayerNorm over the last dimension, one warp per token row, D % 128 == 0.
  * replaces: nn.LayerNorm / CLIP LayerNorm forward — FS/kadaptation.py:274-276,538 (eps 1e-6), FS/model.py:156-162,1156-1157,1208,1214 (eps 1e-5).
@@ -190,6 +197,9 @@ int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* 
 int peft_gemm_f32(const float* a, long long lda, const float* b, long long ldb, int M, int N, int K, const float* bias,
                   float* out, long long ldo, float* out2, long long ldo2, const float* aux, long long ldaux, int epilogue,
                   void* stream);
+int peft_gemm_f32_rs(const float* a, long long lda, const float* b, long long ldb, int M, int N, int K, const float* bias,
+                     float* out, long long ldo, float* out2, long long ldo2, const float* aux, long long ldaux, int epilogue,
+                     const float* rowscale, void* stream);
 /* out[I, J] += x[M, I]^T y[M, J], any I, J (split over M, fp32 atomics) */
 int peft_tn_reduce_f32(const float* x, long long ldx, int I, const float* y, long long ldy, int J, float* out,
                        long long ldout, int M, void* stream);

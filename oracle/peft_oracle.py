@@ -147,27 +147,39 @@ def timm_mlp(x, sd, pfx):
     return F.linear(F.gelu(F.linear(x, sd[pfx + "fc1.weight"], sd[pfx + "fc1.bias"])), sd[pfx + "fc2.weight"], sd[pfx + "fc2.bias"])
 
 
-def timm_block(x, sd, pfx, cfg: VitCfg):
-    """FS/kadaptation.py:273-277 (pre-norm branch); Houlsby variant FS/adapter.py (adapter after the MLP)."""
+def drop_path(x, keep, keep_prob):
+    """timm.models.layers.drop_path (timm 0.4.12, imported at FS/kadaptation.py:30, used :263,276-277) with the Bernoulli
+    draw made explicit: `keep` [B] of 0/1 replaces floor(keep_prob + rand(B)); output = x / keep_prob * keep."""
+    return x.div(keep_prob) * keep.view(-1, 1, 1).to(x.dtype)
+
+
+def timm_block(x, sd, pfx, cfg: VitCfg, drop=None):
+    """FS/kadaptation.py:273-277 (pre-norm branch); Houlsby variant FS/adapter.py (adapter after the MLP).
+    drop = (keep_attn [B], keep_mlp [B], keep_prob) applies stochastic depth to the two branches (training mode)."""
     D = x.shape[-1]
-    x = x + timm_attention(F.layer_norm(x, (D,), sd[pfx + "norm1.weight"], sd[pfx + "norm1.bias"], cfg.ln_eps), sd, pfx + "attn.", cfg)
+    a = timm_attention(F.layer_norm(x, (D,), sd[pfx + "norm1.weight"], sd[pfx + "norm1.bias"], cfg.ln_eps), sd, pfx + "attn.", cfg)
+    x = x + (a if drop is None else drop_path(a, drop[0], drop[2]))
     h = timm_mlp(F.layer_norm(x, (D,), sd[pfx + "norm2.weight"], sd[pfx + "norm2.bias"], cfg.ln_eps), sd, pfx + "mlp.")
     if cfg.adapter == "houlsby":
         h = houlsby_adapter(h, sd, pfx + "adapter.", 1e-5)
     elif cfg.adapter == "compacter":
         h = compacter_adapter(h, sd, pfx + "compacter.", 1e-5)
-    return x + h
+    return x + (h if drop is None else drop_path(h, drop[1], drop[2]))
 
 
-def timm_forward_features(images, sd, cfg: VitCfg):
-    """FS/kadaptation.py:516-544 + PatchEmbed :286-308 — returns the final-LayerNorm cls feature [B, D]."""
+def timm_forward_features(images, sd, cfg: VitCfg, drop_keep=None, drop_path_rate=0.0):
+    """FS/kadaptation.py:516-544 + PatchEmbed :286-308 — returns the final-LayerNorm cls feature [B, D].
+    drop_keep [depth, 2, B] (0/1) + drop_path_rate: stochastic depth with fixed masks, per-block rate
+    linspace(0, rate, depth)[i] (:408)."""
     B = images.shape[0]
     x = F.conv2d(images, sd["patch_embed.proj.weight"], sd["patch_embed.proj.bias"], stride=cfg.patch)
     x = x.flatten(2).transpose(1, 2)
     x = torch.cat((sd["cls_token"].expand(B, -1, -1), x), dim=1)
     x = x + sd["pos_embed"]
+    dpr = [v.item() for v in torch.linspace(0, drop_path_rate, cfg.depth)]
     for i in range(cfg.depth):
-        x = timm_block(x, sd, f"blocks.{i}.", cfg)
+        drop = None if drop_keep is None else (drop_keep[i, 0], drop_keep[i, 1], 1.0 - dpr[i])
+        x = timm_block(x, sd, f"blocks.{i}.", cfg, drop)
     x = F.layer_norm(x, (cfg.width,), sd["norm.weight"], sd["norm.bias"], cfg.ln_eps)
     return x[:, 0]
 

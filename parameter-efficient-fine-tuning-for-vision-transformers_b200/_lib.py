@@ -24,6 +24,8 @@ SIGNATURES = {
     "peft_set_gemm_algo": [C.c_int],
     "peft_set_attention_algo": [C.c_int],
     "peft_gemm_bf16": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
+    "peft_gemm_bf16_rs": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp, _vp],
+    "peft_gemm_f32_rs": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp, _vp],
     "peft_layernorm_fwd": [_vp, _c_ll, C.c_int, _vp, _vp, _vp, _c_ll, C.c_int, _vp, _vp, C.c_int, C.c_int, C.c_float, _vp],
     "peft_layernorm_fwd_add": [_vp, _c_ll, _vp, _vp, _vp, _c_ll, _vp, _vp, _vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_float, _vp],
     "peft_layernorm_bwd": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _vp, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _vp, C.c_int, C.c_int, _vp],

@@ -16,6 +16,12 @@ inline int grid_for(long long total, int threads) {
 extern "C" int peft_gemm_f32(const float* a, long long lda, const float* b, long long ldb, int M, int N, int K,
                              const float* bias, float* out, long long ldo, float* out2, long long ldo2, const float* aux,
                              long long ldaux, int epilogue, void* stream) {
+  return peft_gemm_f32_rs(a, lda, b, ldb, M, N, K, bias, out, ldo, out2, ldo2, aux, ldaux, epilogue, nullptr, stream);
+}
+
+extern "C" int peft_gemm_f32_rs(const float* a, long long lda, const float* b, long long ldb, int M, int N, int K,
+                                const float* bias, float* out, long long ldo, float* out2, long long ldo2, const float* aux,
+                                long long ldaux, int epilogue, const float* rowscale, void* stream) {
   PEFT_REQUIRE(M > 0 && N > 0 && K > 0 && a && b && out, "peft_gemm_f32: bad shape M=%d N=%d K=%d or null operand", M, N, K);
   PEFT_REQUIRE(epilogue >= 0 && epilogue <= 11, "peft_gemm_f32: unknown epilogue %d", epilogue);
   const bool dual = epilogue == 1 || epilogue == 2 || epilogue == 9;
@@ -26,6 +32,7 @@ extern "C" int peft_gemm_f32(const float* a, long long lda, const float* b, long
   p.a = a; p.sa_m = lda; p.sa_k = 1; p.b = b; p.sb_n = ldb; p.sb_k = 1; p.M = M; p.N = N; p.K = K; p.bias = bias;
   p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2; p.aux = need_aux ? aux : nullptr; p.ldaux = ldaux; p.epi = epilogue;
   p.kchunk = K;
+  p.rowscale = rowscale;
   f32::gemm_kernel<<<dim3((N + 63) / 64, (M + 63) / 64, 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
   PEFT_LAUNCH_CHECK();
   return 0;

@@ -143,6 +143,12 @@ using namespace peft;
 extern "C" int peft_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
                               const float* bias, void* out, long long ldo, void* out2, long long ldo2,
                               const void* aux, long long ldaux, int epilogue, void* stream) {
+  return peft_gemm_bf16_rs(a, lda, b, ldb, M, N, K, bias, out, ldo, out2, ldo2, aux, ldaux, epilogue, nullptr, stream);
+}
+
+extern "C" int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
+                                 const float* bias, void* out, long long ldo, void* out2, long long ldo2,
+                                 const void* aux, long long ldaux, int epilogue, const float* rowscale, void* stream) {
   PEFT_REQUIRE(M > 0 && N > 0 && K > 0, "peft_gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
   PEFT_REQUIRE(a && b && out, "peft_gemm_bf16: null operand");
   PEFT_REQUIRE(K % 8 == 0, "peft_gemm_bf16: K must be a multiple of 8 (got %d)", K);
@@ -163,12 +169,16 @@ extern "C" int peft_gemm_bf16(const void* a, long long lda, const void* b, long 
                  "peft_gemm_bf16: epilogue %d needs an aligned aux operand", epilogue);
   }
   if (bias) PEFT_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "peft_gemm_bf16: bias must be 16-byte aligned");
+  if (rowscale)
+    PEFT_REQUIRE(epilogue == EPI_RESID_F32 || epilogue == EPI_STORE || epilogue == EPI_DGELU || epilogue == EPI_DQUICKGELU,
+                 "peft_gemm_bf16_rs: rowscale is supported with the STORE / RESID_F32 / DGELU / DQUICKGELU epilogues (got %d)", epilogue);
 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   GemmParams p;
   p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
   p.aux = aux; p.ldaux = ldaux;
-  p.ksplit = pick_ksplit(M, N, K, epilogue, bias, ldo);
+  p.rowscale = rowscale;
+  p.ksplit = rowscale ? 1 : pick_ksplit(M, N, K, epilogue, bias, ldo);
   {
     static const int dbg = [] { const char* e = getenv("PEFT_GEMM_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;

@@ -47,10 +47,12 @@ struct GemmArgs {
   const float* aux; long long ldaux;
   int epi;
   int kchunk;   // K range per blockIdx.z
+  const float* rowscale = nullptr;   // optional [M]: (acc + bias) *= rowscale[m] (stochastic depth)
 };
 
 __device__ __forceinline__ void gemm_epilogue(const GemmArgs& p, int m, int n, float acc) {
   float v = acc + (p.bias ? p.bias[n] : 0.f);
+  if (p.rowscale) v *= p.rowscale[m];
   float* o = p.out + (long long)m * p.ldo + n;
   const float ax = p.aux ? p.aux[(long long)m * p.ldaux + n] : 0.f;
   switch (p.epi) {

@@ -399,6 +399,14 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               if (colu + j < p.N) v[j] += __ldg(p.bias + colu + j);
           }
         }
+        // stochastic-depth row scale, lane = row (re-read per unit: no register held across units); only the epilogues the
+        // engine uses it with are compiled with it (the host rejects the others)
+        if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE || EPI == EPI_DGELU || EPI == EPI_DQUICKGELU)
+        if (p.rowscale != nullptr) {
+          const float rs = (row0 + lane < p.M) ? __ldg(p.rowscale + row0 + lane) : 0.0f;
+#pragma unroll
+          for (int j = 0; j < T::kUnitCols; ++j) v[j] *= rs;
+        }
         // ---- slot availability / auxiliary operand
         if constexpr (T::kAux) {
           ptx::mbar_wait(&abar[s], (aux_phase >> s) & 1u);

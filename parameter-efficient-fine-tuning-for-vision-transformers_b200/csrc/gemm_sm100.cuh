@@ -48,6 +48,8 @@ struct GemmParams {
   long long ldaux;
   int ksplit = 1;     // 2-CTA kernel, EPI_STORE_F32 only: K is cut into `ksplit` ranges that are separate tiles and are
                       // summed into a pre-zeroed `out` by TMA reduce-add (weight-gradient products: small output, long K)
+  const float* rowscale = nullptr;   // optional fp32 [M]: (acc + bias) is multiplied by rowscale[row] before the rest of the
+                      // epilogue — the per-sample stochastic-depth keep mask / keep_prob of DropPath (FS/kadaptation.py:263,276-277)
   int dbg = 0;        // diagnostics (env PEFT_GEMM_DBG, results are WRONG when set; bench_ops.py gemm_dbg): bit 0 = no B-operand
                       // loads, bit 1 = every tile loads the operands of tile 0, bit 2 = epilogue only drains TMEM (no math / stores)
 };
@@ -108,6 +110,12 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
       for (int j = 0; j < NV; ++j)
         if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
     }
+  }
+  if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE || EPI == EPI_DGELU || EPI == EPI_DQUICKGELU)
+  if (p.rowscale != nullptr) {
+    const float rs = __ldg(p.rowscale + row);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] *= rs;
   }
 
   if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE_F32) {

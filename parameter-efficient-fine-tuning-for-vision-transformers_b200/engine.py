@@ -275,7 +275,9 @@ class VitEngine:
             self.lga = lg.detach().float().contiguous()
             self.lba = lb.detach().float().contiguous()
 
-    def forward(self, images, Dn=None, UpT=None, bn=None):
+    def forward(self, images, Dn=None, UpT=None, bn=None, drop=None):
+        """`drop`: optional fp32 [depth, 2, B*L] per-row stochastic-depth factors keep/keep_prob of the attention ([:, 0]) and
+        MLP ([:, 1]) branches (timm DropPath, FS/kadaptation.py:263,276-277); folded into the two residual epilogues."""
         cfg = self.cfg
         if not self.frozen_loaded:
             raise RuntimeError("VitEngine.forward before load_frozen()")
@@ -286,6 +288,15 @@ class VitEngine:
         w = self._workspace(B)
         self._refresh_adapter(Dn, UpT)
         m = cfg.bottleneck
+        if drop is not None:
+            if m or cfg.train_all:
+                raise NotImplementedError("stochastic depth is supported for the q/v-adapter (PEFT) engine, not with a bottleneck "
+                                          "adapter or in full mode")
+            drop = drop.detach().to(self.dev, torch.float32).contiguous()
+            if tuple(drop.shape) != (dep, 2, B * L):
+                raise ValueError(f"drop must be [depth, 2, B*L] = {(dep, 2, B * L)}, got {tuple(drop.shape)}")
+        w.drop = drop
+        rs = (lambda i, j: None) if drop is None else (lambda i, j: drop[i, j])
         if m:
             if bn is None:
                 raise RuntimeError("VitEngine.forward: bottleneck adapter operands missing")
@@ -320,13 +331,13 @@ class VitEngine:
             else:
                 ops.gemm(xn1[:, :D], self.wqkv[i][:, :D], w.qkv[i], bias=self.bqkv[i])
             ops.attention_fwd(w.qkv[i], w.o[i], w.lse2[i], B, H, L, scale)
-            ops.gemm(w.o[i], self.wproj[i], w.x1[i], bias=self.bproj[i], epilogue=ops.EPI_RESID_F32, aux=w.x0[i])
+            ops.gemm(w.o[i], self.wproj[i], w.x1[i], bias=self.bproj[i], epilogue=ops.EPI_RESID_F32, aux=w.x0[i], rowscale=rs(i, 0))
             xn2 = w.xn2_l[i] if cfg.train_all else w.xn2
             act = w.act_l[i] if cfg.train_all else w.act
             ops.layernorm_fwd(w.x1[i], self.ln2_w[i], self.ln2_b[i], xn2, w.mean2[i], w.rstd2[i], cfg.eps)
             ops.gemm(xn2, self.wfc1[i], w.h[i], bias=self.bfc1[i], epilogue=self.act_fwd, out2=act)
             if not m:
-                ops.gemm(act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i])
+                ops.gemm(act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i], rowscale=rs(i, 1))
             else:
                 # x_{i+1} = x1 + h + up(act(down(LN_a(h)))),  h = mlp(ln2(x1))     (adapter_model.py:330-334 computed once, Q6)
                 ops.gemm(act, self.wfc2[i], w.hf[i], bias=self.bfc2[i], epilogue=ops.EPI_STORE_F32)
@@ -371,6 +382,8 @@ class VitEngine:
         else:
             ops.gemm(dfeat.to(cfg.cdt), self.vproj, w.dyf)                       # dy = dfeat proj^T
             ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
+        drop = getattr(w, "drop", None)
+        rs = (lambda i, j: None) if drop is None else (lambda i, j: drop[i, j])
         dDn = dUpT = None
         if r:
             dDn = torch.zeros(dep, rp, D, device=self.dev, dtype=torch.float32)
@@ -400,13 +413,13 @@ class VitEngine:
                 ops.layernorm_bwd_f32g(w.dxn, w.hf[i], w.mean_a[i], w.rstd_a[i], self.lga[i], w.g, w.gh, w.ghb, dlg[i], dlb[i])
                 gmlp = w.ghb
             # MLP: dh = (g W2) * act'(h) ; dxn2 = dh W1 ; g += LN2'(dxn2)
-            ops.gemm(gmlp, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i])
+            ops.gemm(gmlp, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i], rowscale=rs(i, 1))
             ops.gemm(w.dh, self.wfc1T[i], w.dxn)
             ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb)
             if i == 0 and not rp:
                 break       # nothing trainable is upstream of block 0's attention when there is no q/v adapter
             # attention: d_o = g Wproj ; dqkv = attn'(d_o)
-            ops.gemm(w.gb, self.wprojT[i], w.d_o)
+            ops.gemm(w.gb, self.wprojT[i], w.d_o, rowscale=rs(i, 0))
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
             if rp and cfg.dialect == "clip":
                 dq = w.dqkv[:, :3 * D]
@@ -598,10 +611,10 @@ def backbone_full(engine: VitEngine, images, named_tensors):
 
 class _BackboneFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, engine, images, Dn, UpT, *bn):
+    def forward(ctx, engine, images, Dn, UpT, drop, *bn):
         ctx.engine = engine
         ctx.nbn = len(bn)
-        out = engine.forward(images, Dn, UpT, bn if bn else None)
+        out = engine.forward(images, Dn, UpT, bn if bn else None, drop)
         ctx.generation = engine._fwd_generation
         return out
 
@@ -609,9 +622,9 @@ class _BackboneFn(torch.autograd.Function):
     def backward(ctx, dfeat):
         dDn, dUpT, bng = ctx.engine.backward(dfeat, ctx.generation)
         extra = tuple(bng) if bng is not None else (None,) * ctx.nbn
-        return (None, None, dDn, dUpT) + extra
+        return (None, None, dDn, dUpT, None) + extra
 
 
-def backbone(engine: VitEngine, images, Dn=None, UpT=None, bn=None):
+def backbone(engine: VitEngine, images, Dn=None, UpT=None, bn=None, drop=None):
     """Differentiable (w.r.t. Dn / UpT / the bottleneck-adapter operands) visual-tower feature extraction."""
-    return _BackboneFn.apply(engine, images, Dn, UpT, *(bn if bn is not None else ()))
+    return _BackboneFn.apply(engine, images, Dn, UpT, drop, *(bn if bn is not None else ()))

@@ -32,11 +32,19 @@ def _mat(t: torch.Tensor, dtype=None, name="tensor"):
     return t.data_ptr(), t.stride(0)
 
 
-def gemm(a, b, out, bias=None, epilogue=EPI_STORE, out2=None, aux=None):
-    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T (+ bias)); bf16 operands, see peft_gemm_bf16.  fp32 operands select the fp32
-    verification kernels (peft_gemm_f32: every tensor fp32, same epilogue semantics)."""
+def _rowscale(rs, M):
+    if rs is None:
+        return 0
+    if not rs.is_cuda or rs.dtype != torch.float32 or rs.numel() != M or not rs.is_contiguous():
+        raise ValueError("gemm: rowscale must be a contiguous CUDA fp32 vector of length M")
+    return rs.data_ptr()
+
+
+def gemm(a, b, out, bias=None, epilogue=EPI_STORE, out2=None, aux=None, rowscale=None):
+    """out[M,N] = epilogue((a[M,K] @ b[N,K]^T (+ bias)) * rowscale[:, None]); bf16 operands, see peft_gemm_bf16 / _rs.  fp32
+    operands select the fp32 verification kernels (peft_gemm_f32: every tensor fp32, same epilogue semantics)."""
     if a.dtype == torch.float32:
-        return _gemm_f32(a, b, out, bias, epilogue, out2, aux)
+        return _gemm_f32(a, b, out, bias, epilogue, out2, aux, rowscale)
     pa, lda = _mat(a, torch.bfloat16, "a")
     pb, ldb = _mat(b, torch.bfloat16, "b")
     M, K = a.shape
@@ -55,12 +63,12 @@ def gemm(a, b, out, bias=None, epilogue=EPI_STORE, out2=None, aux=None):
         pax, ldax = _mat(aux, torch.float32 if epilogue == EPI_RESID_F32 else torch.bfloat16, "aux")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != N or not bias.is_contiguous()):
         raise ValueError("gemm: bias must be contiguous fp32 [N]")
-    _lib.check(_lib.load().peft_gemm_bf16(pa, lda, pb, ldb, M, N, K, _p(bias), po, ldo, po2, ldo2, pax, ldax, epilogue,
-                                          _stream()), "peft_gemm_bf16")
+    _lib.check(_lib.load().peft_gemm_bf16_rs(pa, lda, pb, ldb, M, N, K, _p(bias), po, ldo, po2, ldo2, pax, ldax, epilogue,
+                                             _rowscale(rowscale, M), _stream()), "peft_gemm_bf16")
     return out
 
 
-def _gemm_f32(a, b, out, bias, epilogue, out2, aux):
+def _gemm_f32(a, b, out, bias, epilogue, out2, aux, rowscale=None):
     f32 = torch.float32
     pa, lda = _mat(a, f32, "a")
     pb, ldb = _mat(b, f32, "b")
@@ -73,8 +81,8 @@ def _gemm_f32(a, b, out, bias, epilogue, out2, aux):
     pax, ldax = _mat(aux, f32, "aux") if aux is not None else (0, 0)
     if bias is not None and (bias.dtype != f32 or bias.numel() != N or not bias.is_contiguous()):
         raise ValueError("gemm: bias must be contiguous fp32 [N]")
-    _lib.check(_lib.load().peft_gemm_f32(pa, lda, pb, ldb, M, N, K, _p(bias), po, ldo, po2, ldo2, pax, ldax, epilogue,
-                                         _stream()), "peft_gemm_f32")
+    _lib.check(_lib.load().peft_gemm_f32_rs(pa, lda, pb, ldb, M, N, K, _p(bias), po, ldo, po2, ldo2, pax, ldax, epilogue,
+                                            _rowscale(rowscale, M), _stream()), "peft_gemm_f32")
     return out
 
 

@@ -149,8 +149,9 @@ class Block(nn.Module):
         super().__init__()
         if not pre_norm:
             raise NotImplementedError("post-norm blocks are not supported")
-        if drop_path != 0.:
-            raise NotImplementedError("stochastic depth > 0 is not supported")
+        # stochastic depth (timm DropPath, FS/kadaptation.py:263,276-277): the per-sample keep mask / keep_prob is folded into
+        # the two residual epilogues by the engine; the rate lives here like in the reference block
+        self.drop_path_rate = float(drop_path)
         self.norm1 = norm_layer(dim)
         self.attn = Attention(dim, num_heads=num_heads, qkv_bias=qkv_bias, qk_scale=qk_scale, attn_drop=attn_drop,
                               proj_drop=drop, res_score=res_score, **adapter_kw)
@@ -347,7 +348,26 @@ def tower_tensors(root, keys):
     return out
 
 
-def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck):
+def sample_drop_path(model, B, L, device):
+    """fp32 [depth, 2, B*L] row factors keep/keep_prob of the attention and MLP residual branches, or None (eval mode /
+    all rates 0).  One Bernoulli(keep_prob) draw per sample and branch, exactly timm's `drop_path`:
+    floor(keep_prob + U[0,1)) / keep_prob.  `model.drop_path_keep` ([depth, 2, B] of 0/1), when set, replaces the random
+    draw (parity tests against the oracle with a fixed mask)."""
+    rates = [getattr(b, "drop_path_rate", 0.0) for b in model.blocks]
+    if not model.training or not any(r > 0 for r in rates):
+        return None
+    keep_prob = 1.0 - torch.tensor(rates, device=device, dtype=torch.float32).view(-1, 1, 1)
+    fixed = getattr(model, "drop_path_keep", None)
+    if fixed is not None:
+        keep = fixed.to(device=device, dtype=torch.float32)
+        if tuple(keep.shape) != (len(rates), 2, B):
+            raise ValueError(f"drop_path_keep must be [depth, 2, B] = {(len(rates), 2, B)}")
+    else:
+        keep = torch.floor(keep_prob + torch.rand(len(rates), 2, B, device=device))
+    return (keep / keep_prob).repeat_interleave(L, dim=2).contiguous()
+
+
+def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck, drop=None):
     """Shared forward of both dialects' VisionTransformer: picks the PEFT engine (frozen tower, adapters trainable) or the
     full engine (any tower tensor requires grad: full fine-tuning, bias/LayerNorm tuning, Fastfood)."""
     if not x.is_cuda:
@@ -365,6 +385,8 @@ def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck):
         setattr(model, slot, eng)
         model._frozen_sig = None
     if full:
+        if drop is not None:
+            raise NotImplementedError("stochastic depth is not supported in full (train-all) mode")
         return backbone_full(eng, x, tensors)
     cacheable = all(isinstance(t, nn.Parameter) for _, t in tensors)
     sig = (slot,) + tuple((k, t.data_ptr(), t._version) for k, t in tensors) if cacheable else None
@@ -372,7 +394,7 @@ def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck):
         eng.load_frozen({k: t.detach() for k, t in tensors})
         model._frozen_sig = sig
     Dn, UpT = lowrank()
-    return backbone(eng, x, Dn, UpT, bottleneck())
+    return backbone(eng, x, Dn, UpT, bottleneck(), drop)
 
 
 class VisionTransformer(nn.Module):
@@ -386,8 +408,8 @@ class VisionTransformer(nn.Module):
         super().__init__()
         if hybrid_backbone is not None or norm_embed or not use_cls_tocken or in_chans != 3:
             raise NotImplementedError("hybrid backbone / norm_embed / no-cls-token / in_chans != 3 are not supported")
-        if drop_rate != 0. or drop_path_rate != 0.:
-            raise NotImplementedError("dropout / stochastic depth > 0 are not supported")
+        if drop_rate != 0.:
+            raise NotImplementedError("dropout > 0 is not supported (the reference configs use 0)")
         norm_layer = norm_layer or partial(nn.LayerNorm, eps=1e-6)
         self.num_classes = num_classes
         self.num_features = self.embed_dim = embed_dim
@@ -396,11 +418,12 @@ class VisionTransformer(nn.Module):
         num_patches = self.patch_embed.num_patches
         self.cls_token = nn.Parameter(torch.zeros(1, 1, embed_dim))
         self.pos_embed = nn.Parameter(torch.zeros(1, num_patches + 1, embed_dim))
+        dpr = [v.item() for v in torch.linspace(0, drop_path_rate, depth)]      # stochastic depth decay rule (FS/kadaptation.py:408)
         self.blocks = nn.ModuleList([
             Block(dim=embed_dim, num_heads=num_heads, mlp_ratio=mlp_ratio, qkv_bias=qkv_bias, qk_scale=qk_scale,
-                  drop=drop_rate, attn_drop=attn_drop_rate, drop_path=0., norm_layer=norm_layer, pre_norm=pre_norm,
+                  drop=drop_rate, attn_drop=attn_drop_rate, drop_path=dpr[i], norm_layer=norm_layer, pre_norm=pre_norm,
                   res_score=res_score, adapter=adapter, **adapter_kw)
-            for _ in range(depth)])
+            for i in range(depth)])
         self.norm = norm_layer(embed_dim)
         self.head = nn.Linear(embed_dim, num_classes) if num_classes > 0 else nn.Identity()
         nn.init.trunc_normal_(self.cls_token, std=.02)
@@ -468,7 +491,8 @@ class VisionTransformer(nn.Module):
         extra = dict(rank=self._rank(), **self._bottleneck_cfg())
         if self.adapter_kind == "kron" and kron_is_dense(self.blocks[0].attn):
             extra["dense_delta"] = True
-        return run_tower(self, x, "timm", self._cfg, extra, self.lowrank_operands, self.bottleneck_operands)
+        drop = sample_drop_path(self, x.shape[0], self.patch_embed.num_patches + 1, x.device)
+        return run_tower(self, x, "timm", self._cfg, extra, self.lowrank_operands, self.bottleneck_operands, drop)
 
     def forward(self, x):
         return self.forward_features(x)
