@@ -47,6 +47,11 @@ unsigned long long peft_kernel_count(int kind);
 /* tuning / test knob: which tensor-core GEMM kernel peft_gemm_bf16 uses — 0 = automatic (2-CTA cta_group::2 kernel when
  * the problem fills the 74 SM pairs, else the 1-CTA kernel), 1 = always 1-CTA, 2 = always 2-CTA. */
 int peft_set_gemm_algo(int algo);
+/* diagnostics (tests/bench_ops.py gemm_stats): with PEFT_GEMM_STATS=1 in the environment the 2-CTA GEMM records, per CTA,
+ * the cycles its TMA producer, MMA issuer and first epilogue warp spent waiting on their mbarriers during the LAST launch:
+ * host_out[cta*8 + {0: producer wait-empty, 1: producer total, 2: issuer wait-full, 3: issuer wait-tmem-empty, 4: issuer
+ * total, 5: epilogue wait-accumulator, 6: epilogue total}].  Synchronises the device. */
+int peft_debug_gemm_stats(unsigned long long* host_out, int n_ctas);
 /* same for the attention kernels: 0 = automatic (tcgen05/TMEM kernels for L <= 272), 1 = mma.sync kernels, 2 = tcgen05 */
 int peft_set_attention_algo(int algo);
 

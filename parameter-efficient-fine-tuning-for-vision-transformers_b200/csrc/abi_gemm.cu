@@ -41,6 +41,18 @@ static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, c
   }
 }
 
+// diagnostics: per-CTA wait-cycle counters of the LAST 2-CTA GEMM launch (env PEFT_GEMM_STATS=1 allocates the buffer)
+static unsigned long long* gemm_stats_buffer() {
+  static unsigned long long* buf = [] {
+    const char* e = getenv("PEFT_GEMM_STATS");
+    unsigned long long* p = nullptr;
+    if (e && atoi(e) > 0 && cudaMalloc(&p, 256 * 8 * sizeof(unsigned long long)) == cudaSuccess) cudaMemset(p, 0, 256 * 8 * sizeof(unsigned long long));
+    else p = nullptr;
+    return p;
+  }();
+  return buf;
+}
+
 // ---------------------------------------------------------------- 2-CTA kernel (gemm2_sm100.cuh)
 static std::atomic<int>& gemm_algo() {
   static std::atomic<int> a{0};   // 0 = auto, 1 = force 1-CTA kernel, 2 = force 2-CTA kernel
@@ -183,6 +195,7 @@ extern "C" int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, lo
     static const int dbg = [] { const char* e = getenv("PEFT_GEMM_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
   }
+  p.stats = gemm_stats_buffer();
   if (p.ksplit > 1) PEFT_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)M * N * sizeof(float), s));
   if (p.ksplit > 1 || use_gemm2(M, N)) {
     CUtensorMap ta, tb, to, to2, tx;
@@ -244,4 +257,13 @@ extern "C" int peft_gemm_tn_bf16(const void* x, long long ldx, const void* y, lo
   rc = make_tmap_2d(&to, out, true, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldo, 32, 32);
   if (rc) return rc;
   return launch_gemm2<EPI_STORE_F32, true>(ta, tb, to, to, to, p, s);
+}
+
+extern "C" int peft_debug_gemm_stats(unsigned long long* host_out, int n_ctas) {
+  unsigned long long* buf = peft::gemm_stats_buffer();
+  PEFT_REQUIRE(buf != nullptr, "peft_debug_gemm_stats: set PEFT_GEMM_STATS=1 before the first GEMM");
+  PEFT_REQUIRE(host_out && n_ctas > 0 && n_ctas <= 256, "peft_debug_gemm_stats: bad arguments");
+  PEFT_CUDA_CHECK(cudaDeviceSynchronize());
+  PEFT_CUDA_CHECK(cudaMemcpy(host_out, buf, (size_t)n_ctas * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return 0;
 }

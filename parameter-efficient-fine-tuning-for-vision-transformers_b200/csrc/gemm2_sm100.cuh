@@ -71,6 +71,61 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_2sm_u32(uint32_t smem_dst, const CUtensorMap* tm, uint32_t bar_cluster_addr, int c0,
+                                                    int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+// true in exactly one lane of the (fully active) warp — always the same lane, so tcgen05.commit tracks the MMAs it issued
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.b32 %0, 1, 0, P;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+// One 64-wide k-block of the 2-CTA product: up to four tcgen05.mma (K = 16 each) whose shared-memory descriptors differ only
+// in the start-address field of the low word (+step per K-step).  The first MMA accumulates iff acc_first != 0.
+__device__ __forceinline__ void umma_kblock_bf16_2sm(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                                     uint32_t acc_first, int ksteps, uint32_t step) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p0, p1, p2, p3, pt;\n"
+      ".reg .b64 da, db;\n"
+      ".reg .b32 al, bl;\n"
+      "setp.ne.b32 p0, %5, 0;\n"
+      "setp.gt.s32 p1, %6, 1;\n"
+      "setp.gt.s32 p2, %6, 2;\n"
+      "setp.gt.s32 p3, %6, 3;\n"
+      "setp.eq.u32 pt, %7, %7;\n"
+      "mov.b64 da, {%1, %3};\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p0;\n"
+      "add.u32 al, %1, %7;\n"
+      "add.u32 bl, %2, %7;\n"
+      "mov.b64 da, {al, %3};\n"
+      "mov.b64 db, {bl, %3};\n"
+      "@p1 tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, pt;\n"
+      "add.u32 al, al, %7;\n"
+      "add.u32 bl, bl, %7;\n"
+      "mov.b64 da, {al, %3};\n"
+      "mov.b64 db, {bl, %3};\n"
+      "@p2 tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, pt;\n"
+      "add.u32 al, al, %7;\n"
+      "add.u32 bl, bl, %7;\n"
+      "mov.b64 da, {al, %3};\n"
+      "mov.b64 db, {bl, %3};\n"
+      "@p3 tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, pt;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(acc_first), "r"(ksteps), "r"(step)
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* smem_src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(tm)),
@@ -257,73 +312,113 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
 
+  // Warps 0 and 1 run their loops CONVERGED (all 32 lanes) and only the TMA / MMA / commit instructions sit under an
+  // elect.sync predicate: every operand of those instructions is then provably warp-uniform and lives in uniform registers.
+  // With the whole loop inside `if (lane == 0)` the compiler has to move each descriptor into uniform registers through an
+  // ELECT / R2UR.BROADCAST waterfall loop (~25 dependent scalar instructions per tcgen05.mma), and that chain — not the
+  // tensor pipe, the operand feed or the epilogue — paced the kernel at ~200 clk per 128-clk UMMA (r02 gemm_probe).
   if (warp == 0) {
-    // ===================== TMA producer (one lane, both CTAs) =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        const int ks = tile % ksplit, mn = tile / ksplit;
-        const int mp = mn / num_n, n_blk = mn % num_n;
-        const int row_a = (p.dbg & 2) ? (int)cta_rank * kBM : mp * 2 * kBM + (int)cta_rank * kBM;
-        const int row_b = (p.dbg & 2) ? (int)cta_rank * (kG2BN / 2) : n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
-        const int kb0 = ks * kb_per, kb1 = min(num_kb, kb0 + kb_per);
-        for (int kb = kb0; kb < kb1; ++kb) {
+    // ===================== TMA producer (both CTAs) =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    long long t_wait = 0, t_begin = clock64();
+    const uint32_t tiles_u32 = ptx::smem_u32(tiles);
+    const uint32_t full0 = ptx::mapa(ptx::smem_u32(&full_bar[0]), 0);     // the leader's full barriers (8 bytes apart)
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int ks = tile % ksplit, mn = tile / ksplit;
+      const int mp = mn / num_n, n_blk = mn % num_n;
+      const int row_a = (p.dbg & 2) ? (int)cta_rank * kBM : mp * 2 * kBM + (int)cta_rank * kBM;
+      const int row_b = (p.dbg & 2) ? (int)cta_rank * (kG2BN / 2) : n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
+      const int kb0 = ks * kb_per, kb1 = min(num_kb, kb0 + kb_per);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (p.stats) {
+          const long long t0 = clock64();
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = tiles + stage * kG2StageBytes;
-          uint8_t* sb = sa + kBM * kBK * 2;
-          const uint32_t bar = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
-          if (!TN && (p.dbg & 1)) {          // diagnostic: A operand only (the B slot keeps stale data)
-            if (leader) ptx::mbar_expect_tx(&full_bar[stage], kG2StageBytes);
-            ptx::tma_load_2d_2sm(sa, &tmap_a, bar, kb * kBK, row_a);
-            if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
-            continue;
-          }
-          if (leader) ptx::mbar_expect_tx(&full_bar[stage], 2 * kG2StageBytes);
-          if constexpr (TN) {
-            ptx::tma_load_2d_2sm(sa, &tmap_a, bar, row_a, kb * kBK);
-            ptx::tma_load_2d_2sm(sa + 8192, &tmap_a, bar, row_a + 64, kb * kBK);
-            ptx::tma_load_2d_2sm(sb, &tmap_b, bar, row_b, kb * kBK);
-            ptx::tma_load_2d_2sm(sb + 8192, &tmap_b, bar, row_b + 64, kb * kBK);
-          } else {
-            ptx::tma_load_2d_2sm(sa, &tmap_a, bar, kb * kBK, row_a);
-            ptx::tma_load_2d_2sm(sb, &tmap_b, bar, kb * kBK, row_b);
-          }
-          if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
+          t_wait += clock64() - t0;
+        } else {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
         }
+        const uint32_t sa = tiles_u32 + stage * kG2StageBytes;
+        const uint32_t sb = sa + kBM * kBK * 2;
+        const uint32_t bar = full0 + stage * 8;
+        if (ptx::elect_one()) {
+          if (p.dbg & 8) {                   // diagnostic: no operand loads at all (pure MMA + epilogue on stale smem)
+            if (leader) ptx::mbar_expect_tx(&full_bar[stage], 0);
+          } else if (!TN && (p.dbg & 1)) {   // diagnostic: A operand only (the B slot keeps stale data)
+            if (leader) ptx::mbar_expect_tx(&full_bar[stage], kG2StageBytes);
+            ptx::tma_load_2d_2sm_u32(sa, &tmap_a, bar, kb * kBK, row_a);
+          } else {
+            if (leader) ptx::mbar_expect_tx(&full_bar[stage], 2 * kG2StageBytes);
+            if constexpr (TN) {
+              ptx::tma_load_2d_2sm_u32(sa, &tmap_a, bar, row_a, kb * kBK);
+              ptx::tma_load_2d_2sm_u32(sa + 8192, &tmap_a, bar, row_a + 64, kb * kBK);
+              ptx::tma_load_2d_2sm_u32(sb, &tmap_b, bar, row_b, kb * kBK);
+              ptx::tma_load_2d_2sm_u32(sb + 8192, &tmap_b, bar, row_b + 64, kb * kBK);
+            } else {
+              ptx::tma_load_2d_2sm_u32(sa, &tmap_a, bar, kb * kBK, row_a);
+              ptx::tma_load_2d_2sm_u32(sb, &tmap_b, bar, kb * kBK, row_b);
+            }
+          }
+        }
+        __syncwarp();
+        if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
       }
     }
+    if (p.stats && lane == 0) { p.stats[blockIdx.x * 8 + 0] = t_wait; p.stats[blockIdx.x * 8 + 1] = clock64() - t_begin; }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one lane of the leader CTA) =====================
-    if (leader && lane == 0) {
+    // ===================== MMA issuer (leader CTA; one elected lane issues) =====================
+    if (leader) {
       constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kG2BN) | (TN ? ((1u << 15) | (1u << 16)) : 0u);
+      // shared-memory matrix descriptor = {lo: start address >> 4 | LBO field, hi: SBO 1024 B | version 1 | SWIZZLE_128B}; the
+      // K-step advance (32 B inside the swizzle row, or 2 KB for the MN-major TN tiles) only touches the low word
+      constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
+      constexpr uint32_t kDescLoFlags = TN ? ((8192u >> 4) << 16) : (1u << 16);
+      constexpr uint32_t kStepUnits = TN ? (2048u >> 4) : (32u >> 4);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      long long t_wfull = 0, t_wtmem = 0, t_begin = clock64();
+      const uint32_t tiles_u32 = ptx::smem_u32(tiles);
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
+        if (p.stats) {
+          const long long t0 = clock64();
+          ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
+          t_wtmem += clock64() - t0;
+        } else {
+          ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
+        }
         ptx::tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kG2BN);
         const int kb0 = (tile % ksplit) * kb_per, kb1 = min(num_kb, kb0 + kb_per);
         for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait_cluster(&full_bar[stage], phase);
+          if (p.stats) {
+            const long long t0 = clock64();
+            ptx::mbar_wait_cluster(&full_bar[stage], phase);
+            t_wfull += clock64() - t0;
+          } else {
+            ptx::mbar_wait_cluster(&full_bar[stage], phase);
+          }
           ptx::tcgen05_fence_after();
-          const uint32_t sa = ptx::smem_u32(tiles + stage * kG2StageBytes);
-          const uint64_t adesc = TN ? ptx::make_smem_desc_sw128_mn128(sa) : ptx::make_smem_desc_sw128(sa);
-          const uint64_t bdesc = TN ? ptx::make_smem_desc_sw128_mn128(sa + kBM * kBK * 2) : ptx::make_smem_desc_sw128(sa + kBM * kBK * 2);
+          const uint32_t sa = tiles_u32 + stage * kG2StageBytes;
+          const uint32_t a_lo = ((sa & 0x3FFFFu) >> 4) | kDescLoFlags;
+          const uint32_t b_lo = (((sa + kBM * kBK * 2) & 0x3FFFFu) >> 4) | kDescLoFlags;
           const int krem = p.K - kb * kBK;
           const int ksteps = krem >= kBK ? (kBK / 16) : ((krem + 15) / 16);
-          constexpr uint64_t kstep = TN ? (2048 >> 4) : (32 >> 4);     // descriptor start-address units per UMMA K-step
-          for (int k = 0; k < ksteps; ++k)
-            ptx::umma_bf16_2sm(tmem_d, adesc + kstep * static_cast<uint64_t>(k), bdesc + kstep * static_cast<uint64_t>(k), idesc,
-                               (kb != kb0 || k != 0) ? 1u : 0u);
-          ptx::umma_commit_2sm(&empty_bar[stage], 3);       // frees this smem slot in both CTAs
+          if (ptx::elect_one()) {
+            ptx::umma_kblock_bf16_2sm(tmem_d, a_lo, b_lo, kDescHi, idesc, kb != kb0 ? 1u : 0u, ksteps, kStepUnits);
+            ptx::umma_commit_2sm(&empty_bar[stage], 3);       // frees this smem slot in both CTAs
+          }
+          __syncwarp();
           if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit_2sm(&tmem_full_bar[acc], 3);       // accumulator complete -> both CTAs' epilogues
+        if (ptx::elect_one()) ptx::umma_commit_2sm(&tmem_full_bar[acc], 3);   // accumulator complete -> both CTAs' epilogues
+        __syncwarp();
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
+      }
+      if (p.stats && lane == 0) {
+        p.stats[blockIdx.x * 8 + 2] = t_wfull; p.stats[blockIdx.x * 8 + 3] = t_wtmem; p.stats[blockIdx.x * 8 + 4] = clock64() - t_begin;
       }
     }
   } else if (warp >= 4) {
@@ -339,6 +434,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     const uint32_t tmem_empty_remote1 = ptx::mapa(ptx::smem_u32(&tmem_empty_bar[1]), 0);
     int acc = 0;
     uint32_t acc_phase = 0;
+    long long t_wacc = 0, t_begin = clock64();
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       const int mn = tile / ksplit;
       const int mp = mn / num_n, n_blk = mn % num_n;
@@ -355,7 +451,13 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           }
         }
       }
-      ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+      if (p.stats) {
+        const long long t0 = clock64();
+        ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+        t_wacc += clock64() - t0;
+      } else {
+        ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+      }
       ptx::tcgen05_fence_after();
       const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                               static_cast<uint32_t>(acc * kG2BN + half * 128);
@@ -501,6 +603,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       if (acc == 0) acc_phase ^= 1;
     }
     if (lane == 0) ptx::bulk_wait<0>();   // all global writes of this warp are complete before the CTA exits
+    if (p.stats && ew == 0 && lane == 0) { p.stats[blockIdx.x * 8 + 5] = t_wacc; p.stats[blockIdx.x * 8 + 6] = clock64() - t_begin; }
   }
   ptx::tcgen05_fence_before();
   __syncthreads();

@@ -79,6 +79,17 @@ _CLIP_KEYS = dict(ln1_w="transformer.resblocks.{i}.ln_1.weight", ln1_b="transfor
                   fc2_w="transformer.resblocks.{i}.mlp.c_proj.weight", fc2_b="transformer.resblocks.{i}.mlp.c_proj.bias")
 
 
+def _tn_chunks(rp):
+    """(offset, width) pieces of the rank_pad adapter columns that peft_tn_reduce accepts (I in {64, 32, 16}); rank_pad is a
+    multiple of 16, so a 48-wide tail becomes 32 + 16."""
+    out, c = [], 0
+    while c < rp:
+        cw = 64 if rp - c >= 64 else (32 if rp - c >= 32 else 16)
+        out.append((c, cw))
+        c += cw
+    return out
+
+
 class _Workspace:
     """Activations saved for backward + scratch, for one batch size."""
 
@@ -150,11 +161,16 @@ class VitEngine:
             raise RuntimeError("peft_b200.VitEngine needs a CUDA device (sm_100a); there is no CPU fallback")
         if cfg.precision not in ("bf16", "fp32"):
             raise ValueError(f"EngineCfg.precision must be 'bf16' or 'fp32', got {cfg.precision!r}")
+        if cfg.bottleneck and cfg.precision == "bf16" and cfg.bottleneck not in (16, 32, 64):
+            raise NotImplementedError(f"bottleneck width {cfg.bottleneck}: the adapter-gradient reductions (peft_tn_reduce) take "
+                                      "16, 32 or 64 columns (the reference uses 64)")
         self.cfg = cfg
         self.dev = torch.device(device)
         self.ws = {}
         self.frozen_loaded = False
         self._fwd_generation = 0
+        self._opgen = 0        # bumped whenever the per-ENGINE operands backward reads are rewritten (adapter K-extension columns,
+                               # bottleneck weights, re-packed frozen weights): a backward whose forward is older must not run
 
     # ------------------------------------------------------------------ frozen weights
     def load_frozen(self, sd: dict):
@@ -229,6 +245,7 @@ class VitEngine:
         self.act_fwd = ops.EPI_GELU if cfg.dialect == "timm" else ops.EPI_QUICKGELU
         self.act_bwd = ops.EPI_DGELU if cfg.dialect == "timm" else ops.EPI_DQUICKGELU
         self.frozen_loaded = True
+        self._opgen += 1
 
     def _pad_k(self, w2d):
         kp = self.cfg.patch_k
@@ -358,7 +375,9 @@ class VitEngine:
             feat = torch.empty(B, cfg.out_dim, device=self.dev, dtype=torch.float32)
             ops.gemm(w.yf, self.vprojT, feat, epilogue=ops.EPI_STORE_F32)
         w.generation += 1
-        self._fwd_generation = (B, w.generation)
+        if cfg.rank or cfg.bottleneck:
+            self._opgen += 1           # _refresh_adapter / _refresh_bottleneck rewrote operands the backward reads
+        self._fwd_generation = (B, w.generation, self._opgen)
         return feat
 
     # ------------------------------------------------------------------ backward
@@ -369,8 +388,9 @@ class VitEngine:
         D, L, H, dep, r, rp = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.rank, cfg.rank_pad
         B = dfeat.shape[0]
         w = self._workspace(B)
-        if (generation or self._fwd_generation) != (B, w.generation):
-            raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
+        if (generation or self._fwd_generation) != (B, w.generation, self._opgen):
+            raise RuntimeError("VitEngine.backward: the saved activations or the adapter / weight operands of this forward were "
+                               "overwritten by a later forward (run backward before the next forward of the same engine)")
         dfeat = dfeat.contiguous().float()
         w.g.zero_()
         w.gb.zero_()
@@ -425,8 +445,7 @@ class VitEngine:
                 dq = w.dqkv[:, :3 * D]
                 ops.clip_delta(dq, w.dlt, B, H, L, 1.0 / scale, 1.0, backward=True)  # d[dq|dv] gathered back (Q1 inverse)
                 ops.gemm(w.dlt, self.up2T_bf[i], w.dqkv[:, 3 * D:])                 # dp = d[dq|dv] [Up_q;Up_v]
-                for c in range(0, rp, 64):
-                    cw = min(64, rp - c)
+                for c, cw in _tn_chunks(rp):
                     pc = w.xn1[i][:, D + c:D + c + cw]
                     ops.tn_reduce(pc, w.dlt[:, :D], dUpT[i, c:c + cw, :D])
                     ops.tn_reduce(pc, w.dlt[:, D:], dUpT[i, c:c + cw, 2 * D:])
@@ -436,14 +455,12 @@ class VitEngine:
                 ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
                 self._dw(w, w.xn1[i][:, D:], dq, dUpT[i])                           # dUp^T = p^T dqkv as ONE tensor-core product
                 if not cfg.dense_delta:
-                    for c in range(0, rp, 64):
-                        cw = min(64, rp - c)
+                    for c, cw in _tn_chunks(rp):
                         ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
             elif rp:
                 dq = w.dqkv[:, :3 * D]
                 ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up
-                for c in range(0, rp, 64):                                          # adapter-gradient token reductions
-                    cw = min(64, rp - c)
+                for c, cw in _tn_chunks(rp):                                        # adapter-gradient token reductions
                     ops.tn_reduce(w.xn1[i][:, D + c:D + c + cw], dq, dUpT[i, c:c + cw])            # dUp^T = p^T dqkv
                     if not cfg.dense_delta:
                         ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])  # dDn = dp^T x
@@ -499,8 +516,9 @@ class VitEngine:
         D, L, H, dep, F = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.mlp
         B = dfeat.shape[0]
         w = self._workspace(B)
-        if (generation or self._fwd_generation) != (B, w.generation):
-            raise RuntimeError("VitEngine.backward: the saved activations were overwritten by a later forward")
+        if (generation or self._fwd_generation) != (B, w.generation, self._opgen):
+            raise RuntimeError("VitEngine.backward: the saved activations or the adapter / weight operands of this forward were "
+                               "overwritten by a later forward (run backward before the next forward of the same engine)")
         dev, f32 = self.dev, torch.float32
         z = lambda *sh: torch.zeros(*sh, device=dev, dtype=f32)
         e = lambda *sh: torch.empty(*sh, device=dev, dtype=f32)

@@ -110,6 +110,56 @@ def bench_gemm(M=50432, iters=20, only=None):
         print(f"gemm {name:24s} M={M} N={N} K={K}: {t:7.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
 
 
+def gemm_stats(M=50432):
+    """PEFT_GEMM_STATS=1: where the three roles of the 2-CTA GEMM wait (cycles, mean over CTAs) for each C3 product."""
+    import ctypes
+    cases = [("qkv store", 2304, 784, ops.EPI_STORE), ("proj +resid f32", 768, 768, ops.EPI_RESID_F32),
+             ("fc1 +GELU", 3072, 768, ops.EPI_GELU), ("fc2 +resid f32", 768, 3072, ops.EPI_RESID_F32),
+             ("fc2^T *gelu'", 3072, 768, ops.EPI_DGELU), ("fc1^T store", 768, 3072, ops.EPI_STORE)]
+    buf = (ctypes.c_ulonglong * (148 * 8))()
+    for name, N, K, epi in cases:
+        a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+        b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+        bias = torch.randn(N, device="cuda")
+        f32 = epi == ops.EPI_RESID_F32
+        out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
+        out2 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16) if epi == ops.EPI_GELU else None
+        aux = torch.randn(M, N, device="cuda") if f32 else (torch.randn(M, N, device="cuda").to(torch.bfloat16) if epi == ops.EPI_DGELU else None)
+        run = lambda: ops.gemm(a, b, out, bias=bias, epilogue=epi, out2=out2, aux=aux)
+        t = timeit(run, iters=5, warm=2)
+        run()
+        _lib.check(_lib.load().peft_debug_gemm_stats(buf, 148))
+        v = torch.tensor(list(buf), dtype=torch.float64).view(148, 8)
+        lead = v[0::2]
+        tot = float(lead[:, 4].mean())
+        print(f"{name:18s} M={M} N={N} K={K}: {t:7.1f} us | issuer total {tot:9.0f} clk: wait-full {100 * float(lead[:, 2].mean()) / tot:5.1f}% "
+              f"wait-tmem-empty {100 * float(lead[:, 3].mean()) / tot:5.1f}% | producer wait-empty {100 * float((v[:, 0] / v[:, 1]).mean()):5.1f}% | "
+              f"epilogue wait-acc {100 * float((v[:, 5] / v[:, 6]).mean()):5.1f}% | clk/kblock {tot / (((M + 255) // 256) * ((N + 255) // 256) / 74.0 * ((K + 63) // 64)):6.0f}", flush=True)
+
+
+def gemm_scaling_probe():
+    """Per-UMMA pace of the 2-CTA kernel as a function of how many SM pairs are busy: one 256 x 256 tile per cluster with a
+    long K (pure MMA when PEFT_GEMM_DBG=12).  Separates a per-SM limit from a chip-level (power / fabric) limit."""
+    import ctypes
+    _lib.check(_lib.load().peft_set_gemm_algo(2))
+    buf = (ctypes.c_ulonglong * (148 * 8))()
+    K = 16384
+    for clusters in (1, 2, 8, 24, 48, 74):
+        M, N = 256 * clusters, 256
+        a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+        b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+        out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        run = lambda: ops.gemm(a, b, out)
+        t = timeit(run, iters=5, warm=2)
+        run()
+        _lib.check(_lib.load().peft_debug_gemm_stats(buf, 148))
+        v = torch.tensor(list(buf), dtype=torch.float64).view(148, 8)[0:2 * clusters:2]
+        tot = float(v[:, 4].mean())
+        print(f"clusters={clusters:3d} K={K}: {t:7.1f} us  issuer {tot:9.0f} clk  clk/kblock {tot / (K // 64):6.0f}  wait-full {100 * float(v[:, 2].mean()) / tot:5.1f}%  "
+              f"=> {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s, {2.0 * M * N * K / t / 1e6 / clusters:6.2f} per pair", flush=True)
+    _lib.check(_lib.load().peft_set_gemm_algo(0))
+
+
 def bench_gemm_dw(tokens=12800, iters=20):
     """Weight-gradient products of the full mode (C5): out[N_out, K_in] = dY^T X, contraction over the tokens."""
     for name, No, Ki in [("dW qkv", 2304, 768), ("dW proj", 768, 768), ("dW fc1", 3072, 768), ("dW fc2", 768, 3072)]:
@@ -191,9 +241,17 @@ if __name__ == "__main__":
         bench_attn(32, 12, 197)
         bench_ln(6304)
         bench_reduce(6304)
+    if what == "gemm_probe":
+        print("PEFT_GEMM_DBG =", os.environ.get("PEFT_GEMM_DBG", "0"), flush=True)
+        gemm_scaling_probe()
+    if what == "gemm_stats":
+        gemm_stats(50432)
+        gemm_stats(6304)
     if what == "gemm_dbg":    # PEFT_GEMM_DBG diagnostics: plain-store and GELU products only (results are wrong by design)
         print("PEFT_GEMM_DBG =", os.environ.get("PEFT_GEMM_DBG", "0"), flush=True)
         bench_gemm(50432, iters=10, only=(0, 2, 5))
+        if os.environ.get("PEFT_GEMM_STATS"):
+            gemm_stats(50432)
     if what == "prof":      # one pass of each hot kernel, for ncu captures
         bench_gemm(iters=1)
         B, H, L = 256, 12, 197

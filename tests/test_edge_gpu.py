@@ -73,6 +73,48 @@ def test_backward_after_a_later_forward_raises():
         f1.sum().backward()
 
 
+def test_backward_after_a_forward_at_another_batch_size_raises():
+    """the adapter operands the backward reads (K-extension columns of W_qkv, Up^T, Dn) are per ENGINE, not per
+    batch size — a forward at a different batch size with changed adapter weights rewrites them, so the older graph's
+    backward must be refused as well (it would silently use the new weights)."""
+    cfg, sd, names, model = _model()
+    images, _ = synth.make_batch(cfg, 8)
+    f8 = model(images.cuda())
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n in names:
+                p.mul_(1.5)
+    _ = model(images[:4].cuda())
+    with pytest.raises(RuntimeError, match="overwritten"):
+        f8.sum().backward()
+
+
+def test_lora_rank_24_tail_chunk():
+    """rank_pad % 64 == 48 (LoRA r = 24 -> 48 adapter columns) made the engine hand peft_tn_reduce a 48-wide
+    chunk, which the kernel rejects; the tail is now split 32 + 16.  Forward AND backward against the oracle."""
+    cfg = VitCfg(dialect="timm", adapter="lora", lora_r=24, img=64, patch=32, depth=2)
+    sd = synth.make_state_dict(cfg, seed=0, grad_test=True)
+    for k in sd:
+        if "_proj_adapter2" in k:
+            sd[k] = sd[k] * 0.4          # 6x the default rank: keep |delta q| in the range of the r = 4 cases
+    names = synth.trainable_names(cfg, sd)
+    model = build_timm(cfg, sd)
+    for n, p in model.named_parameters():
+        p.requires_grad_(n in names)
+    images, _ = synth.make_batch(cfg, 6)
+    w = torch.randn(6, cfg.feat_dim, generator=torch.Generator().manual_seed(3))
+    feat = model(images.cuda())
+    (feat * w.cuda()).sum().backward()
+    sd_o = {k: v.clone().requires_grad_(k in names) for k, v in sd.items()}
+    rfeat = O.visual_forward(images, sd_o, cfg)
+    (rfeat * w).sum().backward()
+    assert rel(feat, rfeat) < 2e-2
+    params = dict(model.named_parameters())
+    got = torch.cat([params[k].grad.float().cpu().reshape(-1) for k in names])
+    ref = torch.cat([sd_o[k].grad.reshape(-1) for k in names])
+    assert rel(got, ref) < 2e-2, rel(got, ref)
+
+
 def test_frozen_weight_edit_is_picked_up():
     """load_state_dict / in-place edits of a frozen tensor after the first forward re-pack the engine's operands."""
     cfg, sd, names, model = _model()
