@@ -164,17 +164,17 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      for (int g = 0; g < G; ++g) {
-        const int hl = g / TQ, t = g % TQ;
-        const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
-        const int b = bh / H, h = bh % H;
-        if (t == 0) {
-          const int kvb = hl % C::kDqKVBufs, n = hl / C::kDqKVBufs;
-          ptx::mbar_wait(&kv_empty[kvb], (n & 1) ^ 1);
-          uint8_t* sK = sKV + kvb * 2 * C::kHeadBytes;
-          uint8_t* sV = sK + C::kHeadBytes;
+    // ===================== TMA producer (converged warp, elected lane issues) =====================
+    for (int g = 0; g < G; ++g) {
+      const int hl = g / TQ, t = g % TQ;
+      const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
+      const int b = bh / H, h = bh % H;
+      if (t == 0) {
+        const int kvb = hl % C::kDqKVBufs, n = hl / C::kDqKVBufs;
+        ptx::mbar_wait(&kv_empty[kvb], (n & 1) ^ 1);
+        uint8_t* sK = sKV + kvb * 2 * C::kHeadBytes;
+        uint8_t* sV = sK + C::kHeadBytes;
+        if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&kv_full[kvb], 2 * C::kHeadBytes);
 #pragma unroll
           for (int r = 0; r < C::kNKT; r += NKC) {
@@ -182,20 +182,26 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             ptx::tma_load_3d(sV + r * 128, &tmap_kv, &kv_full[kvb], 2 * D + h * 64, r, b);
           }
         }
-        const int qb = g & 1;
-        ptx::mbar_wait(&t_empty[qb], ((g >> 1) & 1) ^ 1);
-        uint8_t* st = sT + qb * 3 * C::kTileBytes;
+        __syncwarp();
+      }
+      const int qb = g & 1;
+      ptx::mbar_wait(&t_empty[qb], ((g >> 1) & 1) ^ 1);
+      uint8_t* st = sT + qb * 3 * C::kTileBytes;
+      if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&t_full[qb], 3 * C::kTileBytes);
         ptx::tma_load_3d(st, &tmap_q, &t_full[qb], h * 64, t * 128, b);
         ptx::tma_load_3d(st + C::kTileBytes, &tmap_do, &t_full[qb], h * 64, t * 128, b);
         ptx::tma_load_3d(st + 2 * C::kTileBytes, &tmap_o, &t_full[qb], h * 64, t * 128, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (converged warp; tcgen05.mma / commit under elect.sync, see attention2_sm100.cuh) ==========
+    {
       constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, NKC);
       constexpr uint32_t idesc_o = ptx::make_idesc_bf16_ex(128, 64, 0, 1);
+      constexpr uint32_t HI = ptx::kDescHiSw128;
+      const uint32_t sT_u32 = ptx::smem_u32(sT), sKV_u32 = ptx::smem_u32(sKV);
       uint32_t n = 0;
       for (int g = 0; g < G; ++g) {
         const int hl = g / TQ, t = g % TQ;
@@ -203,20 +209,22 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         if (t == 0) ptx::mbar_wait(&kv_full[kvb], (hl / C::kDqKVBufs) & 1);
         ptx::mbar_wait(&t_full[qb], (g >> 1) & 1);
         ptx::tcgen05_fence_after();
-        const uint32_t sq = ptx::smem_u32(sT + qb * 3 * C::kTileBytes);
+        const uint32_t sq = sT_u32 + qb * 3 * C::kTileBytes;
         const uint32_t sdo = sq + C::kTileBytes;
-        const uint32_t sk0 = ptx::smem_u32(sKV + kvb * 2 * C::kHeadBytes);
+        const uint32_t sk0 = sKV_u32 + kvb * 2 * C::kHeadBytes;
         const uint32_t sv0 = sk0 + C::kHeadBytes;
 #pragma unroll 1
         for (int kc = 0; kc < NCH; ++kc) {
           const uint32_t sk = sk0 + kc * NKC * 128, sv = sv0 + kc * NKC * 128;
+          if (ptx::elect_one()) {
+            const uint32_t q_lo = ptx::desc_lo(sq), k_lo = ptx::desc_lo(sk), do_lo = ptx::desc_lo(sdo), v_lo = ptx::desc_lo(sv);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tmem_base, ptx::make_smem_desc_sw128(sq) + 2 * k, ptx::make_smem_desc_sw128(sk) + 2 * k, idesc_s, k != 0);
+            for (int k = 0; k < 4; ++k) ptx::umma_bf16_ss_lohi(tmem_base, q_lo + 2 * k, k_lo + 2 * k, HI, idesc_s, k != 0);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tmem_base + NKC, ptx::make_smem_desc_sw128(sdo) + 2 * k, ptx::make_smem_desc_sw128(sv) + 2 * k, idesc_s, k != 0);
-          ptx::umma_commit(sdp_ready);
+            for (int k = 0; k < 4; ++k) ptx::umma_bf16_ss_lohi(tmem_base + NKC, do_lo + 2 * k, v_lo + 2 * k, HI, idesc_s, k != 0);
+            ptx::umma_commit(sdp_ready);
+          }
+          __syncwarp();
           ptx::mbar_wait(ds_ready, n & 1);
           ++n;
           ptx::tcgen05_fence_after();
@@ -224,14 +232,21 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             ptx::mbar_wait(dq_free, (g & 1) ^ 1);
             ptx::tcgen05_fence_after();
           }
+          if (ptx::elect_one()) {
+            const uint32_t k_lo = ptx::desc_lo(sk);
 #pragma unroll
-          for (int j = 0; j < NKC / 16; ++j)
-            ptx::umma_bf16_ts(tmem_base + 2 * NKC, tmem_base + bwd_pcol<NKC, NCH>(j), ptx::make_smem_desc_sw128_mn(sk + j * 2048),
-                              idesc_o, (kc | j) != 0 ? 1u : 0u);
+            for (int j = 0; j < NKC / 16; ++j)
+              ptx::umma_bf16_ts_lohi(tmem_base + 2 * NKC, tmem_base + bwd_pcol<NKC, NCH>(j), k_lo + j * (2048 >> 4), HI, idesc_o,
+                                     (kc | j) != 0 ? 1u : 0u);
+          }
+          __syncwarp();
         }
-        ptx::umma_commit(dq_ready);
-        ptx::umma_commit(&t_empty[qb]);
-        if (t == TQ - 1) ptx::umma_commit(&kv_empty[kvb]);
+        if (ptx::elect_one()) {
+          ptx::umma_commit(dq_ready);
+          ptx::umma_commit(&t_empty[qb]);
+          if (t == TQ - 1) ptx::umma_commit(&kv_empty[kvb]);
+        }
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {
@@ -396,17 +411,17 @@ attn2_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      for (int g = 0; g < G; ++g) {
-        const int hl = g / TK, j = g % TK;
-        const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
-        const int b = bh / H, h = bh % H;
-        if (j == 0) {
-          const int qdb = hl % C::kDkvQDBufs, n = hl / C::kDkvQDBufs;
-          ptx::mbar_wait(&qd_empty[qdb], (n & 1) ^ 1);
-          uint8_t* sQ = sQD + qdb * 2 * C::kHeadBytes;
-          uint8_t* sdO = sQ + C::kHeadBytes;
+    // ===================== TMA producer (converged warp, elected lane issues) =====================
+    for (int g = 0; g < G; ++g) {
+      const int hl = g / TK, j = g % TK;
+      const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
+      const int b = bh / H, h = bh % H;
+      if (j == 0) {
+        const int qdb = hl % C::kDkvQDBufs, n = hl / C::kDkvQDBufs;
+        ptx::mbar_wait(&qd_empty[qdb], (n & 1) ^ 1);
+        uint8_t* sQ = sQD + qdb * 2 * C::kHeadBytes;
+        uint8_t* sdO = sQ + C::kHeadBytes;
+        if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&qd_full[qdb], 2 * C::kHeadBytes);
 #pragma unroll
           for (int r = 0; r < C::kNKT; r += NKC) {
@@ -414,19 +429,25 @@ attn2_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
             ptx::tma_load_3d(sdO + r * 128, &tmap_do, &qd_full[qdb], h * 64, r, b);
           }
         }
-        const int kb = g & 1;
-        ptx::mbar_wait(&t_empty[kb], ((g >> 1) & 1) ^ 1);
-        uint8_t* st = sT + kb * 2 * C::kTileBytes;
+        __syncwarp();
+      }
+      const int kb = g & 1;
+      ptx::mbar_wait(&t_empty[kb], ((g >> 1) & 1) ^ 1);
+      uint8_t* st = sT + kb * 2 * C::kTileBytes;
+      if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&t_full[kb], 2 * C::kTileBytes);
         ptx::tma_load_3d(st, &tmap_kt, &t_full[kb], D + h * 64, j * 128, b);
         ptx::tma_load_3d(st + C::kTileBytes, &tmap_kt, &t_full[kb], 2 * D + h * 64, j * 128, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (converged warp; tcgen05.mma / commit under elect.sync) =====================
+    {
       constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, NKC);
       constexpr uint32_t idesc_o = ptx::make_idesc_bf16_ex(128, 64, 0, 1);
+      constexpr uint32_t HI = ptx::kDescHiSw128;
+      const uint32_t sT_u32 = ptx::smem_u32(sT), sQD_u32 = ptx::smem_u32(sQD);
       uint32_t n = 0;
       for (int g = 0; g < G; ++g) {
         const int hl = g / TK, j = g % TK;
@@ -435,34 +456,43 @@ attn2_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
         ptx::mbar_wait(&t_full[kb], (g >> 1) & 1);
         ptx::mbar_wait(out_free, (g & 1) ^ 1);          // the previous tile's dK / dV accumulators have been read out
         ptx::tcgen05_fence_after();
-        const uint32_t skj = ptx::smem_u32(sT + kb * 2 * C::kTileBytes);
+        const uint32_t skj = sT_u32 + kb * 2 * C::kTileBytes;
         const uint32_t svj = skj + C::kTileBytes;
-        const uint32_t sq0 = ptx::smem_u32(sQD + qdb * 2 * C::kHeadBytes);
+        const uint32_t sq0 = sQD_u32 + qdb * 2 * C::kHeadBytes;
         const uint32_t sdo0 = sq0 + C::kHeadBytes;
 #pragma unroll 1
         for (int qc = 0; qc < NCH; ++qc) {
           const uint32_t sq = sq0 + qc * NKC * 128, sdo = sdo0 + qc * NKC * 128;
+          if (ptx::elect_one()) {
+            const uint32_t k_lo = ptx::desc_lo(skj), q_lo = ptx::desc_lo(sq), v_lo = ptx::desc_lo(svj), do_lo = ptx::desc_lo(sdo);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tmem_base, ptx::make_smem_desc_sw128(skj) + 2 * k, ptx::make_smem_desc_sw128(sq) + 2 * k, idesc_s, k != 0);
+            for (int k = 0; k < 4; ++k) ptx::umma_bf16_ss_lohi(tmem_base, k_lo + 2 * k, q_lo + 2 * k, HI, idesc_s, k != 0);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tmem_base + NKC, ptx::make_smem_desc_sw128(svj) + 2 * k, ptx::make_smem_desc_sw128(sdo) + 2 * k, idesc_s, k != 0);
-          ptx::umma_commit(sdp_ready);
+            for (int k = 0; k < 4; ++k) ptx::umma_bf16_ss_lohi(tmem_base + NKC, v_lo + 2 * k, do_lo + 2 * k, HI, idesc_s, k != 0);
+            ptx::umma_commit(sdp_ready);
+          }
+          __syncwarp();
           ptx::mbar_wait(pds_ready, n & 1);
           ++n;
           ptx::tcgen05_fence_after();
+          if (ptx::elect_one()) {
+            const uint32_t q_lo = ptx::desc_lo(sq), do_lo = ptx::desc_lo(sdo);
 #pragma unroll
-          for (int jj = 0; jj < NKC / 16; ++jj) {
-            const uint32_t pc = bwd_pcol<NKC, NCH>(jj);
-            const uint32_t acc = (qc | jj) != 0 ? 1u : 0u;
-            ptx::umma_bf16_ts(tmem_base + C::kDvCol, tmem_base + pc, ptx::make_smem_desc_sw128_mn(sdo + jj * 2048), idesc_o, acc);
-            ptx::umma_bf16_ts(tmem_base + C::kDkCol, tmem_base + NKC + pc, ptx::make_smem_desc_sw128_mn(sq + jj * 2048), idesc_o, acc);
+            for (int jj = 0; jj < NKC / 16; ++jj) {
+              const uint32_t pc = bwd_pcol<NKC, NCH>(jj);
+              const uint32_t acc = (qc | jj) != 0 ? 1u : 0u;
+              ptx::umma_bf16_ts_lohi(tmem_base + C::kDvCol, tmem_base + pc, do_lo + jj * (2048 >> 4), HI, idesc_o, acc);
+              ptx::umma_bf16_ts_lohi(tmem_base + C::kDkCol, tmem_base + NKC + pc, q_lo + jj * (2048 >> 4), HI, idesc_o, acc);
+            }
           }
+          __syncwarp();
         }
-        ptx::umma_commit(out_ready);
-        ptx::umma_commit(&t_empty[kb]);
-        if (j == TK - 1) ptx::umma_commit(&qd_empty[qdb]);
+        if (ptx::elect_one()) {
+          ptx::umma_commit(out_ready);
+          ptx::umma_commit(&t_empty[kb]);
+          if (j == TK - 1) ptx::umma_commit(&qd_empty[qdb]);
+        }
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {

@@ -44,6 +44,37 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
       "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// ---- descriptor-by-halves forms: {lo = (addr >> 4) | LBO field 1, hi = SBO 1024 B | version 1 | SWIZZLE_128B}; K-major tiles
+// advance lo by 2 per 16-element K step, MN-major tiles by 128 (2 KB) — 32-bit uniform-datapath arithmetic only
+constexpr uint32_t kDescHiSw128 = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16); }
+__device__ __forceinline__ void umma_bf16_ss_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b64 da, db;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "mov.b64 da, {%1, %3};\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ts_lohi(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b64 db;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -206,17 +237,17 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      for (int g = 0; g < G; ++g) {
-        const int hl = g / TQ, t = g % TQ;
-        const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
-        const int b = bh / H, h = bh % H;
-        if (t == 0) {
-          const int kvb = hl & 1;
-          ptx::mbar_wait(&kv_empty[kvb], ((hl >> 1) & 1) ^ 1);
-          uint8_t* sK = sKV + kvb * 2 * C::kKVBytes;
-          uint8_t* sV = sK + C::kKVBytes;
+    // ===================== TMA producer (converged warp, elected lane issues) =====================
+    for (int g = 0; g < G; ++g) {
+      const int hl = g / TQ, t = g % TQ;
+      const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
+      const int b = bh / H, h = bh % H;
+      if (t == 0) {
+        const int kvb = hl & 1;
+        ptx::mbar_wait(&kv_empty[kvb], ((hl >> 1) & 1) ^ 1);
+        uint8_t* sK = sKV + kvb * 2 * C::kKVBytes;
+        uint8_t* sV = sK + C::kKVBytes;
+        if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&kv_full[kvb], 2 * C::kKVBytes);
 #pragma unroll
           for (int r = 0; r < NK; r += C::kKVBox) {
@@ -224,30 +255,41 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::tma_load_3d(sV + r * 128, &tmap_kv, &kv_full[kvb], 2 * D + h * 64, r, b);
           }
         }
-        const int qb = g & 1;
-        ptx::mbar_wait(&q_empty[qb], ((g >> 1) & 1) ^ 1);
+        __syncwarp();
+      }
+      const int qb = g & 1;
+      ptx::mbar_wait(&q_empty[qb], ((g >> 1) & 1) ^ 1);
+      if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&q_full[qb], C::kQBytes);
         ptx::tma_load_3d(sQ + qb * C::kQBytes, &tmap_q, &q_full[qb], h * 64, t * 128, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // The warp runs converged; only the tcgen05.mma / commit instructions sit under elect.sync, so that their descriptors are
+    // warp-uniform values in uniform registers (a loop inside `if (lane == 0)` costs an R2UR waterfall of ~25 dependent
+    // scalar instructions per MMA, several times the 32-clk cost of a 128 x 64 x 16 P.V step).
+    {
       constexpr uint32_t idesc_pv = ptx::make_idesc_bf16_ex(128, 64, 0, 1);
+      const uint32_t sKV_u32 = ptx::smem_u32(sKV), sQ_u32 = ptx::smem_u32(sQ);
       auto issue_pv = [&](int g) {
         const int hl = g / TQ, t = g % TQ;
         const int kvb = hl & 1;
         const int buf = g % C::kBufs;
         ptx::mbar_wait(&p_ready[g & 1], (g >> 1) & 1);
         ptx::tcgen05_fence_after();
-        const uint32_t sV = ptx::smem_u32(sKV + kvb * 2 * C::kKVBytes + C::kKVBytes);
+        const uint32_t sV = sKV_u32 + kvb * 2 * C::kKVBytes + C::kKVBytes;
         const uint32_t tbuf = tmem_base + (uint32_t)(buf * C::kBufCols);
+        if (ptx::elect_one()) {
+          const uint32_t v_lo = ptx::desc_lo(sV);
 #pragma unroll
-        for (int j = 0; j < NK / 16; ++j)
-          ptx::umma_bf16_ts(tbuf + C::kOOff, tbuf + 8 * j, ptx::make_smem_desc_sw128_mn(sV + j * 2048), idesc_pv,
-                            j != 0 ? 1u : 0u);
-        ptx::umma_commit(&o_ready[g & 1]);
-        if (t == TQ - 1) ptx::umma_commit(&kv_empty[kvb]);
+          for (int j = 0; j < NK / 16; ++j)
+            ptx::umma_bf16_ts_lohi(tbuf + C::kOOff, tbuf + 8 * j, v_lo + j * (2048 >> 4), ptx::kDescHiSw128, idesc_pv, j != 0 ? 1u : 0u);
+          ptx::umma_commit(&o_ready[g & 1]);
+          if (t == TQ - 1) ptx::umma_commit(&kv_empty[kvb]);
+        }
+        __syncwarp();
       };
       for (int g = 0; g < G; ++g) {
         const int hl = g / TQ, t = g % TQ;
@@ -262,27 +304,31 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           if (g >= 1) ptx::mbar_wait(&buf_free[(g - 1) & 1], ((g - 1) >> 1) & 1);
         }
         ptx::tcgen05_fence_after();
-        const uint32_t sq = ptx::smem_u32(sQ + qb * C::kQBytes);
-        const uint32_t sk = ptx::smem_u32(sKV + kvb * 2 * C::kKVBytes);
+        const uint32_t sq = sQ_u32 + qb * C::kQBytes;
+        const uint32_t sk = sKV_u32 + kvb * 2 * C::kKVBytes;
         const uint32_t tbuf = tmem_base + (uint32_t)(buf * C::kBufCols);
-        if constexpr (NK <= 256) {
-          constexpr uint32_t idesc = ptx::make_idesc_bf16(128, NK);
+        if (ptx::elect_one()) {
+          const uint32_t q_lo = ptx::desc_lo(sq), k_lo = ptx::desc_lo(sk);
+          if constexpr (NK <= 256) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(128, NK);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tbuf, ptx::make_smem_desc_sw128(sq) + 2 * k, ptx::make_smem_desc_sw128(sk) + 2 * k, idesc, k != 0);
-        } else {
-          constexpr int N0 = 144, N1 = NK - 144;
-          constexpr uint32_t idesc0 = ptx::make_idesc_bf16(128, N0), idesc1 = ptx::make_idesc_bf16(128, N1);
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_bf16_ss_lohi(tbuf, q_lo + 2 * k, k_lo + 2 * k, ptx::kDescHiSw128, idesc, k != 0);
+          } else {
+            constexpr int N0 = 144, N1 = NK - 144;
+            constexpr uint32_t idesc0 = ptx::make_idesc_bf16(128, N0), idesc1 = ptx::make_idesc_bf16(128, N1);
+            const uint32_t k1_lo = ptx::desc_lo(sk + N0 * 128);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tbuf, ptx::make_smem_desc_sw128(sq) + 2 * k, ptx::make_smem_desc_sw128(sk) + 2 * k, idesc0, k != 0);
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_bf16_ss_lohi(tbuf, q_lo + 2 * k, k_lo + 2 * k, ptx::kDescHiSw128, idesc0, k != 0);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::umma_bf16(tbuf + N0, ptx::make_smem_desc_sw128(sq) + 2 * k, ptx::make_smem_desc_sw128(sk + N0 * 128) + 2 * k,
-                           idesc1, k != 0);
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_bf16_ss_lohi(tbuf + N0, q_lo + 2 * k, k1_lo + 2 * k, ptx::kDescHiSw128, idesc1, k != 0);
+          }
+          ptx::umma_commit(&q_empty[qb]);
+          ptx::umma_commit(&s_ready[g & 1]);
         }
-        ptx::umma_commit(&q_empty[qb]);
-        ptx::umma_commit(&s_ready[g & 1]);
+        __syncwarp();
         if constexpr (C::kBufs == 2) {
           if (g >= 1) issue_pv(g - 1);
         } else {

@@ -260,8 +260,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   const int num_kb = (p.K + kBK - 1) / kBK;
 
   if (warp == 0) {
-    // ===================== TMA producer (one lane) =====================
-    if (lane == 0) {
+    // ===================== TMA producer (converged warp; the elected lane issues) =====================
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -270,21 +270,28 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = tiles + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          ptx::mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
-          ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kBK, n_blk * BN);
+          if (ptx::elect_one_sync()) {
+            ptx::mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
+            ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kBK, n_blk * BN);
+          }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one lane) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (converged warp; tcgen05.mma / commit under elect.sync) =====================
+    // Every lane walks the loop so that the descriptors are warp-uniform values held in uniform registers; a loop under
+    // `if (lane == 0)` makes the compiler move them through an R2UR waterfall (~25 dependent instructions per MMA).
+    {
       constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN);
+      constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B | version 1 | SWIZZLE_128B
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      const uint32_t tiles_u32 = ptx::smem_u32(tiles);
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         ptx::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         ptx::tcgen05_fence_after();
@@ -292,20 +299,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tcgen05_fence_after();
-          const uint32_t sa = ptx::smem_u32(tiles + stage * Cfg::kStageBytes);
-          const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
-          const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + Cfg::kABytes);
+          const uint32_t sa = tiles_u32 + stage * Cfg::kStageBytes;
+          const uint32_t a_lo = ((sa & 0x3FFFFu) >> 4) | (1u << 16);
+          const uint32_t b_lo = (((sa + Cfg::kABytes) & 0x3FFFFu) >> 4) | (1u << 16);
           const int krem = p.K - kb * kBK;
           const int ksteps = krem >= kBK ? (kBK / 16) : ((krem + 15) / 16);
-          for (int k = 0; k < ksteps; ++k) {
-            // advance 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-            ptx::umma_bf16(tmem_d, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k), idesc,
-                           (kb | k) != 0 ? 1u : 0u);
+          if (ptx::elect_one_sync()) {
+            // advance 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field of the low word
+            ptx::umma_kblock_bf16(tmem_d, a_lo, b_lo, kDescHi, idesc, kb != 0 ? 1u : 0u, ksteps);
+            ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
           }
-          ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
+        if (ptx::elect_one_sync()) ptx::umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
+        __syncwarp();
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }

@@ -126,6 +126,53 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(2) << 61;                            // layout type: SWIZZLE_128B
   return d;
 }
+// true in exactly one lane of the (fully active) warp — always the same lane, so tcgen05.commit tracks the MMAs it issued
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.b32 %0, 1, 0, P;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+// One 64-wide k-block (1-CTA): up to four tcgen05.mma (K = 16) whose descriptors differ by +2 in the low word per K-step.
+__device__ __forceinline__ void umma_kblock_bf16(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                                 uint32_t acc_first, int ksteps) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p0, p1, p2, p3, pt;\n"
+      ".reg .b64 da, db;\n"
+      ".reg .b32 al, bl;\n"
+      "setp.ne.b32 p0, %5, 0;\n"
+      "setp.gt.s32 p1, %6, 1;\n"
+      "setp.gt.s32 p2, %6, 2;\n"
+      "setp.gt.s32 p3, %6, 3;\n"
+      "setp.eq.u32 pt, %6, %6;\n"
+      "mov.b64 da, {%1, %3};\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p0;\n"
+      "add.u32 al, %1, 2;\n"
+      "add.u32 bl, %2, 2;\n"
+      "mov.b64 da, {al, %3};\n"
+      "mov.b64 db, {bl, %3};\n"
+      "@p1 tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, pt;\n"
+      "add.u32 al, %1, 4;\n"
+      "add.u32 bl, %2, 4;\n"
+      "mov.b64 da, {al, %3};\n"
+      "mov.b64 db, {bl, %3};\n"
+      "@p2 tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, pt;\n"
+      "add.u32 al, %1, 6;\n"
+      "add.u32 bl, %2, 6;\n"
+      "mov.b64 da, {al, %3};\n"
+      "mov.b64 db, {bl, %3};\n"
+      "@p3 tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, pt;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(acc_first), "r"(ksteps)
+      : "memory");
+}
 // Instruction descriptor, kind::f16: D=f32, A=B=bf16, both K-major, dense.
 __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t M, uint32_t N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
