@@ -237,6 +237,82 @@ __device__ __forceinline__ float fast_dgelu_tanh(float x) {
   return fmaf(0.5f * x * (1.0f - t * t), du, fmaf(0.5f, t, 0.5f));
 }
 
+// ---- packed fp32 arithmetic (sm_100 FFMA2 / FMUL2 / FADD2: two fp32 lanes per instruction, full precision).  The epilogues
+// of the activation products are issue-bound with two warps per scheduler, so halving the FP instruction count is what
+// brings the per-tile epilogue under the per-tile MMA time (r02: fc1+GELU 18 -> ~9 instructions per element).
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("{\n.reg .b64 ra, rb, rc, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmov.b64 rc, {%6, %7};\n"
+      "fma.rn.f32x2 rd, ra, rb, rc;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return d;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n.reg .b64 ra, rb, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmul.rn.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n.reg .b64 ra, rb, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nadd.rn.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 splat2(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float2 tanh2(float2 u) { return make_float2(ptx::tanh_approx(u.x), ptx::tanh_approx(u.y)); }
+
+// gelu_erf(x) ~ x (0.5 + 0.5 tanh(u)), u = x q(min(x^2, 50)) — the same fit as phi_u, one MUFU per element
+__device__ __forceinline__ float2 gelu_u2(float2 x, float2& s) {
+  s = mul2(x, x);
+  s.x = fminf(s.x, 50.0f);
+  s.y = fminf(s.y, 50.0f);
+  const float2 q = fma2(s, fma2(s, splat2(-3.53110710e-4f), splat2(3.70155061e-2f)), splat2(7.97496957e-1f));
+  return mul2(x, q);
+}
+__device__ __forceinline__ float2 gelu_erf2(float2 x) {
+  float2 s;
+  const float2 t = tanh2(gelu_u2(x, s));
+  const float2 hx = mul2(x, splat2(0.5f));
+  return fma2(hx, t, hx);
+}
+// exact derivative of the fitted function above (so backward differentiates what forward evaluated):
+// d/dx = 0.5 + 0.5 t + 0.5 x (1 - t^2) u'(x),  u' = q + 2 s q'(s) = c0 + 3 c1 s + 5 c2 s^2  (in the clamped range 1 - t^2 = 0)
+__device__ __forceinline__ float2 dgelu_erf2(float2 x) {
+  float2 s;
+  const float2 t = tanh2(gelu_u2(x, s));
+  const float2 du = fma2(s, fma2(s, splat2(5.0f * -3.53110710e-4f), splat2(3.0f * 3.70155061e-2f)), splat2(7.97496957e-1f));
+  const float2 omt = fma2(mul2(t, splat2(-1.0f)), t, splat2(1.0f));
+  const float2 z = mul2(mul2(x, splat2(0.5f)), du);
+  return fma2(z, omt, fma2(t, splat2(0.5f), splat2(0.5f)));
+}
+// x sigmoid(1.702 x) = x (0.5 + 0.5 tanh(0.851 x))
+__device__ __forceinline__ float2 quickgelu2(float2 x) {
+  const float2 t = tanh2(mul2(x, splat2(0.851f)));
+  const float2 hx = mul2(x, splat2(0.5f));
+  return fma2(hx, t, hx);
+}
+// sigma + 1.702 x sigma (1 - sigma), sigma = 0.5 + 0.5 t:  sigma (1 - sigma) = 0.25 (1 - t^2)
+__device__ __forceinline__ float2 dquickgelu2(float2 x) {
+  const float2 t = tanh2(mul2(x, splat2(0.851f)));
+  const float2 omt = fma2(mul2(t, splat2(-1.0f)), t, splat2(1.0f));
+  return fma2(mul2(x, splat2(0.25f * 1.702f)), omt, fma2(t, splat2(0.5f), splat2(0.5f)));
+}
+// gelu_new: 0.5 x (1 + tanh(x (0.79788 + 0.035677 x^2)))
+__device__ __forceinline__ float2 gelu_tanh2(float2 x) {
+  const float2 s = mul2(x, x);
+  const float2 t = tanh2(mul2(x, fma2(s, splat2(0.7978845608028654f * 0.044715f), splat2(0.7978845608028654f))));
+  const float2 hx = mul2(x, splat2(0.5f));
+  return fma2(hx, t, hx);
+}
+__device__ __forceinline__ float2 dgelu_tanh2(float2 x) {
+  const float2 s = mul2(x, x);
+  const float2 t = tanh2(mul2(x, fma2(s, splat2(0.7978845608028654f * 0.044715f), splat2(0.7978845608028654f))));
+  const float2 du = fma2(s, splat2(3.0f * 0.7978845608028654f * 0.044715f), splat2(0.7978845608028654f));
+  const float2 omt = fma2(mul2(t, splat2(-1.0f)), t, splat2(1.0f));
+  return fma2(mul2(mul2(x, splat2(0.5f)), du), omt, fma2(t, splat2(0.5f), splat2(0.5f)));
+}
+
 template <int EPI>
 struct EpiTraits {
   static constexpr bool kF32Out = (EPI == EPI_RESID_F32 || EPI == EPI_STORE_F32);
@@ -465,7 +541,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       for (int u = 0; u < T::kUnits; ++u) {
         const int s = u & 1;
         const int colu = col0 + u * T::kUnitCols;
-        float v[T::kUnitCols];
+        constexpr int NP = T::kUnitCols / 2;     // the unit as fp32 PAIRS: all arithmetic below is packed (FFMA2 / FMUL2 / FADD2)
+        float2 v[NP];
         {
           uint32_t r[32];
           ptx::tmem_ld_32x32b_x32(taddr0 + u * T::kUnitCols, r);
@@ -474,11 +551,14 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             ptx::tmem_ld_32x32b_x32(taddr0 + u * T::kUnitCols + 32, r2);
             ptx::tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r[j]); v[32 + j] = __uint_as_float(r2[j]); }
+            for (int j = 0; j < 16; ++j) {
+              v[j] = make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+              v[16 + j] = make_float2(__uint_as_float(r2[2 * j]), __uint_as_float(r2[2 * j + 1]));
+            }
           } else {
             ptx::tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            for (int j = 0; j < 16; ++j) v[j] = make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
           }
         }
         if (u == T::kUnits - 1) {
@@ -491,23 +571,26 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         if (p.bias != nullptr) {
           if (colu + T::kUnitCols <= p.N) {
 #pragma unroll
-            for (int j = 0; j < T::kUnitCols; j += 4) {
-              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + colu + j));
-              v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+            for (int j = 0; j < NP; j += 2) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + colu + 2 * j));
+              v[j] = add2(v[j], make_float2(b.x, b.y));
+              v[j + 1] = add2(v[j + 1], make_float2(b.z, b.w));
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < T::kUnitCols; ++j)
-              if (colu + j < p.N) v[j] += __ldg(p.bias + colu + j);
+            for (int j = 0; j < NP; ++j) {
+              if (colu + 2 * j < p.N) v[j].x += __ldg(p.bias + colu + 2 * j);
+              if (colu + 2 * j + 1 < p.N) v[j].y += __ldg(p.bias + colu + 2 * j + 1);
+            }
           }
         }
         // stochastic-depth row scale, lane = row (re-read per unit: no register held across units); only the epilogues the
         // engine uses it with are compiled with it (the host rejects the others)
         if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE || EPI == EPI_DGELU || EPI == EPI_DQUICKGELU)
         if (p.rowscale != nullptr) {
-          const float rs = (row0 + lane < p.M) ? __ldg(p.rowscale + row0 + lane) : 0.0f;
+          const float2 rs = splat2((row0 + lane < p.M) ? __ldg(p.rowscale + row0 + lane) : 0.0f);
 #pragma unroll
-          for (int j = 0; j < T::kUnitCols; ++j) v[j] *= rs;
+          for (int j = 0; j < NP; ++j) v[j] = mul2(v[j], rs);
         }
         // ---- slot availability / auxiliary operand
         if constexpr (T::kAux) {
@@ -517,7 +600,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 a = *reinterpret_cast<const float4*>(slot_ptr(s) + slot_off(lane, j));
-              v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+              v[2 * j] = add2(v[2 * j], make_float2(a.x, a.y));
+              v[2 * j + 1] = add2(v[2 * j + 1], make_float2(a.z, a.w));
             }
           } else {
 #pragma unroll
@@ -527,52 +611,61 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
                 const float2 h = ptx::unpack_bf16x2(au[q]);
-                float& v0 = v[8 * j + 2 * q];
-                float& v1 = v[8 * j + 2 * q + 1];
-                if constexpr (EPI == EPI_DGELU) { v0 *= fast_dgelu_erf(h.x); v1 *= fast_dgelu_erf(h.y); }
-                if constexpr (EPI == EPI_DQUICKGELU) { v0 *= fast_dquickgelu(h.x); v1 *= fast_dquickgelu(h.y); }
-                if constexpr (EPI == EPI_DGELU_TANH) { v0 *= fast_dgelu_tanh(h.x); v1 *= fast_dgelu_tanh(h.y); }
-                if constexpr (EPI == EPI_DRELU) { v0 = h.x > 0.f ? v0 : 0.f; v1 = h.y > 0.f ? v1 : 0.f; }
-                if constexpr (EPI == EPI_RESID_BF16) { v0 += h.x; v1 += h.y; }
+                float2& vv = v[4 * j + q];
+                if constexpr (EPI == EPI_DGELU) vv = mul2(vv, dgelu_erf2(h));
+                if constexpr (EPI == EPI_DQUICKGELU) vv = mul2(vv, dquickgelu2(h));
+                if constexpr (EPI == EPI_DGELU_TANH) vv = mul2(vv, dgelu_tanh2(h));
+                if constexpr (EPI == EPI_DRELU) { vv.x = h.x > 0.f ? vv.x : 0.f; vv.y = h.y > 0.f ? vv.y : 0.f; }
+                if constexpr (EPI == EPI_RESID_BF16) vv = add2(vv, h);
               }
             }
           }
           __syncwarp();   // every lane has read its aux row before anyone overwrites the slot
         } else if constexpr (T::kDual) {
-          if (lane == 0) ptx::bulk_wait_read<0>();   // both slots are rewritten by this unit
-          __syncwarp();
+          if (lane == 0) ptx::bulk_wait_read<1>();   // slot 0's previous store (h of the previous unit) has been read; the
+          __syncwarp();                              // activation store issued after it may still be draining slot 1
         } else {
           if (lane == 0) ptx::bulk_wait_read<1>();   // the store issued two units ago (same slot) has been read
           __syncwarp();
         }
         if constexpr (EPI == EPI_RELU) {
 #pragma unroll
-          for (int j = 0; j < T::kUnitCols; ++j) v[j] = fmaxf(v[j], 0.f);
+          for (int j = 0; j < NP; ++j) { v[j].x = fmaxf(v[j].x, 0.f); v[j].y = fmaxf(v[j].y, 0.f); }
         }
         // ---- registers -> swizzled slot
         if constexpr (T::kF32Out) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(slot_ptr(s) + slot_off(lane, j)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            *reinterpret_cast<float4*>(slot_ptr(s) + slot_off(lane, j)) = make_float4(v[2 * j].x, v[2 * j].y, v[2 * j + 1].x, v[2 * j + 1].y);
         } else {
           uint8_t* dst = T::kDual ? slot_ptr(0) : slot_ptr(s);
           uint32_t pk[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) pk[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
+          for (int j = 0; j < 32; ++j) pk[j] = ptx::pack_bf16x2(v[j].x, v[j].y);
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *reinterpret_cast<uint4*>(dst + slot_off(lane, j)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
           if constexpr (T::kDual) {
-            // activation of the bf16-ROUNDED pre-activation: backward differentiates exactly what forward evaluated
+            // the pre-activation store leaves now, so that its shared-memory read drains under the activation math
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && !(p.dbg & 16)) {
+              ptx::tma_store_2d(&tmap_out, slot_ptr(0), colu, row0);
+              ptx::bulk_commit();
+            }
+            // the activation is evaluated on the fp32 pre-activation (its bf16 copy goes to `out` for the backward pass: the
+            // two differ by one bf16 rounding of h, 2^-9 relative, far inside the activation's own bf16 output rounding)
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              const float2 h = ptx::unpack_bf16x2(pk[j]);
-              float a0, a1;
-              if constexpr (EPI == EPI_GELU) { a0 = fast_gelu_erf(h.x); a1 = fast_gelu_erf(h.y); }
-              else if constexpr (EPI == EPI_QUICKGELU) { a0 = fast_quickgelu(h.x); a1 = fast_quickgelu(h.y); }
-              else { a0 = fast_gelu_tanh(h.x); a1 = fast_gelu_tanh(h.y); }
-              pk[j] = ptx::pack_bf16x2(a0, a1);
+              float2 a;
+              if (p.dbg & 32) { pk[j] = ptx::pack_bf16x2(v[j].y, v[j].x); continue; }   // diagnostic: no activation math
+              if constexpr (EPI == EPI_GELU) a = gelu_erf2(v[j]);
+              else if constexpr (EPI == EPI_QUICKGELU) a = quickgelu2(v[j]);
+              else a = gelu_tanh2(v[j]);
+              pk[j] = ptx::pack_bf16x2(a.x, a.y);
             }
+            if (lane == 0) ptx::bulk_wait_read<1>();   // slot 1's previous store has been read (only the h store above is younger)
+            __syncwarp();
 #pragma unroll
             for (int j = 0; j < 8; ++j)
               *reinterpret_cast<uint4*>(slot_ptr(1) + slot_off(lane, j)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
@@ -581,8 +674,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          if constexpr (T::kDual) {
-            ptx::tma_store_2d(&tmap_out, slot_ptr(0), colu, row0);
+          if (p.dbg & 16) {                          // diagnostic: no output stores
+          } else if constexpr (T::kDual) {
             ptx::tma_store_2d(&tmap_out2, slot_ptr(1), colu, row0);
           } else if (EPI == EPI_STORE_F32 && ksplit > 1) {
             ptx::tma_reduce_add_2d(&tmap_out, slot_ptr(s), colu, row0);

@@ -52,7 +52,7 @@ struct GemmParams {
                       // epilogue — the per-sample stochastic-depth keep mask / keep_prob of DropPath (FS/kadaptation.py:263,276-277)
   unsigned long long* stats = nullptr;   // diagnostics (env PEFT_GEMM_STATS=1): per-CTA wait-cycle counters, see peft_debug_gemm_stats
   int dbg = 0;        // diagnostics (env PEFT_GEMM_DBG, results are WRONG when set; bench_ops.py gemm_dbg): bit 0 = no B-operand
-                      // loads, bit 1 = every tile loads the operands of tile 0, bit 2 = epilogue only drains TMEM (no math / stores), bit 3 = no operand loads at all
+                      // loads, bit 1 = every tile loads the operands of tile 0, bit 2 = epilogue only drains TMEM (no math / stores), bit 3 = no operand loads at all, bit 4 = no output stores, bit 5 = no activation math
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
