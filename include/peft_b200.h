@@ -47,6 +47,10 @@ unsigned long long peft_kernel_count(int kind);
 /* tuning / test knob: which tensor-core GEMM kernel peft_gemm_bf16 uses — 0 = automatic (2-CTA cta_group::2 kernel when
  * the problem fills the 74 SM pairs, else the 1-CTA kernel), 1 = always 1-CTA, 2 = always 2-CTA. */
 int peft_set_gemm_algo(int algo);
+/* stream-K scheduling of the 2-CTA GEMM (long contractions whose tile count leaves the last wave mostly empty, e.g. 75 tiles
+ * on 74 SM pairs at M = 6304): 0 = off, 1 = automatic (default), 2 = whenever the shape allows it (tests).  Partial tiles
+ * travel through ONE per-device workspace, so stream-K products of one device must be issued on one stream at a time. */
+int peft_set_gemm_streamk(int mode);
 /* diagnostics (tests/bench_ops.py gemm_stats): with PEFT_GEMM_STATS=1 in the environment the 2-CTA GEMM records, per CTA,
  * the cycles its TMA producer, MMA issuer and first epilogue warp spent waiting on their mbarriers during the LAST launch:
  * host_out[cta*8 + {0: producer wait-empty, 1: producer total, 2: issuer wait-full, 3: issuer wait-tmem-empty, 4: issuer

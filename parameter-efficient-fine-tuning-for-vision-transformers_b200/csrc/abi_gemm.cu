@@ -53,6 +53,63 @@ static unsigned long long* gemm_stats_buffer() {
   return buf;
 }
 
+// ---------------------------------------------------------------- stream-K (see GemmParams::sk_dp_tiles, TileSched)
+static std::atomic<int>& streamk_mode() {
+  static std::atomic<int> m{[] { const char* e = getenv("PEFT_GEMM_STREAMK"); return e ? atoi(e) : 1; }()};
+  return m;       // 0 = off, 1 = automatic, 2 = whenever the shape allows it (tests)
+}
+// One workspace per device, allocated at the first 2-CTA launch (i.e. during warm-up, never inside a graph capture): a
+// [256 x 256] fp32 slot per cluster + per-warp flags.  Stream-K launches of one device must not overlap in time (they are
+// issued on one stream by the engine); concurrent multi-stream callers switch it off with peft_set_gemm_streamk(0).
+struct SkWorkspace { float4* ws = nullptr; int* flags = nullptr; bool tried = false; };
+static SkWorkspace* sk_workspace() {
+  static std::mutex mu;
+  static SkWorkspace per_dev[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> g(mu);
+  SkWorkspace& w = per_dev[dev];
+  if (!w.tried) {
+    w.tried = true;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    const size_t clusters = 128, slot = (size_t)2 * kEpiWarps * 1024 * sizeof(float4);
+    void* a = nullptr;
+    void* f = nullptr;
+    if (cudaMalloc(&a, clusters * slot) == cudaSuccess && cudaMalloc(&f, clusters * 2 * kEpiWarps * sizeof(int)) == cudaSuccess &&
+        cudaMemset(f, 0, clusters * 2 * kEpiWarps * sizeof(int)) == cudaSuccess) {
+      w.ws = reinterpret_cast<float4*>(a);
+      w.flags = reinterpret_cast<int*>(f);
+    } else {
+      (void)cudaGetLastError();
+      (void)st;
+    }
+  }
+  return w.ws ? &w : nullptr;
+}
+// Decide whether (and from which tile on) the product runs stream-K: only long contractions (>= 16 k-blocks: the fix-up
+// moves a 256 KB partial tile through L2, which a short K cannot amortise) whose tile count leaves the last wave mostly
+// empty.  All but the last full wave stay data-parallel; the last full wave + the remainder are dealt out by k-blocks.
+static void decide_streamk(GemmParams& p, int M, int N, int K) {
+  p.sk_dp_tiles = -1;
+  const int mode = streamk_mode().load(std::memory_order_relaxed);
+  if (mode == 0 || p.ksplit > 1) return;
+  SkWorkspace* w = sk_workspace();
+  if (w == nullptr) return;
+  const long long T = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  const int C = sm_count() / 2;
+  const int KB = (K + kBK - 1) / kBK;
+  if (C > 128 || T > (1 << 24)) return;
+  const long long waves = (T + C - 1) / C;
+  const double eff = (double)T / (double)(waves * C);
+  if (mode == 1 && (KB < 16 || eff >= 0.92)) return;
+  if (mode == 2 && KB < 2) return;
+  const long long dp = T >= C ? (T / C - 1) * C : 0;
+  if ((T - dp) * KB < 4LL * C) return;          // every cluster must get a non-empty k-block range
+  p.sk_dp_tiles = (int)dp;
+  p.sk_ws = w->ws;
+  p.sk_flags = w->flags;
+}
+
 // ---------------------------------------------------------------- 2-CTA kernel (gemm2_sm100.cuh)
 static std::atomic<int>& gemm_algo() {
   static std::atomic<int> a{0};   // 0 = auto, 1 = force 1-CTA kernel, 2 = force 2-CTA kernel
@@ -70,7 +127,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
   }
   const int num_tiles = ((p.M + 2 * kBM - 1) / (2 * kBM)) * ((p.N + kG2BN - 1) / kG2BN) * (p.ksplit > 1 ? p.ksplit : 1);
   const int max_clusters = sm_count() / 2;
-  const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+  const int clusters = (num_tiles < max_clusters && p.sk_dp_tiles < 0) ? num_tiles : max_clusters;   // stream-K uses every pair
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * clusters, 1, 1);
   cfg.blockDim = dim3(kG2Threads, 1, 1);
@@ -198,6 +255,8 @@ extern "C" int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, lo
   p.stats = gemm_stats_buffer();
   if (p.ksplit > 1) PEFT_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)M * N * sizeof(float), s));
   if (p.ksplit > 1 || use_gemm2(M, N)) {
+    (void)sk_workspace();                     // allocated on the first 2-CTA launch of the device (outside any capture)
+    decide_streamk(p, M, N, K);
     CUtensorMap ta, tb, to, to2, tx;
     int rc = make_tmap_2d(&ta, a, false, (unsigned long long)M, (unsigned long long)K, (unsigned long long)lda, kBM, 64);
     if (rc) return rc;
@@ -228,6 +287,12 @@ extern "C" int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, lo
     case 128: return dispatch_epi<128>(epilogue, ta, tb, p, s);
     default: return dispatch_epi<32>(epilogue, ta, tb, p, s);
   }
+}
+
+extern "C" int peft_set_gemm_streamk(int mode) {
+  PEFT_REQUIRE(mode >= 0 && mode <= 2, "peft_set_gemm_streamk: mode must be 0 (off), 1 (automatic) or 2 (whenever possible)");
+  streamk_mode().store(mode);
+  return 0;
 }
 
 extern "C" int peft_set_gemm_algo(int algo) {

@@ -323,6 +323,59 @@ struct EpiTraits {
   static constexpr int kUnits = 128 / kUnitCols;         // units per warp per tile (the warp owns 128 columns)
 };
 
+// Tile scheduler shared by the three roles of the kernel.  Work items ("segments") are (tile, [kb0, kb1), kind):
+//   kSegFull     a whole tile, or — with GemmParams::ksplit > 1 — one K range of a tile that is reduce-added into `out`;
+//   kSegOwner    stream-K: the first k-blocks of a tile; the epilogue adds the partial sums of the following cluster(s);
+//   kSegPartial  stream-K: later k-blocks of a tile; the accumulator is handed to the owner through the workspace.
+// A cluster's stream-K range starts with at most one kSegPartial and ends with at most one kSegOwner, so a waiting owner
+// only ever depends on segments that other clusters process FIRST in their range: no cyclic waits.
+enum : int { kSegFull = 0, kSegOwner = 1, kSegPartial = 2 };
+struct TileSched {
+  int cid, C, ksplit, num_kb, kb_per, n_dp, i;
+  long long u, u1;        // stream-K cursor / end, in k-block units over the stream-K tiles
+  int sk_base;            // first stream-K tile
+  __device__ TileSched(const GemmParams& p, int num_tiles_mn, int num_kb_, int cluster_id, int num_clusters) {
+    cid = cluster_id; C = num_clusters; num_kb = num_kb_; i = 0;
+    ksplit = p.ksplit > 1 ? p.ksplit : 1;
+    kb_per = (num_kb + ksplit - 1) / ksplit;
+    if (p.sk_dp_tiles >= 0 && ksplit == 1) {
+      n_dp = p.sk_dp_tiles;
+      sk_base = p.sk_dp_tiles;
+      const long long sku = (long long)(num_tiles_mn - p.sk_dp_tiles) * num_kb;
+      u = sku * cid / C;
+      u1 = sku * (cid + 1) / C;
+    } else {
+      n_dp = num_tiles_mn * ksplit;
+      sk_base = 0;
+      u = u1 = 0;
+    }
+  }
+  // first unit of cluster c's stream-K range (for the owner's contributor walk)
+  __device__ long long range_begin(const GemmParams& p, int num_tiles_mn, int c) const {
+    return (long long)(num_tiles_mn - p.sk_dp_tiles) * num_kb * c / C;
+  }
+  __device__ bool next(int& mn, int& kb0, int& kb1, int& kind) {
+    const int t = cid + i * C;
+    if (t < n_dp) {
+      ++i;
+      mn = t / ksplit;
+      kb0 = (t % ksplit) * kb_per;
+      kb1 = min(num_kb, kb0 + kb_per);
+      kind = kSegFull;
+      return true;
+    }
+    if (u >= u1) return false;
+    const int st = (int)(u / num_kb);
+    kb0 = (int)(u - (long long)st * num_kb);
+    const long long left = u1 - u;
+    kb1 = (left >= (long long)(num_kb - kb0)) ? num_kb : kb0 + (int)left;
+    mn = sk_base + st;
+    kind = (kb0 == 0) ? (kb1 == num_kb ? kSegFull : kSegOwner) : kSegPartial;
+    u += kb1 - kb0;
+    return true;
+  }
+};
+
 // 16-byte chunk j of row `lane` inside a 128B-swizzled [32 x 128 B] slot (the layout TMA expects for SWIZZLE_128B).
 __device__ __forceinline__ uint32_t slot_off(int lane, int j) { return (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4)); }
 
@@ -382,9 +435,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   const int num_mp = (p.M + 2 * kBM - 1) / (2 * kBM);     // 256-row pair tiles
   const int num_n = (p.N + kG2BN - 1) / kG2BN;
   const int ksplit = p.ksplit > 1 ? p.ksplit : 1;
-  const int num_tiles = num_mp * num_n * ksplit;            // tile = (mp * num_n + n_blk) * ksplit + ks
+  const int num_tiles_mn = num_mp * num_n;                  // output tiles; the scheduler adds K splits / stream-K segments
   const int num_kb = (p.K + kBK - 1) / kBK;
-  const int kb_per = (num_kb + ksplit - 1) / ksplit;        // k-blocks per split (the host guarantees none is empty)
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
 
@@ -400,12 +452,12 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     long long t_wait = 0, t_begin = clock64();
     const uint32_t tiles_u32 = ptx::smem_u32(tiles);
     const uint32_t full0 = ptx::mapa(ptx::smem_u32(&full_bar[0]), 0);     // the leader's full barriers (8 bytes apart)
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-      const int ks = tile % ksplit, mn = tile / ksplit;
+    TileSched sched(p, num_tiles_mn, num_kb, cluster_id, num_clusters);
+    int mn, kb0, kb1, kind;
+    while (sched.next(mn, kb0, kb1, kind)) {
       const int mp = mn / num_n, n_blk = mn % num_n;
       const int row_a = (p.dbg & 2) ? (int)cta_rank * kBM : mp * 2 * kBM + (int)cta_rank * kBM;
       const int row_b = (p.dbg & 2) ? (int)cta_rank * (kG2BN / 2) : n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
-      const int kb0 = ks * kb_per, kb1 = min(num_kb, kb0 + kb_per);
       for (int kb = kb0; kb < kb1; ++kb) {
         if (p.stats) {
           const long long t0 = clock64();
@@ -456,7 +508,9 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       uint32_t acc_phase = 0;
       long long t_wfull = 0, t_wtmem = 0, t_begin = clock64();
       const uint32_t tiles_u32 = ptx::smem_u32(tiles);
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      TileSched sched(p, num_tiles_mn, num_kb, cluster_id, num_clusters);
+      int mn, kb0, kb1, kind;
+      while (sched.next(mn, kb0, kb1, kind)) {
         if (p.stats) {
           const long long t0 = clock64();
           ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
@@ -466,7 +520,6 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         }
         ptx::tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kG2BN);
-        const int kb0 = (tile % ksplit) * kb_per, kb1 = min(num_kb, kb0 + kb_per);
         for (int kb = kb0; kb < kb1; ++kb) {
           if (p.stats) {
             const long long t0 = clock64();
@@ -511,12 +564,23 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     int acc = 0;
     uint32_t acc_phase = 0;
     long long t_wacc = 0, t_begin = clock64();
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-      const int mn = tile / ksplit;
+    TileSched sched(p, num_tiles_mn, num_kb, cluster_id, num_clusters);
+    // stream-K workspace of this warp inside cluster c's slot: [2 CTAs][8 warps][1024 float4], unit-major then 16-byte chunk
+    // then lane (coalesced); sk_flags[(c * 2 + cta) * 8 + warp] = 1 once that warp's part of the partial tile is visible
+    auto sk_slot = [&](int c) { return p.sk_ws + ((size_t)(c * 2 + (int)cta_rank) * kEpiWarps + ew) * 1024; };
+    auto sk_flag = [&](int c) { return p.sk_flags + (c * 2 + (int)cta_rank) * kEpiWarps + ew; };
+    int mn, kb0, kb1, kind;
+    while (sched.next(mn, kb0, kb1, kind)) {
       const int mp = mn / num_n, n_blk = mn % num_n;
       const int row0 = mp * 2 * kBM + (int)cta_rank * kBM + quarter * 32;   // first row of this warp's 32-row slab
       const int col0 = n_blk * kG2BN + half * 128;                          // first of this warp's 128 columns
-      if constexpr (T::kAux) {
+      // stream-K owner: clusters cluster_id + 1 .. sk_last hold the rest of this tile's K range
+      int sk_last = cluster_id;
+      if (kind == kSegOwner) {
+        const long long tile_end = (long long)(mn - p.sk_dp_tiles + 1) * num_kb;
+        while (sk_last + 1 < num_clusters && sched.range_begin(p, num_tiles_mn, sk_last + 1) < tile_end) ++sk_last;
+      }
+      if (T::kAux && kind != kSegPartial) {
         // prefetch the auxiliary operand of units 0 and 1 (independent of the accumulator)
         if (lane == 0) {
           ptx::bulk_wait_read<0>();                   // previous tile's stores have released both slots
@@ -537,6 +601,20 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       ptx::tcgen05_fence_after();
       const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                               static_cast<uint32_t>(acc * kG2BN + half * 128);
+      if (kind == kSegOwner) {
+        // the contributors' parts of this tile (same CTA rank, same warp role) must be visible before they are added below
+        if (lane == 0) {
+          for (int c = cluster_id + 1; c <= sk_last; ++c) {
+            unsigned spins = 0;
+            int f;
+            do {
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(f) : "l"(sk_flag(c)) : "memory");
+              if (f == 0 && ++spins > (1u << 28)) __trap();     // watchdog: a lost partial must not hang the GPU
+            } while (f == 0);
+          }
+        }
+        __syncwarp();
+      }
 #pragma unroll 1
       for (int u = 0; u < T::kUnits; ++u) {
         const int s = u & 1;
@@ -568,6 +646,24 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           if (lane == 0) ptx::mbar_arrive_cluster(acc ? tmem_empty_remote1 : tmem_empty_remote0);
         }
         if constexpr (!T::kAux) { if (p.dbg & 4) continue; }   // diagnostic: drain TMEM only
+        if (kind == kSegPartial) {
+          // stream-K: raw fp32 accumulator -> this cluster's workspace slot (L2-resident, read back once by the owner)
+          float4* ws = sk_slot(cluster_id) + u * (NP / 2) * 32 + lane;
+#pragma unroll
+          for (int jj = 0; jj < NP / 2; ++jj) __stcg(ws + jj * 32, make_float4(v[2 * jj].x, v[2 * jj].y, v[2 * jj + 1].x, v[2 * jj + 1].y));
+          continue;
+        }
+        if (kind == kSegOwner) {
+          for (int c = cluster_id + 1; c <= sk_last; ++c) {
+            const float4* ws = sk_slot(c) + u * (NP / 2) * 32 + lane;
+#pragma unroll
+            for (int jj = 0; jj < NP / 2; ++jj) {
+              const float4 a = __ldcg(ws + jj * 32);
+              v[2 * jj] = add2(v[2 * jj], make_float2(a.x, a.y));
+              v[2 * jj + 1] = add2(v[2 * jj + 1], make_float2(a.z, a.w));
+            }
+          }
+        }
         if (p.bias != nullptr) {
           if (colu + T::kUnitCols <= p.N) {
 #pragma unroll
@@ -691,6 +787,17 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             }
           }
         }
+      }
+      if (kind == kSegPartial) {
+        __syncwarp();                         // every lane's partial-sum stores are ordered before lane 0's fence + flag
+        if (lane == 0) {
+          __threadfence();
+          asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(sk_flag(cluster_id)), "r"(1) : "memory");
+        }
+      } else if (kind == kSegOwner) {
+        __syncwarp();                         // all lanes have read the partials: re-arm the flags for the next launch
+        if (lane == 0)
+          for (int c = cluster_id + 1; c <= sk_last; ++c) *reinterpret_cast<volatile int*>(sk_flag(c)) = 0;
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;

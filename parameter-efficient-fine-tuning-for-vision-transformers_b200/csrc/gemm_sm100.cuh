@@ -48,6 +48,13 @@ struct GemmParams {
   long long ldaux;
   int ksplit = 1;     // 2-CTA kernel, EPI_STORE_F32 only: K is cut into `ksplit` ranges that are separate tiles and are
                       // summed into a pre-zeroed `out` by TMA reduce-add (weight-gradient products: small output, long K)
+  // stream-K (2-CTA kernel, ksplit == 1): the first `sk_dp_tiles` tiles are processed one whole tile per cluster as usual; the
+  // k-blocks of the remaining tiles are dealt out evenly over the clusters, so a tile may be computed by several clusters —
+  // the one that holds its first k-block owns the epilogue and adds the others' fp32 partial accumulators, which travel
+  // through `sk_ws` (one 256 x 256 fp32 slot per cluster) guarded by per-warp flags in `sk_flags`.  sk_dp_tiles < 0: off.
+  int sk_dp_tiles = -1;
+  float4* sk_ws = nullptr;
+  int* sk_flags = nullptr;
   const float* rowscale = nullptr;   // optional fp32 [M]: (acc + bias) is multiplied by rowscale[row] before the rest of the
                       // epilogue — the per-sample stochastic-depth keep mask / keep_prob of DropPath (FS/kadaptation.py:263,276-277)
   unsigned long long* stats = nullptr;   // diagnostics (env PEFT_GEMM_STATS=1): per-CTA wait-cycle counters, see peft_debug_gemm_stats

@@ -260,3 +260,77 @@ def test_tower_matches_oracle_at_bench_geometry(lib, name):
     for k in names:
         e = rel(cpu(params[k].grad), sd_o[k].grad.detach())
         assert e < per_tensor, (k, e)
+
+
+# ---------------------------------------------------------------------------------------------------------------- stream-K
+class streamk:
+    def __init__(self, lib, mode):
+        self.lib, self.mode = lib, mode
+
+    def __enter__(self):
+        self.lib.check(self.lib.load().peft_set_gemm_streamk(self.mode))
+
+    def __exit__(self, *exc):
+        self.lib.check(self.lib.load().peft_set_gemm_streamk(1))
+
+
+@pytest.mark.parametrize("M,N,K,epi", [
+    (6304, 768, 3072, "store"), (6304, 768, 3072, "resid"), (6304, 768, 2320, "store"),     # 75 tiles on 74 pairs (8 GPUs)
+    (12608, 768, 3072, "resid"), (25216, 768, 3072, "store"),                                 # 150 / 297 tiles (4 / 2 GPUs)
+    (6304, 3072, 768, "gelu"), (6304, 3072, 768, "dgelu"), (6304, 2304, 784, "store"),        # short K: only under mode 2
+    (3000, 768, 3072, "resid"), (1100, 520, 4104, "store"),                                   # fewer tiles than pairs: a tile
+])                                                                                            # is shared by 3+ clusters
+def test_gemm2_streamk_matches_reference(ops, lib, M, N, K, epi):
+    """Stream-K scheduling of the 2-CTA kernel (the last full wave and the remainder dealt out by k-blocks, partial tiles
+    summed by the owner through the L2 workspace): every epilogue family, repeated launches (flag re-arm), tiles shared by
+    two and by more clusters, M / N tails.  Must agree with the fp32 reference AND, to accumulation-order noise, with the
+    data-parallel schedule."""
+    a = _r(M, K, dtype=torch.bfloat16, seed=1)
+    b = _r(N, K, scale=0.05, dtype=torch.bfloat16, seed=2)
+    bias = _r(N, scale=0.5, seed=3)
+    acc = a.float() @ b.float().T
+
+    def run(out_dtype):
+        if epi == "store":
+            out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+            ops.gemm(a, b, out, bias=bias)
+            return (out,)
+        if epi == "resid":
+            res = _r(M, N, seed=4)
+            out = torch.full((M, N), float("nan"), device="cuda")
+            ops.gemm(a, b, out, bias=bias, epilogue=ops.EPI_RESID_F32, aux=res)
+            return (out,)
+        if epi == "gelu":
+            h = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+            act = torch.full_like(h, float("nan"))
+            ops.gemm(a, b, h, bias=bias, epilogue=ops.EPI_GELU, out2=act)
+            return h, act
+        hpre = _r(M, N, dtype=torch.bfloat16, seed=5)
+        out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+        ops.gemm(a, b, out, epilogue=ops.EPI_DGELU, aux=hpre)
+        return (out,)
+
+    if epi == "store":
+        refs = (acc + bias,)
+    elif epi == "resid":
+        refs = (acc + bias + _r(M, N, seed=4),)
+    elif epi == "gelu":
+        refs = (acc + bias, F.gelu(acc + bias))
+    else:
+        hh = _r(M, N, dtype=torch.bfloat16, seed=5).float().requires_grad_(True)
+        F.gelu(hh).backward(acc)
+        refs = (hh.grad,)
+    with forced_algo(lib, 2) as fa:
+        with streamk(lib, 0):
+            base = run(None)
+        with streamk(lib, 2):
+            first = run(None)
+            second = run(None)          # the flags were re-armed by the owners of the first launch
+        torch.cuda.synchronize()
+        assert fa.big_launches() == 3
+    tol = 1e-4 if epi == "resid" else 1e-2
+    for o1, o2, ob, ref in zip(first, second, base, refs):
+        assert not torch.isnan(o1.float()).any() and not torch.isnan(o2.float()).any()
+        assert rel(o1, ref) < tol and rel(o2, ref) < tol
+        assert rel(o1, ob) < (1e-5 if epi == "resid" else 4e-3)     # same sums, different accumulation order
+        assert torch.equal(o1, o2)                                   # the schedule is deterministic
