@@ -56,6 +56,9 @@ int peft_set_gemm_streamk(int mode);
  * host_out[cta*8 + {0: producer wait-empty, 1: producer total, 2: issuer wait-full, 3: issuer wait-tmem-empty, 4: issuer
  * total, 5: epilogue wait-accumulator, 6: epilogue total}].  Synchronises the device. */
 int peft_debug_gemm_stats(unsigned long long* host_out, int n_ctas);
+/* same for the tcgen05 attention forward (PEFT_ATTN_STATS=1): host_out[(cta*2 + warpgroup)*8 + {0: wait S, 1: max pass,
+ * 2: exp pass, 3: wait O, 4: O epilogue + store, 5: total}] of the first softmax warp of each warpgroup. */
+int peft_debug_attn_stats(unsigned long long* host_out, int n_ctas);
 /* same for the attention kernels: 0 = automatic (tcgen05/TMEM kernels for L <= 272), 1 = mma.sync kernels, 2 = tcgen05 */
 int peft_set_attention_algo(int algo);
 

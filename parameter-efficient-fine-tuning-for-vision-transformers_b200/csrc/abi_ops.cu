@@ -161,6 +161,26 @@ extern "C" int peft_set_attention_algo(int algo) {
   return 0;
 }
 
+// diagnostics: per-phase cycle counters of the LAST tcgen05 attention-forward launch (env PEFT_ATTN_STATS=1)
+static unsigned long long* attn_stats_buffer() {
+  static unsigned long long* buf = [] {
+    const char* e = getenv("PEFT_ATTN_STATS");
+    unsigned long long* p = nullptr;
+    if (e && atoi(e) > 0 && cudaMalloc(&p, 256 * 16 * sizeof(unsigned long long)) == cudaSuccess) cudaMemset(p, 0, 256 * 16 * sizeof(unsigned long long));
+    else p = nullptr;
+    return p;
+  }();
+  return buf;
+}
+extern "C" int peft_debug_attn_stats(unsigned long long* host_out, int n_ctas) {
+  unsigned long long* buf = attn_stats_buffer();
+  PEFT_REQUIRE(buf != nullptr, "peft_debug_attn_stats: set PEFT_ATTN_STATS=1 before the first attention call");
+  PEFT_REQUIRE(host_out && n_ctas > 0 && n_ctas <= 256, "peft_debug_attn_stats: bad arguments");
+  PEFT_CUDA_CHECK(cudaDeviceSynchronize());
+  PEFT_CUDA_CHECK(cudaMemcpy(host_out, buf, (size_t)n_ctas * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 template <int NK>
 static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long ldo, float* lse2, int B, int H, int L,
                             float scale, cudaStream_t s) {
@@ -180,6 +200,7 @@ static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long
   }
   Attn2Params p{};
   p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
+  p.stats = attn_stats_buffer();
   const int grid = B * H < sm_count() ? B * H : sm_count();
   kern<<<grid, kA2Threads, C::kSmemBytes, s>>>(tq, tkv, to, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_FWD);
@@ -317,7 +338,7 @@ extern "C" int peft_tn_reduce(const void* x, long long ldx, int I, const void* y
   PEFT_REQUIRE(M > 0 && (I == 16 || I == 32 || I == 64) && J > 0 && J % 64 == 0, "peft_tn_reduce: need I in {16,32,64}, J %% 64 == 0 (I=%d J=%d)", I, J);
   PEFT_REQUIRE(aligned16(x) && aligned16(y) && ldx % 8 == 0 && ldy % 8 == 0, "peft_tn_reduce: operands must be 16-byte aligned with pitch %% 8 == 0");
   const int jt = J / 64;
-  int target_ctas = sm_count() * 4;
+  int target_ctas = sm_count() * 2;      // every CTA ends in I x 64 global atomics: few, long CTAs (>= 4 stages of 64 rows each)
   int my = (target_ctas + jt - 1) / jt;
   int rows = (M + my - 1) / my;
   rows = ((rows + 63) / 64) * 64;

@@ -115,6 +115,7 @@ struct Attn2Params {
   float* delta_out;        // backward (dQ kernel): [B*H, L]
   int B, H, L;
   float scale;
+  unsigned long long* stats;   // diagnostics (PEFT_ATTN_STATS=1): cycles per phase of the first softmax warp of each CTA
 };
 
 
@@ -350,6 +351,8 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint8_t* stage = sO + wg * C::kQBytes;
     constexpr int NF = NK / 32;
     constexpr bool kTail = (NK % 32) != 0;
+    long long tS = 0, tP1 = 0, tP2 = 0, tO = 0, tE = 0, tc0 = clock64(), tbeg = tc0;
+    auto lap = [&](long long& acc) { const long long n = clock64(); acc += n - tc0; tc0 = n; };
     for (int g = wg; g < G; g += 2) {
       const int hl = g / TQ, t = g % TQ;
       const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
@@ -360,6 +363,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const uint32_t tb = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + (uint32_t)(buf * C::kBufCols);
       ptx::mbar_wait(&s_ready[wg], (g >> 1) & 1);
       ptx::tcgen05_fence_after();
+      if (p.stats) lap(tS);
       float mx = -INFINITY, sum = 0.f, mc = 0.f;
       if (warp_active) {
         uint32_t r[2][32];
@@ -388,6 +392,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           }
         }
         mc = mx * c;
+        if (p.stats) lap(tP1);
         // ---- pass 2: P = exp2(S c - m c) -> bf16 in place (ascending: writes only touch columns already consumed)
         tm_ld32(tb, r[0]);
 #pragma unroll
@@ -433,9 +438,11 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
       ptx::tcgen05_fence_before();
       ptx::mbar_arrive(&p_ready[wg]);
+      if (p.stats) lap(tP2);
       // ---- epilogue: O / rowsum -> bf16 -> staging -> TMA store
       ptx::mbar_wait(&o_ready[wg], (g >> 1) & 1);
       ptx::tcgen05_fence_after();
+      if (p.stats) lap(tO);
       uint32_t o[64];
       if (warp_active) {
         tm_ld32(tb + C::kOOff, o);
@@ -465,8 +472,13 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         ptx::tma_store_3d(&tmap_o, stage, h * 64, t * 128, b);
         ptx::bulk_commit();
       }
+      if (p.stats) lap(tE);
     }
     if (issuer) ptx::bulk_wait<0>();
+    if (p.stats && (cw & 3) == 0 && lane == 0) {
+      unsigned long long* o = p.stats + (blockIdx.x * 2 + wg) * 8;
+      o[0] = tS; o[1] = tP1; o[2] = tP2; o[3] = tO; o[4] = tE; o[5] = clock64() - tbeg;
+    }
   }
   ptx::tcgen05_fence_before();
   __syncthreads();

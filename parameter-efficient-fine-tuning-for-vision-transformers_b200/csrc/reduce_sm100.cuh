@@ -91,20 +91,30 @@ tn_reduce_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const __nv_
     __syncthreads();
   }
 
-  // combine the 4 warps' partial sums, then one atomic per element
-  for (int i = threadIdx.x; i < I * 64; i += kRedThreads) sRed[i] = 0.f;
-  __syncthreads();
+  // combine the 4 warps' partial sums in shared memory — warp after warp with plain read-modify-writes (a float atomicAdd
+  // on shared memory is a CAS loop, and the four warps collide on every address) — then one global atomic per element
+#pragma unroll 1
+  for (int w = 0; w < kRedThreads / 32; ++w) {
+    if (warp == w) {
 #pragma unroll
-  for (int a = 0; a < IT; ++a)
+      for (int a = 0; a < IT; ++a)
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt) {
-      const int row = a * 16 + (lane >> 2), col = nt * 8 + (lane & 3) * 2;
-      atomicAdd(&sRed[row * 64 + col], acc[a][nt][0]);
-      atomicAdd(&sRed[row * 64 + col + 1], acc[a][nt][1]);
-      atomicAdd(&sRed[(row + 8) * 64 + col], acc[a][nt][2]);
-      atomicAdd(&sRed[(row + 8) * 64 + col + 1], acc[a][nt][3]);
+        for (int nt = 0; nt < 8; ++nt) {
+          const int row = a * 16 + (lane >> 2), col = nt * 8 + (lane & 3) * 2;
+          float2* lo = reinterpret_cast<float2*>(&sRed[row * 64 + col]);
+          float2* hi = reinterpret_cast<float2*>(&sRed[(row + 8) * 64 + col]);
+          if (w == 0) {
+            *lo = make_float2(acc[a][nt][0], acc[a][nt][1]);
+            *hi = make_float2(acc[a][nt][2], acc[a][nt][3]);
+          } else {
+            const float2 l = *lo, h = *hi;
+            *lo = make_float2(l.x + acc[a][nt][0], l.y + acc[a][nt][1]);
+            *hi = make_float2(h.x + acc[a][nt][2], h.y + acc[a][nt][3]);
+          }
+        }
     }
-  __syncthreads();
+    __syncthreads();
+  }
   for (int i = threadIdx.x; i < I * 64; i += kRedThreads) {
     const int row = i >> 6, col = i & 63;
     atomicAdd(out + (long long)row * ldout + j0 + col, sRed[i]);

@@ -160,6 +160,67 @@ def gemm_scaling_probe():
     _lib.check(_lib.load().peft_set_gemm_algo(0))
 
 
+def graph_time(fn, reps=20, iters=10):
+    """us per call of `fn` when `reps` calls are replayed from one CUDA graph (no Python / launch-API time)."""
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        fn(); fn()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                fn()
+        g.replay()
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (iters * reps) * 1e3
+
+
+def bench_fixed_costs():
+    """Per-launch floor of each kernel family inside a CUDA graph (tiny problems) and the B = 32 layer kernels (M = 6304)."""
+    def gemm_case(M, N, K, epi=ops.EPI_STORE, algo=0):
+        a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+        b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+        bias = torch.randn(N, device="cuda")
+        f32 = epi == ops.EPI_RESID_F32
+        out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
+        out2 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16) if epi == ops.EPI_GELU else None
+        aux = torch.randn(M, N, device="cuda") if f32 else (torch.randn(M, N, device="cuda").to(torch.bfloat16) if epi == ops.EPI_DGELU else None)
+        _lib.check(_lib.load().peft_set_gemm_algo(algo))
+        t = graph_time(lambda: ops.gemm(a, b, out, bias=bias, epilogue=epi, out2=out2, aux=aux))
+        _lib.check(_lib.load().peft_set_gemm_algo(0))
+        return t
+    print(f"gemm2 floor  (256x256x64, forced 2-CTA): {gemm_case(256, 256, 64, algo=2):6.1f} us")
+    print(f"gemm2 1 wave (18944x256x64 = 74 tiles) : {gemm_case(18944, 256, 64, algo=2):6.1f} us")
+    print(f"gemm1 floor  (128x128x64, 1-CTA)       : {gemm_case(128, 128, 64, algo=1):6.1f} us")
+    M = 6304
+    for name, N, K, epi in [("qkv", 2304, 784, ops.EPI_STORE), ("proj+res", 768, 768, ops.EPI_RESID_F32), ("fc1+gelu", 3072, 768, ops.EPI_GELU),
+                            ("fc2+res", 768, 3072, ops.EPI_RESID_F32), ("fc2T*dgelu", 3072, 768, ops.EPI_DGELU), ("fc1T", 768, 3072, ops.EPI_STORE),
+                            ("projT", 768, 768, ops.EPI_STORE), ("qkvT", 768, 2320, ops.EPI_STORE), ("p = x Dn^T", 32, 768, ops.EPI_STORE)]:
+        t = gemm_case(M, N, K, epi)
+        print(f"gemm {name:12s} M={M} N={N} K={K}: {t:6.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
+    x = torch.randn(M, 768, device="cuda"); gamma = torch.ones(768, device="cuda"); beta = torch.zeros(768, device="cuda")
+    y = torch.empty(M, 768, device="cuda", dtype=torch.bfloat16); mean = torch.empty(M, device="cuda"); rstd = torch.empty(M, device="cuda")
+    print(f"ln_fwd M={M}: {graph_time(lambda: ops.layernorm_fwd(x, gamma, beta, y, mean, rstd, 1e-6)):6.1f} us")
+    dy = torch.randn(M, 768, device="cuda").to(torch.bfloat16); g = torch.randn(M, 768, device="cuda"); gb = torch.empty(M, 768, device="cuda", dtype=torch.bfloat16)
+    print(f"ln_bwd_f32g M={M}: {graph_time(lambda: ops.layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g, g, gb)):6.1f} us")
+    wide = torch.randn(M, 800, device="cuda").to(torch.bfloat16); yy = torch.randn(M, 2304, device="cuda").to(torch.bfloat16)
+    o1 = torch.zeros(32, 2304, device="cuda"); o2 = torch.zeros(32, 768, device="cuda")
+    print(f"tn_reduce 32x2304 M={M}: {graph_time(lambda: ops.tn_reduce(wide[:, 768:800], yy, o1)):6.1f} us")
+    print(f"tn_reduce 32x768  M={M}: {graph_time(lambda: ops.tn_reduce(yy[:, :32], wide[:, :768], o2)):6.1f} us")
+    B, H, L = 32, 12, 197
+    qkv = torch.randn(B * L, 2304, device="cuda").to(torch.bfloat16); o = torch.empty(B * L, 768, device="cuda", dtype=torch.bfloat16)
+    d_o = torch.randn(B * L, 768, device="cuda").to(torch.bfloat16); dqkv = torch.zeros(B * L, 2304, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * L, device="cuda"); delta = torch.empty(B * H * L, device="cuda")
+    print(f"attn fwd B={B}: {graph_time(lambda: ops.attention_fwd(qkv, o, lse2, B, H, L, 0.125)):6.1f} us")
+    print(f"attn bwd B={B}: {graph_time(lambda: ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)):6.1f} us")
+
+
 def bench_gemm_dw(tokens=12800, iters=20):
     """Weight-gradient products of the full mode (C5): out[N_out, K_in] = dY^T X, contraction over the tokens."""
     for name, No, Ki in [("dW qkv", 2304, 768), ("dW proj", 768, 768), ("dW fc1", 3072, 768), ("dW fc2", 768, 3072)]:
@@ -241,6 +302,23 @@ if __name__ == "__main__":
         bench_attn(32, 12, 197)
         bench_ln(6304)
         bench_reduce(6304)
+    if what == "attn_stats":
+        import ctypes
+        for (B, H, L) in ((256, 12, 197), (128, 16, 257)):
+            D = H * 64
+            qkv = torch.randn(B * L, 3 * D, device="cuda").to(torch.bfloat16)
+            o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+            lse2 = torch.empty(B * H * L, device="cuda")
+            t = timeit(lambda: ops.attention_fwd(qkv, o, lse2, B, H, L, 0.125), iters=5, warm=2)
+            buf = (ctypes.c_ulonglong * (148 * 16))()
+            _lib.check(_lib.load().peft_debug_attn_stats(buf, 148))
+            v = torch.tensor(list(buf), dtype=torch.float64).view(148, 2, 8)
+            tot = v[:, :, 5].mean()
+            names = ["wait S", "max pass", "exp pass", "wait O", "epilogue"]
+            print(f"attn fwd B={B} H={H} L={L}: {t:.1f} us; softmax warp total {tot:.0f} clk per CTA ({B * H / 148:.1f} heads): " +
+                  ", ".join(f"{n} {100 * float(v[:, :, i].mean() / tot):.1f}%" for i, n in enumerate(names)), flush=True)
+    if what == "fixed":
+        bench_fixed_costs()
     if what == "gemm_probe":
         print("PEFT_GEMM_DBG =", os.environ.get("PEFT_GEMM_DBG", "0"), flush=True)
         gemm_scaling_probe()
