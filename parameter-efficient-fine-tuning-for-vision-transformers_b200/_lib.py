@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libpeftb200.so")
+# PEFT_B200_LIB: A/B measurements of two builds of the SAME ABI inside one GPU session (developer knob, not a fallback)
+LIB_PATH = os.environ.get("PEFT_B200_LIB") or os.path.join(_HERE, "csrc", "libpeftb200.so")
 
 _c_ll = C.c_longlong
 _vp = C.c_void_p

@@ -57,42 +57,55 @@ ln_fwd_kernel(const InT* __restrict__ x, long long ldx, const float* __restrict_
     load4<float>(gamma + (i * 32 + lane) * 4, g[i]);
     load4<float>(beta + (i * 32 + lane) * 4, b[i]);
   }
-  for (long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < M;
-       row += (long long)gridDim.x * warps_per_block) {
-    float v[NV][4];
-    float s = 0.f;
+  // two rows per warp iteration, all loads issued before the first reduction: twice the bytes in flight per warp (the
+  // kernel is latency-bound, not issue-bound)
+  const long long stride = (long long)gridDim.x * warps_per_block;
+  for (long long row0 = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row0 < M; row0 += 2 * stride) {
+    const long long row1 = row0 + stride;
+    const bool two = row1 < M;
+    float v[2][NV][4];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      load4<InT>(x + row * ldx + (i * 32 + lane) * 4, v[i]);
-      s += v[i][0] + v[i][1] + v[i][2] + v[i][3];
-      if (add_out != nullptr) {   // side output: add_out = x + add_in (the residual sum the adapter's up-projection lands on)
-        float a[4];
-        load4<float>(add_in + row * ldai + (i * 32 + lane) * 4, a);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) a[j] += v[i][j];
-        store4<float>(add_out + row * ldao + (i * 32 + lane) * 4, a);
-      }
+      load4<InT>(x + row0 * ldx + (i * 32 + lane) * 4, v[0][i]);
+      if (two) load4<InT>(x + row1 * ldx + (i * 32 + lane) * 4, v[1][i]);
     }
-    const float mean = warp_sum(s) * (1.0f / D);
-    float q = 0.f;
 #pragma unroll
-    for (int i = 0; i < NV; ++i)
+    for (int rr = 0; rr < 2; ++rr) {
+      if (rr == 1 && !two) break;
+      const long long row = rr == 0 ? row0 : row1;
+      float s = 0.f;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float d = v[i][j] - mean;
-        q += d * d;
+      for (int i = 0; i < NV; ++i) {
+        s += v[rr][i][0] + v[rr][i][1] + v[rr][i][2] + v[rr][i][3];
+        if (add_out != nullptr) {   // side output: add_out = x + add_in (the residual sum the adapter's up-projection lands on)
+          float a[4];
+          load4<float>(add_in + row * ldai + (i * 32 + lane) * 4, a);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) a[j] += v[rr][i][j];
+          store4<float>(add_out + row * ldao + (i * 32 + lane) * 4, a);
+        }
       }
-    const float rstd = rsqrtf(warp_sum(q) * (1.0f / D) + eps);
+      const float mean = warp_sum(s) * (1.0f / D);
+      float q = 0.f;
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      float o[4];
+      for (int i = 0; i < NV; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) o[j] = (v[i][j] - mean) * rstd * g[i][j] + b[i][j];
-      store4<OutT>(y + row * ldy + (i * 32 + lane) * 4, o);
-    }
-    if (lane == 0) {
-      if (mean_out) mean_out[row] = mean;
-      if (rstd_out) rstd_out[row] = rstd;
+        for (int j = 0; j < 4; ++j) {
+          const float d = v[rr][i][j] - mean;
+          q += d * d;
+        }
+      const float rstd = rsqrtf(warp_sum(q) * (1.0f / D) + eps);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = (v[rr][i][j] - mean) * rstd * g[i][j] + b[i][j];
+        store4<OutT>(y + row * ldy + (i * 32 + lane) * 4, o);
+      }
+      if (lane == 0) {
+        if (mean_out) mean_out[row] = mean;
+        if (rstd_out) rstd_out[row] = rstd;
+      }
     }
   }
 }
@@ -124,12 +137,19 @@ ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__
   for (long long row = (long long)blockIdx.x * warps_per_block + warp; row < M;
        row += (long long)gridDim.x * warps_per_block) {
     const float mean = mean_in[row], rstd = rstd_in[row];
-    float d[NV][4], xh[NV][4];
+    float d[NV][4], xh[NV][4], o[NV][4];
     float s1 = 0.f, s2 = 0.f;
+    // every load of the row is issued up front — the residual-gradient input too, although it is only needed after the two
+    // warp reductions: one HBM round trip per row instead of two (the kernel is latency-bound at 16 warps per SM)
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       load4<DyT>(dy + row * lddy + (i * 32 + lane) * 4, d[i]);
       load4<XT>(x + row * ldx + (i * 32 + lane) * 4, xh[i]);
+      if (g_in != nullptr) load4<GT>(g_in + row * ldgi + (i * 32 + lane) * 4, o[i]);
+      else o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         xh[i][j] = (xh[i][j] - mean) * rstd;
@@ -146,13 +166,10 @@ ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__
     s2 = warp_sum(s2) * (1.0f / D);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      float o[4];
-      if (g_in != nullptr) load4<GT>(g_in + row * ldgi + (i * 32 + lane) * 4, o);
-      else o[0] = o[1] = o[2] = o[3] = 0.f;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) o[j] += rstd * (d[i][j] - s1 - xh[i][j] * s2);
-      store4<GT>(g_out + row * ldgo + (i * 32 + lane) * 4, o);
-      if (g_copy != nullptr) store4<__nv_bfloat16>(g_copy + row * ldgc + (i * 32 + lane) * 4, o);
+      for (int j = 0; j < 4; ++j) o[i][j] += rstd * (d[i][j] - s1 - xh[i][j] * s2);
+      store4<GT>(g_out + row * ldgo + (i * 32 + lane) * 4, o[i]);
+      if (g_copy != nullptr) store4<__nv_bfloat16>(g_copy + row * ldgc + (i * 32 + lane) * 4, o[i]);
     }
   }
   if constexpr (kParamGrad) {

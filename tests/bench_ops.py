@@ -59,6 +59,10 @@ def bench_ln(M=50432, D=768):
     go = torch.empty_like(gi)
     t = timeit(lambda: ops.layernorm_bwd(dy, x, mean, rstd, gamma, gi, go))
     print(f"ln_bwd  M={M} D={D}: {t:7.1f} us  {(M * D * 10) / t / 1e3:7.1f} GB/s")
+    g32 = torch.randn(M, D, device="cuda")
+    gb = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+    t = timeit(lambda: ops.layernorm_bwd_f32g(dy, x, mean, rstd, gamma, g32, g32, gb))
+    print(f"ln_bwd_f32g (engine form: bf16 dy, fp32 x, fp32 g in place + bf16 copy) M={M} D={D}: {t:7.1f} us  {(M * D * 16) / t / 1e3:7.1f} GB/s")
 
 
 def bench_ln_pg(D=768):
