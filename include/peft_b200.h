@@ -201,6 +201,19 @@ int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_ff_tensor* 
                       int n_items, const uint16_t* pi_lo, const float* gg, const float* bsign, float* wu, float* scratch,
                       int* counters, float* dV, void* stream);
 
+/* One-shot all-reduce (mean) of the flat fp32 gradient bucket over NVLink peer memory, fused with the SGD-momentum update of
+ * the flat parameter replica and the zeroing of the bucket for the next step.
+ * replaces: dist.all_reduce + 1/N scaling + torch.optim.SGD.step() + zero_grad of the data-parallel PEFT step; optimiser
+ * semantics of few_shot/vision_benchmark/optim/build.py:120-159 (SGD: momentum mu, dampening 0, weight decay, no Nesterov),
+ * stepped at few_shot/vision_benchmark/evaluation/kadaptation_clip.py:308-314.
+ * peer_grads / peer_pads: DEVICE arrays of `world` pointers to every rank's bucket / signal pad (torch symmetric memory:
+ * buffer_ptrs_dev / signal_pad_ptrs_dev); pad slots [pad_base, pad_base + 2 * blocks * world) of the uint32 pad are used
+ * (blocks <= 32) and are left zero.  lr is a device scalar (LR schedules need no graph re-capture).  world == 1: plain fused
+ * SGD + zeroing, no peer access.  n %% 4 == 0.  Every rank ends with bit-identical parameters (rank-ordered sums). */
+int peft_allreduce_sgd(const void* const* peer_grads, void* const* peer_pads, int rank, int world, float* grad, float* param,
+                       float* momentum, long long n, const float* lr, float mu, float weight_decay, int zero_grad,
+                       int pad_base, int pad_slots, void* stream);
+
 /* ---- fp32 verification mode ("within 1e-5 relative for fp32 mode", BASELINE.json north_star) -------------------------
  * Plain CUDA-core fp32 counterparts of the entry points above: same operand layouts (row pitches in elements), same
  * epilogue semantics with every bf16 tensor replaced by fp32, IEEE expf/erff/tanhf.  The Python engine selects them

@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "clip_delta_sm100.cuh"
 #include "fastfood_sm100.cuh"
+#include "allreduce_sgd_sm100.cuh"
 
 using namespace peft;
 
@@ -167,6 +168,28 @@ extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_
   ff_bwd_kernel<<<n_items, kFfThreads, (kFfTile + wn) * 4, s>>>(a);
   PEFT_LAUNCH_CHECK();
   ff_small_kernel<1><<<T, 256, wn * 4, s>>>(tensors, bsign, nullptr, wu, dV, d, wn);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_allreduce_sgd(const void* const* peer_grads, void* const* peer_pads, int rank, int world, float* grad,
+                                  float* param, float* momentum, long long n, const float* lr, float mu, float weight_decay,
+                                  int zero_grad, int pad_base, int pad_slots, void* stream) {
+  PEFT_REQUIRE(world >= 1 && world <= kArMaxWorld && rank >= 0 && rank < world, "peft_allreduce_sgd: bad rank %d / world %d", rank, world);
+  PEFT_REQUIRE(grad && param && momentum && lr && n > 0 && n % 4 == 0, "peft_allreduce_sgd: null operand or n %% 4 != 0 (n=%lld)", n);
+  PEFT_REQUIRE(al16(grad) && al16(param) && al16(momentum), "peft_allreduce_sgd: flat buffers must be 16-byte aligned");
+  PEFT_REQUIRE(world == 1 || (peer_grads && peer_pads), "peft_allreduce_sgd: peer pointer tables missing");
+  long long blocks = (n / 4 + 4 * kArThreads - 1) / (4 * kArThreads);      // >= 4 float4 per thread
+  if (blocks < 1) blocks = 1;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  PEFT_REQUIRE(world == 1 || pad_base + 2 * blocks * world <= pad_slots, "peft_allreduce_sgd: signal pad too small (%d slots, need %lld)",
+               pad_slots, pad_base + 2 * blocks * world);
+  AllreduceSgdArgs a{};
+  a.peer_grads = reinterpret_cast<const float* const*>(peer_grads);
+  a.peer_pads = reinterpret_cast<uint32_t* const*>(peer_pads);
+  a.grad = grad; a.param = param; a.momentum = momentum; a.lr = lr; a.n = n; a.rank = rank; a.world = world;
+  a.mu = mu; a.weight_decay = weight_decay; a.zero_grad = zero_grad; a.pad_base = pad_base;
+  allreduce_sgd_kernel<<<(unsigned)blocks, kArThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

@@ -71,7 +71,6 @@ static SkWorkspace* sk_workspace() {
   SkWorkspace& w = per_dev[dev];
   if (!w.tried) {
     w.tried = true;
-    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
     const size_t clusters = 128, slot = (size_t)2 * kEpiWarps * 1024 * sizeof(float4);
     void* a = nullptr;
     void* f = nullptr;
@@ -81,7 +80,6 @@ static SkWorkspace* sk_workspace() {
       w.flags = reinterpret_cast<int*>(f);
     } else {
       (void)cudaGetLastError();
-      (void)st;
     }
   }
   return w.ws ? &w : nullptr;

@@ -55,6 +55,107 @@ class GradBucket:
         self.flat.mul_(1.0 / ws)
 
 
+class FusedSGDBucket(GradBucket):
+    """GradBucket + flat parameter / momentum replicas + ONE kernel per step for `all-reduce(mean) -> SGD-momentum update ->
+    zero the bucket` ("fuse SGD-momentum into the all-reduce").
+
+    replaces, in the data-parallel step: `bucket.all_reduce_mean()` (an NCCL kernel + a scaling kernel), `torch.optim.SGD.step()`
+    (multi_tensor_apply kernels) and `bucket.zero()` of the next step.  Optimiser semantics = torch.optim.SGD(lr, momentum,
+    dampening=0, weight_decay, nesterov=False) as built by few_shot/vision_benchmark/optim/build.py:120-159.
+
+    * every trainable parameter becomes a view of one flat fp32 buffer (`p.data` is re-pointed; names, shapes, state_dict are
+      unchanged), its `.grad` a view of the flat bucket, and the momentum lives in a third flat buffer;
+    * with world size > 1 the bucket is allocated in torch symmetric memory (NVLink peer mapping): the kernel
+      (csrc/allreduce_sgd_sm100.cuh) reads every peer's bucket directly and synchronises through the signal pads, so no NCCL
+      call is on the step path; all ranks compute bit-identical parameters;
+    * `lr` is a device scalar: `set_lr()` changes it without re-capturing a CUDA graph of the step.
+    CPU tensors (the gloo tests of the host logic) take the unfused torch path with the same arithmetic.
+    """
+
+    MAX_BLOCKS = 32                     # csrc/allreduce_sgd_sm100.cuh kArMaxBlocks
+
+    def __init__(self, params, lr, momentum=0.9, weight_decay=0.0, process_group=None):
+        params = [p for p in params if p.requires_grad]
+        if not params:
+            raise ValueError("FusedSGDBucket: no trainable parameters")
+        dev = params[0].device
+        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = dist.get_rank(process_group) if self.world > 1 else 0
+        n = sum(p.numel() for p in params)
+        self.padded = (n + 3) // 4 * 4
+        self._symm = None
+        flat = None
+        if dev.type == "cuda" and self.world > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            group = process_group if process_group is not None else dist.group.WORLD
+            need = 2 * self.MAX_BLOCKS * self.world          # 2 barriers x blocks x ranks, uint32 slots
+            if symm_mem.get_signal_pad_size() // 4 < 2 * need:
+                symm_mem.set_signal_pad_size(8 * need)        # bytes; must precede the first symmetric allocation
+            flat = symm_mem.empty(self.padded, dtype=torch.float32, device=dev)
+            flat.zero_()
+            self._symm = symm_mem.rendezvous(flat, group)
+            self.pad_slots = symm_mem.get_signal_pad_size() // 4
+            if self.pad_slots < 2 * need:
+                raise RuntimeError(f"symmetric-memory signal pad too small ({self.pad_slots} slots, need {2 * need})")
+            # the first slots of the pad belong to torch's own barrier / put_signal helpers: this kernel uses the tail
+            self.pad_base = self.pad_slots - need
+        # GradBucket.__init__ allocates its own flat buffer: build the views by hand on the (possibly symmetric) buffer
+        self.params = params
+        self.numel = n
+        self.flat = flat if flat is not None else torch.zeros(self.padded, device=dev, dtype=torch.float32)
+        self.group = process_group
+        self.flat_param = torch.zeros(self.padded, device=dev, dtype=torch.float32)
+        self.flat_mom = torch.zeros(self.padded, device=dev, dtype=torch.float32)
+        self.lr_dev = torch.full((1,), float(lr), device=dev, dtype=torch.float32)
+        self.momentum, self.weight_decay = float(momentum), float(weight_decay)
+        off = 0
+        with torch.no_grad():
+            for p in params:
+                if p.dtype != torch.float32:
+                    raise TypeError("FusedSGDBucket expects fp32 trainable parameters")
+                k = p.numel()
+                self.flat_param[off:off + k].copy_(p.detach().reshape(-1))
+                p.data = self.flat_param[off:off + k].view_as(p)
+                p.grad = self.flat[off:off + k].view_as(p)
+                off += k
+        if self._symm is not None:
+            self._symm.barrier()        # every rank's bucket is zeroed and mapped before the first step
+
+    @property
+    def nbytes(self):
+        return self.numel * 4
+
+    def set_lr(self, lr):
+        self.lr_dev.fill_(float(lr))
+
+    def step(self):
+        """all-reduce(mean) + SGD-momentum update + zero the bucket, in one kernel (CUDA) — call right after backward()."""
+        if self.flat.is_cuda:
+            from . import _lib
+            sm = self._symm
+            _lib.check(_lib.load().peft_allreduce_sgd(
+                sm.buffer_ptrs_dev if sm is not None else 0, sm.signal_pad_ptrs_dev if sm is not None else 0, self.rank, self.world,
+                self.flat.data_ptr(), self.flat_param.data_ptr(), self.flat_mom.data_ptr(), self.padded, self.lr_dev.data_ptr(),
+                self.momentum, self.weight_decay, 1, getattr(self, "pad_base", 0), getattr(self, "pad_slots", 0),
+                torch.cuda.current_stream().cuda_stream), "peft_allreduce_sgd")
+            self._stepped = True
+            return
+        # CPU tensors (gloo tests): the same arithmetic, unfused
+        self.all_reduce_mean()
+        with torch.no_grad():
+            g = self.flat + self.weight_decay * self.flat_param
+            self.flat_mom.mul_(self.momentum).add_(g)
+            self.flat_param.sub_(self.lr_dev * self.flat_mom)
+            self.flat.zero_()
+        self._stepped = True
+
+    def zero(self, force=False):
+        """step() leaves the bucket zeroed, so in the `backward -> step` rhythm of train_one this is a no-op after the first
+        step (one memset launch less per step).  `force=True` clears gradients accumulated without a step()."""
+        if force or not getattr(self, "_stepped", False):
+            self.flat.zero_()
+
+
 class GlobalBatchNorm1d(torch.nn.Module):
     """BatchNorm1d(affine=False) whose TRAIN-mode statistics are taken over the global batch (all ranks), so that an N-rank
     step equals the 1-rank step on the concatenated batch (SURVEY §8e "BN head").  The reference head is

@@ -23,7 +23,8 @@ import torch.nn.functional as F
 
 class GraphedTrainStep:
     def __init__(self, model, bucket, optimizer, images, labels, criterion=None, warmup=3):
-        """`model(images) -> logits`; `bucket` = peft_b200.dist.GradBucket over the trainables; `images` / `labels` are
+        """`model(images) -> logits`; `bucket` = peft_b200.dist.GradBucket over the trainables (`optimizer` = a torch
+        optimizer) or a peft_b200.dist.FusedSGDBucket (`optimizer` = None: its step() is the optimiser); `images` / `labels` are
         example CUDA tensors fixing shape and dtype (their contents are used for the warm-up steps)."""
         if not images.is_cuda:
             raise RuntimeError("GraphedTrainStep needs CUDA tensors (no CPU fallback)")
@@ -56,8 +57,11 @@ class GraphedTrainStep:
         out = self.model(self.images)
         loss = self.criterion(out, self.labels)
         loss.backward()
-        self.bucket.all_reduce_mean()
-        self.optimizer.step()
+        if self.optimizer is None:
+            self.bucket.step()                  # FusedSGDBucket: all-reduce + SGD + zeroing in one kernel
+        else:
+            self.bucket.all_reduce_mean()
+            self.optimizer.step()
         return loss.detach(), out.detach()
 
     def release(self):

@@ -92,3 +92,45 @@ def test_global_batchnorm_two_ranks_equals_single_rank():
     for p in procs:
         p.join(timeout=60)
     assert all(ok for _, ok in res), res
+
+
+def _fused_worker(rank, world, port, q):
+    """Host logic of FusedSGDBucket on CPU tensors (gloo): flat parameter / gradient / momentum views and the unfused
+    arithmetic == torch.optim.SGD on the concatenated batch."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from peft_b200.dist import FusedSGDBucket
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(8, 3)
+    ref = torch.nn.Linear(8, 3)
+    ref.load_state_dict(lin.state_dict())
+    bucket = FusedSGDBucket(list(lin.parameters()), lr=0.1, momentum=0.9, weight_decay=1e-2)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-2)
+    x = torch.randn(6, 8, generator=torch.Generator().manual_seed(1))
+    y = torch.randn(6, 3, generator=torch.Generator().manual_seed(2))
+    xs, ys = x[rank * 3:(rank + 1) * 3], y[rank * 3:(rank + 1) * 3]
+    for _ in range(3):
+        bucket.zero()
+        ((lin(xs) - ys) ** 2).mean().backward()
+        bucket.step()
+        opt.zero_grad()
+        ((ref(x) - y) ** 2).mean().backward()
+        opt.step()
+    ok = all(torch.allclose(a, b, atol=1e-6) for a, b in zip(lin.parameters(), ref.parameters()))
+    ok = ok and float(bucket.flat.abs().max()) == 0.0
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_fused_sgd_bucket_two_ranks_cpu():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fused_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok in res), res

@@ -87,6 +87,67 @@ def _worker(rank, world, port, precision, q):
     dist.destroy_process_group()
 
 
+def _fused_worker(rank, world, port, q):
+    """3 fused steps (peft_allreduce_sgd over symmetric memory) on 2 ranks vs 3 steps of torch.optim.SGD on the concatenated
+    batch in one process: parameters after the steps must agree (fp32 mode), and be bit-identical across the ranks."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from oracle import synth
+    from peft_b200.dist import FusedSGDBucket
+    cfg, clf = _build("fp32", True, dev)
+    B = 16
+    images, labels = synth.make_batch(cfg, B)
+    lo, hi = rank * B // world, (rank + 1) * B // world
+    trainable = [p for p in clf.parameters() if p.requires_grad]
+    bucket = FusedSGDBucket(trainable, lr=0.05, momentum=0.9, weight_decay=1e-3)
+    for _ in range(3):
+        bucket.zero()
+        F.cross_entropy(clf(images[lo:hi].to(dev)), labels[lo:hi].to(dev)).backward()
+        bucket.step()
+    torch.cuda.synchronize()
+    mine = torch.cat([p.detach().float().reshape(-1) for p in trainable])
+    both = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(both, mine)
+    out = None
+    if rank == 0:
+        _, ref = _build("fp32", False, dev)
+        rt = [p for p in ref.parameters() if p.requires_grad]
+        opt = torch.optim.SGD(rt, lr=0.05, momentum=0.9, weight_decay=1e-3)
+        for _ in range(3):
+            opt.zero_grad()
+            F.cross_entropy(ref(images.to(dev)), labels.to(dev)).backward()
+            opt.step()
+        want = torch.cat([p.detach().float().reshape(-1) for p in rt])
+        start = torch.cat([p.detach().float().reshape(-1) for p in [q_ for q_ in _build("fp32", False, dev)[1].parameters() if q_.requires_grad]])
+        moved = float((want - start).norm())
+        out = (float((mine - want).norm()) / (moved + 1e-30), bool(torch.equal(both[0], both[1])), moved)
+    q.put((rank, out))
+    dist.barrier()
+    torch.cuda.synchronize()
+    dist.destroy_process_group()
+
+
+def test_two_rank_fused_allreduce_sgd():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fused_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=120)
+    err, identical, moved = res[0]
+    print(f"[dist fused] 2-rank fused all-reduce + SGD vs 1-rank torch SGD after 3 steps: update error {err:.3e} of |update| {moved:.3e}, "
+          f"ranks bit-identical: {identical}")
+    assert identical and err < 1e-4, (err, identical)
+
+
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-5), ("bf16", 2e-2)])
 def test_two_rank_step_equals_one_rank_step(precision, tol):
     if torch.cuda.device_count() < 2:
