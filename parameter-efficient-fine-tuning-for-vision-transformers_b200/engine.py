@@ -145,13 +145,13 @@ class _Workspace:
             self.dz = e(M, m)
             self.gh = e(M, D, dt=f32)                                # gradient w.r.t. h (fp32) and its bf16 copy
             self.ghb = self.gh if fp32_mode else e(M, D)
+        self.ones = torch.zeros(M, 16, device=dev, dtype=bf)
+        self.ones[:, 0] = 1.0                      # bias sums of the fp32 mode and the (tiny) patch-embed bias
+        self.mean_pre = e(M, dt=f32); self.rstd_pre = e(M, dt=f32)      # clip ln_pre statistics (its parameters may be trainable)
         if cfg.train_all:
             # everything a weight-gradient product needs that the PEFT path recomputes or never keeps
             self.xn2_l = [e(M, D) for _ in range(dep)]
             self.act_l = [e(M, F) for _ in range(dep)]
-            self.ones = torch.zeros(M, 16, device=dev, dtype=bf)
-            self.ones[:, 0] = 1.0                  # bias sums of the fp32 mode and the (tiny) patch-embed bias
-            self.mean_pre = e(M, dt=f32); self.rstd_pre = e(M, dt=f32)
         self.generation = 0
 
 
@@ -247,6 +247,38 @@ class VitEngine:
         self.frozen_loaded = True
         self._opgen += 1
 
+    # vectors of the tower (biases, LayerNorm gains / biases): the tensors that "bias tuning" / "LayerNorm tuning" train TOGETHER
+    # with an adapter (FL/tools/finetune_bias.py, finetune_layernorm.py).  They are re-read every forward (cheap) and their
+    # gradients are column sums / LayerNorm parameter gradients — no weight-gradient product is involved.
+    SMALL_SLOTS = ("ln1_w", "ln1_b", "qkv_b", "proj_b", "ln2_w", "ln2_b", "fc1_b", "fc2_b")
+
+    def small_keys(self):
+        keys = _TIMM_KEYS if self.cfg.dialect == "timm" else _CLIP_KEYS
+        out = {keys[s].format(i=i): (s, i) for s in self.SMALL_SLOTS for i in range(self.cfg.depth)}
+        fin = ("norm.weight", "norm.bias") if self.cfg.dialect == "timm" else ("ln_post.weight", "ln_post.bias")
+        out[fin[0]] = ("lnf_w", -1)
+        out[fin[1]] = ("lnf_b", -1)
+        if self.cfg.dialect == "timm":
+            out["patch_embed.proj.bias"] = ("patch_b", -1)
+        else:
+            out["ln_pre.weight"] = ("lnpre_w", -1)
+            out["ln_pre.bias"] = ("lnpre_b", -1)
+        return out
+
+    def load_small(self, named):
+        """named = {reference key: tensor} of trainable tower vectors: refresh the engine's copies (every forward)."""
+        table = self.small_keys()
+        slots = dict(ln1_w=self.ln1_w, ln1_b=self.ln1_b, qkv_b=self.bqkv, proj_b=self.bproj, ln2_w=self.ln2_w, ln2_b=self.ln2_b,
+                     fc1_b=self.bfc1, fc2_b=self.bfc2)
+        with torch.no_grad():
+            for k, t in named.items():
+                s_, i = table[k]
+                if i < 0:
+                    getattr(self, {"patch_b": "patch_b"}.get(s_, s_)).copy_(t.detach().to(self.dev, torch.float32).reshape(-1))
+                else:
+                    slots[s_][i].copy_(t.detach().to(self.dev, torch.float32).reshape(-1))
+        self._opgen += 1
+
     def _pad_k(self, w2d):
         kp = self.cfg.patch_k
         return w2d if w2d.shape[1] == kp else torch.nn.functional.pad(w2d, (0, kp - w2d.shape[1]))
@@ -324,9 +356,7 @@ class VitEngine:
         ops.gemm(w.patches, self.patch_w, w.pe, bias=self.patch_b)
         if cfg.dialect == "clip":
             ops.assemble_tokens(w.pe, self.cls, self.pos, w.tokens, B, L, D)
-            ta = cfg.train_all
-            ops.layernorm_fwd(w.tokens, self.lnpre_w, self.lnpre_b, w.x0[0], w.mean_pre if ta else None,
-                              w.rstd_pre if ta else None, cfg.eps)
+            ops.layernorm_fwd(w.tokens, self.lnpre_w, self.lnpre_b, w.x0[0], w.mean_pre, w.rstd_pre, cfg.eps)
         else:
             ops.assemble_tokens(w.pe, self.cls, self.pos, w.x0[0], B, L, D)
         scale = 64 ** -0.5
@@ -381,9 +411,11 @@ class VitEngine:
         return feat
 
     # ------------------------------------------------------------------ backward
-    def backward(self, dfeat, generation=None):
+    def backward(self, dfeat, generation=None, small=None):
         """`generation` = the engine's `_fwd_generation` right after the forward this backward belongs to (the autograd
-        node records it); a later forward at the same batch size has overwritten the saved activations."""
+        node records it); a later forward at the same batch size has overwritten the saved activations.
+        `small`: reference keys of tower vectors (biases, LayerNorm parameters) whose gradients are wanted as well; they come
+        back as the 4th result {key: fp32 grad}."""
         cfg = self.cfg
         D, L, H, dep, r, rp = cfg.width, cfg.seq, cfg.heads, cfg.depth, cfg.rank, cfg.rank_pad
         B = dfeat.shape[0]
@@ -394,15 +426,51 @@ class VitEngine:
         dfeat = dfeat.contiguous().float()
         w.g.zero_()
         w.gb.zero_()
+        drop = getattr(w, "drop", None)
+        # ---- gradients of trainable tower vectors (bias / LayerNorm tuning next to an adapter)
+        SG = {}
+        table = self.small_keys() if small else {}
+        want_slot = {}
+        for k in (small or ()):
+            want_slot[table[k]] = k
+        if small and drop is not None:
+            raise NotImplementedError("stochastic depth together with trainable tower biases / LayerNorms is not supported")
+        zvec = lambda n_: torch.zeros(n_, device=self.dev, dtype=torch.float32)
+
+        def ln_pg(slot_w, slot_b, i):
+            """(dgamma, dbeta) buffers if either LayerNorm parameter of this slot is trainable, else (None, None)."""
+            kw_, kb_ = want_slot.get((slot_w, i)), want_slot.get((slot_b, i))
+            if kw_ is None and kb_ is None:
+                return None, None
+            dg_, db_ = zvec(D), zvec(D)
+            if kw_ is not None:
+                SG[kw_] = dg_
+            if kb_ is not None:
+                SG[kb_] = db_
+            return dg_, db_
+
+        def bias_grad(slot, i, dY):
+            k_ = want_slot.get((slot, i))
+            if k_ is None:
+                return
+            n_ = dY.shape[1]
+            if cfg.precision == "fp32":
+                c16 = torch.zeros(16, n_, device=self.dev, dtype=torch.float32)
+                ops.tn_reduce(w.ones[:dY.shape[0]], dY, c16)
+                SG[k_] = c16[0]
+            else:
+                SG[k_] = ops.colsum(dY, zvec(n_))
+
+        need_x0 = any(sl in ("patch_b", "lnpre_w", "lnpre_b") for sl, _ in want_slot)     # gradient w.r.t. the tower input
         xcls = w.x0[dep].view(B, L * D)[:, :D]
         gcls = w.g.view(B, L * D)[:, :D]
         gbcls = w.gb.view(B, L * D)[:, :D]
+        dgf, dbf = ln_pg("lnf_w", "lnf_b", -1)
         if self.vproj is None:
-            ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
+            ops.layernorm_bwd_f32g(dfeat, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dgf, dbf)
         else:
             ops.gemm(dfeat.to(cfg.cdt), self.vproj, w.dyf)                       # dy = dfeat proj^T
-            ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls)
-        drop = getattr(w, "drop", None)
+            ops.layernorm_bwd_f32g(w.dyf, xcls, w.meanf, w.rstdf, self.lnf_w, None, gcls, gbcls, dgf, dbf)
         rs = (lambda i, j: None) if drop is None else (lambda i, j: drop[i, j])
         dDn = dUpT = None
         if r:
@@ -433,12 +501,16 @@ class VitEngine:
                 ops.layernorm_bwd_f32g(w.dxn, w.hf[i], w.mean_a[i], w.rstd_a[i], self.lga[i], w.g, w.gh, w.ghb, dlg[i], dlb[i])
                 gmlp = w.ghb
             # MLP: dh = (g W2) * act'(h) ; dxn2 = dh W1 ; g += LN2'(dxn2)
+            bias_grad("fc2_b", i, gmlp)
             ops.gemm(gmlp, self.wfc2T[i], w.dh, epilogue=self.act_bwd, aux=w.h[i], rowscale=rs(i, 1))
+            bias_grad("fc1_b", i, w.dh)
             ops.gemm(w.dh, self.wfc1T[i], w.dxn)
-            ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb)
-            if i == 0 and not rp:
+            dg2, db2 = ln_pg("ln2_w", "ln2_b", i)
+            ops.layernorm_bwd_f32g(w.dxn, w.x1[i], w.mean2[i], w.rstd2[i], self.ln2_w[i], w.g, w.g, w.gb, dg2, db2)
+            if i == 0 and not rp and not small:
                 break       # nothing trainable is upstream of block 0's attention when there is no q/v adapter
             # attention: d_o = g Wproj ; dqkv = attn'(d_o)
+            bias_grad("proj_b", i, w.gb)
             ops.gemm(w.gb, self.wprojT[i], w.d_o, rowscale=rs(i, 0))
             ops.attention_bwd(w.qkv[i], w.o[i], w.d_o, w.lse2[i], w.delta, w.dqkv, B, H, L, scale)
             if rp and cfg.dialect == "clip":
@@ -464,19 +536,28 @@ class VitEngine:
                     ops.tn_reduce(w.xn1[i][:, D + c:D + c + cw], dq, dUpT[i, c:c + cw])            # dUp^T = p^T dqkv
                     if not cfg.dense_delta:
                         ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])  # dDn = dp^T x
-            if i == 0:
+            bias_grad("qkv_b", i, w.dqkv[:, :3 * D])
+            dg1, db1 = ln_pg("ln1_w", "ln1_b", i)
+            if i == 0 and dg1 is None and not need_x0:
                 break       # block 0's input gradient feeds only the frozen patch embedding: no dX product, no LN1'
             if rp:
                 ops.gemm(w.dqkv, self.wqkvT[i], w.dxn)                              # dxn1 = [dqkv|dp] [W^T|Dn^T]^T
             else:
                 ops.gemm(w.dqkv[:, :3 * D], self.wqkvT[i][:, :3 * D], w.dxn)
-            ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb)
-        # the patch embedding / ln_pre are frozen and the images need no gradient: stop here.
+            ops.layernorm_bwd_f32g(w.dxn, w.x0[i], w.mean1[i], w.rstd1[i], self.ln1_w[i], w.g, w.g, w.gb, dg1, db1)
+        # the patch embedding / ln_pre weights are frozen and the images need no gradient: only their trainable VECTORS go on
+        if need_x0:
+            g3 = w.g.view(B, L, D)
+            if cfg.dialect == "clip":
+                dgp, dbp = ln_pg("lnpre_w", "lnpre_b", -1)
+                ops.layernorm_bwd_f32g(w.g, w.tokens, w.mean_pre, w.rstd_pre, self.lnpre_w, None, w.x1[0], None, dgp, dbp)
+            else:
+                SG[want_slot[("patch_b", -1)]] = g3[:, 1:, :].sum((0, 1))        # conv bias: sum over the patch tokens (glue)
         if m:
             bng = (dWd, dbd16[:, 0], dWuT.transpose(1, 2), dbu16[:, 0], dlg, dlb)
         if r:
-            return (None if cfg.dense_delta else dDn[:, :r]), dUpT[:, :r], bng
-        return None, None, bng
+            return (None if cfg.dense_delta else dDn[:, :r]), dUpT[:, :r], bng, SG
+        return None, None, bng, SG
 
 
 
@@ -629,20 +710,29 @@ def backbone_full(engine: VitEngine, images, named_tensors):
 
 class _BackboneFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, engine, images, Dn, UpT, drop, *bn):
+    def forward(ctx, engine, images, Dn, UpT, drop, nbn, small_names, *rest):
         ctx.engine = engine
-        ctx.nbn = len(bn)
+        ctx.nbn = nbn
+        bn, small = rest[:nbn], rest[nbn:]
+        ctx.small_names = small_names
+        if small_names:
+            engine.load_small(dict(zip(small_names, small)))
         out = engine.forward(images, Dn, UpT, bn if bn else None, drop)
         ctx.generation = engine._fwd_generation
         return out
 
     @staticmethod
     def backward(ctx, dfeat):
-        dDn, dUpT, bng = ctx.engine.backward(dfeat, ctx.generation)
+        dDn, dUpT, bng, SG = ctx.engine.backward(dfeat, ctx.generation, ctx.small_names or None)
         extra = tuple(bng) if bng is not None else (None,) * ctx.nbn
-        return (None, None, dDn, dUpT, None) + extra
+        small = tuple(SG.get(k) for k in ctx.small_names)
+        return (None, None, dDn, dUpT, None, None, None) + extra + small
 
 
-def backbone(engine: VitEngine, images, Dn=None, UpT=None, bn=None, drop=None):
-    """Differentiable (w.r.t. Dn / UpT / the bottleneck-adapter operands) visual-tower feature extraction."""
-    return _BackboneFn.apply(engine, images, Dn, UpT, drop, *(bn if bn is not None else ()))
+def backbone(engine: VitEngine, images, Dn=None, UpT=None, bn=None, drop=None, small=None):
+    """Differentiable (w.r.t. Dn / UpT / the bottleneck-adapter operands and, optionally, trainable tower vectors `small` =
+    [(reference key, tensor)]: biases and LayerNorm parameters) visual-tower feature extraction."""
+    bn = tuple(bn) if bn is not None else ()
+    small = list(small or [])
+    names = tuple(k for k, _ in small)
+    return _BackboneFn.apply(engine, images, Dn, UpT, drop, len(bn), names, *bn, *[t for _, t in small])

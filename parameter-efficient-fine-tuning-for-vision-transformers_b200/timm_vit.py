@@ -373,10 +373,10 @@ def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck, drop=None
     if not x.is_cuda:
         raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
     tensors = tower_tensors(model, model._tower_keys)
-    full = torch.is_grad_enabled() and any(t.requires_grad for _, t in tensors)
-    if full and model.adapter_kind != "none":
-        raise NotImplementedError("training tower weights together with an adapter is not supported: freeze the tower "
-                                  "(PEFT) or build the model with adapter='none' (full fine-tuning / Fastfood)")
+    grad = torch.is_grad_enabled()
+    trainable = [(k, t) for k, t in tensors if t.requires_grad]
+    with_adapter = model.adapter_kind != "none"
+    full = grad and bool(trainable) and not with_adapter
     slot = "_engine_full" if full else "_engine"
     eng = getattr(model, slot, None)
     precision = getattr(model, "precision", "bf16")      # "fp32": verification mode (plain fp32 kernels, 1e-5 gate)
@@ -388,13 +388,26 @@ def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck, drop=None
         if drop is not None:
             raise NotImplementedError("stochastic depth is not supported in full (train-all) mode")
         return backbone_full(eng, x, tensors)
+    # adapter + bias tuning / LayerNorm tuning (FL/tools/finetune_bias.py, finetune_layernorm.py on an adapter model): trainable
+    # tower VECTORS (biases, LayerNorm gains / biases) are re-read every forward and get their gradients inside the PEFT
+    # backward (column sums, LayerNorm parameter gradients).  Weight matrices next to an adapter would need dW products.
+    small = [(k, t) for k, t in trainable if k in eng.small_keys()] if with_adapter else []
+    if grad and with_adapter and len(small) != len(trainable):
+        other = [k for k, _ in trainable if k not in eng.small_keys()]
+        raise NotImplementedError(f"training the tower tensors {other[:4]}... together with an adapter is not supported: weight "
+                                  "matrices need dW products — freeze them (bias / LayerNorm tuning works) or build the model "
+                                  "with adapter='none' (full fine-tuning)")
+    small_names = {k for k, _ in small}
     cacheable = all(isinstance(t, nn.Parameter) for _, t in tensors)
-    sig = (slot,) + tuple((k, t.data_ptr(), t._version) for k, t in tensors) if cacheable else None
+    sig = (slot,) + tuple((k, t.data_ptr(), t._version) for k, t in tensors if k not in small_names) if cacheable else None
     if sig is None or sig != model._frozen_sig:
         eng.load_frozen({k: t.detach() for k, t in tensors})
         model._frozen_sig = sig
+    if small and not grad:                        # eval / no_grad forward: still re-read the trained vectors, no autograd inputs
+        eng.load_small({k: t for k, t in small})
+        small = None
     Dn, UpT = lowrank()
-    return backbone(eng, x, Dn, UpT, bottleneck(), drop)
+    return backbone(eng, x, Dn, UpT, bottleneck(), drop, small)
 
 
 class VisionTransformer(nn.Module):
