@@ -22,7 +22,7 @@ import torch
 import torch.nn as nn
 
 from .timm_vit import (Adapter, HyperComplexAdapter, _no_eager, add_qv_adapter_params, bottleneck_cfg,
-                       bottleneck_operands, lowrank_operands, lowrank_rank, run_tower)
+                       bottleneck_operands, kron_is_dense, lowrank_operands, lowrank_rank, run_tower)
 
 
 class LayerNorm(nn.LayerNorm):
@@ -121,6 +121,8 @@ class VisionTransformer(nn.Module):
         extra = dict(rank=lowrank_rank(blocks[0].attn, self.adapter_kind),
                      out_dim=(self.output_dim if getattr(self, "proj", None) is not None else 0),
                      **bottleneck_cfg(blocks[0], self.adapter_kind))
+        if self.adapter_kind == "kron" and kron_is_dense(blocks[0].attn):
+            extra["dense_delta"] = True          # large-n KAdaptation (the committed phm_dim = 768 through FS/model.py:170-193)
         return run_tower(self, x, "clip", self._geom, extra,
                          lambda: lowrank_operands([b.attn for b in blocks], self.adapter_kind),
                          lambda: bottleneck_operands(blocks, self.adapter_kind))

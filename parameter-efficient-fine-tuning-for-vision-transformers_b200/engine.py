@@ -233,8 +233,8 @@ class VitEngine:
             else:
                 self.vproj = None
         if cfg.dense_delta:
-            if cfg.dialect != "timm" or cfg.rank != D:
-                raise NotImplementedError("the dense q/v update is built for the timm dialect with rank == width")
+            if cfg.rank != D:
+                raise NotImplementedError("the dense q/v update needs rank == width")
             self.wqkvT[:, :, 3 * D:] = torch.eye(D, device=dev, dtype=bf)       # [W^T | I]: dxn = dqkv W + dp
         if rp > 0:
             self.dn_bf = torch.zeros(dep, rp, D, device=dev, dtype=bf)
@@ -297,11 +297,12 @@ class VitEngine:
             return
         with torch.no_grad():
             self.upT_bf[:, :r].copy_(UpT)
-            if cfg.dense_delta:
+            if cfg.dense_delta and cfg.dialect == "timm":
                 self.wqkv[:, :, D:D + r].copy_(UpT.transpose(1, 2))
                 return
-            self.dn_bf[:, :r].copy_(Dn)
-            self.wqkvT[:, :, 3 * D:3 * D + r].copy_(Dn.transpose(1, 2))
+            if not cfg.dense_delta:
+                self.dn_bf[:, :r].copy_(Dn)
+                self.wqkvT[:, :, 3 * D:3 * D + r].copy_(Dn.transpose(1, 2))
             if cfg.dialect == "clip":
                 self.up2T_bf[:, :r, :D].copy_(UpT[:, :, :D])
                 self.up2T_bf[:, :r, D:].copy_(UpT[:, :, 2 * D:])
@@ -365,7 +366,10 @@ class VitEngine:
             ops.layernorm_fwd(w.x0[i], self.ln1_w[i], self.ln1_b[i], xn1[:, :D], w.mean1[i], w.rstd1[i], cfg.eps)
             if rp and cfg.dialect == "clip":
                 # reference order (FS/model.py:967,981-986): q/sqrt(hd) first, then += raw-reshaped update (Q1, Q2)
-                ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                    # p = LN1(x) Dn^T
+                if cfg.dense_delta:
+                    xn1[:, D:].copy_(xn1[:, :D])                                   # Dn = I: p is LN1(x) itself
+                else:
+                    ops.gemm(xn1[:, :D], self.dn_bf[i], xn1[:, D:])                # p = LN1(x) Dn^T
                 ops.gemm(xn1[:, :D], self.wqkv[i][:, :D], w.qkv[i], bias=self.bqkv[i])
                 ops.gemm(xn1[:, D:], self.up2_bf[i], w.dlt)                        # [dq | dv] = p Up^T
                 ops.clip_delta(w.qkv[i], w.dlt, B, H, L, 1.0 / scale, 1.0)
@@ -517,11 +521,19 @@ class VitEngine:
                 dq = w.dqkv[:, :3 * D]
                 ops.clip_delta(dq, w.dlt, B, H, L, 1.0 / scale, 1.0, backward=True)  # d[dq|dv] gathered back (Q1 inverse)
                 ops.gemm(w.dlt, self.up2T_bf[i], w.dqkv[:, 3 * D:])                 # dp = d[dq|dv] [Up_q;Up_v]
-                for c, cw in _tn_chunks(rp):
-                    pc = w.xn1[i][:, D + c:D + c + cw]
-                    ops.tn_reduce(pc, w.dlt[:, :D], dUpT[i, c:c + cw, :D])
-                    ops.tn_reduce(pc, w.dlt[:, D:], dUpT[i, c:c + cw, 2 * D:])
-                    ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
+                if rp > 128 and cfg.precision != "fp32":
+                    d2 = torch.empty(rp, 2 * D, device=self.dev, dtype=torch.float32)
+                    self._dw(w, w.xn1[i][:, D:], w.dlt, d2)                         # d[Up_q|Up_v]^T = p^T d[dq|dv]: one tensor-core product
+                    dUpT[i, :, :D].copy_(d2[:, :D])
+                    dUpT[i, :, 2 * D:].copy_(d2[:, D:])
+                else:
+                    for c, cw in _tn_chunks(rp):
+                        pc = w.xn1[i][:, D + c:D + c + cw]
+                        ops.tn_reduce(pc, w.dlt[:, :D], dUpT[i, c:c + cw, :D])
+                        ops.tn_reduce(pc, w.dlt[:, D:], dUpT[i, c:c + cw, 2 * D:])
+                if not cfg.dense_delta:
+                    for c, cw in _tn_chunks(rp):
+                        ops.tn_reduce(w.dqkv[:, 3 * D + c:3 * D + c + cw], w.xn1[i][:, :D], dDn[i, c:c + cw])
             elif rp > 128 and cfg.precision != "fp32":
                 dq = w.dqkv[:, :3 * D]
                 ops.gemm(dq, self.upT_bf[i], w.dqkv[:, 3 * D:])                    # dp = dqkv Up

@@ -38,6 +38,7 @@ CASES = {
     "clip_c1_kron_n4": (VitCfg(dialect="clip", adapter="kron", phm_dim=4, img=224, patch=32, depth=3), 5),
     "clip_c1_lora": (VitCfg(dialect="clip", adapter="lora", img=224, patch=32, depth=3), 7),
     "clip_none": (VitCfg(dialect="clip", adapter="none", img=64, patch=32, depth=2), 3),
+    "clip_kron_n64_dense": (VitCfg(dialect="clip", adapter="kron", phm_dim=64, img=64, patch=32, depth=2), 4),
     "clip_houlsby": (VitCfg(dialect="clip", adapter="houlsby", img=64, patch=32, depth=2), 8),
     "clip_compacter": (VitCfg(dialect="clip", adapter="compacter", img=64, patch=32, depth=2), 6),
     "clip_c4_houlsby_L257": (VitCfg(dialect="clip", adapter="houlsby", img=224, patch=14, width=1024, heads=16, out_dim=768, depth=2), 2),
