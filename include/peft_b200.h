@@ -175,7 +175,9 @@ int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, in
  * Per tensor p (descriptor below): DD = numel, LL = 2^ll >= DD, coef = 1 / (divisor * sqrt(DD / LL)) with
  * divisor = sqrt(LL * sum(G^2)) (fastfood.py:124-148).  Device arrays, concatenated over tensors:
  *   pi_lo [sum LL] uint16 = Pi[j] mod min(LL, wn);  gg [sum LL] fp32 = G;  bsign [T, wn] fp32 = B[:wn] (zero padded);
- *   theta0 / theta / dtheta fp32 indexed by off_dd;  scratch [sum LL] fp32;  wu [T, wn] fp32 scratch;  counters [T] int.
+ *   theta0 / theta / dtheta fp32 indexed by off_dd;  scratch [sum LL] fp32;  wu [T, wn] fp32 scratch;  counters [T + 1] int
+ *   (per-tensor completion counters + one work-item ticket: items are taken by atomic ticket, never by blockIdx, so an item
+ *   only ever waits on items that running CTAs already hold — forward progress is independent of block dispatch order).
  * wn = power of two >= d, <= 4096.  `items` is a device array of (tensor, tile | kind << 30) int pairs built by the
  * caller — kind 1 = "high" tile (tensors with ll > 13: tiles 0 .. LL/8192 - 1), kind 0 = "low" block (blocks
  * 0 .. ceil(DD/8192) - 1).  Forward lists a tensor's high tiles BEFORE its low blocks, backward its low blocks BEFORE its

@@ -155,7 +155,7 @@ extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_
   if (rc) return rc;
   PEFT_REQUIRE(dtheta && tensors && items && pi_lo && gg && bsign && wu && scratch && counters && dV, "peft_fastfood_bwd: null operand");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  PEFT_CUDA_CHECK(cudaMemsetAsync(counters, 0, (size_t)T * sizeof(int), s));
+  PEFT_CUDA_CHECK(cudaMemsetAsync(counters, 0, (size_t)(T + 1) * sizeof(int), s));     // [T] per-tensor counters + the item ticket
   PEFT_CUDA_CHECK(cudaMemsetAsync(wu, 0, (size_t)T * wn * 4, s));
   FfArgs a{};
   a.tensors = tensors; a.items = reinterpret_cast<const int2*>(items); a.pi_lo = pi_lo; a.gg = gg; a.u = wu; a.scratch = scratch;

@@ -340,13 +340,18 @@ __global__ void __launch_bounds__(kFfThreads, 2) ff_fwd_kernel(FfArgs a) {
 // high tile: butterflies over bits [13, ll), times G, folded through Pi^T into wn bins (shared atomics, then global)
 // One CTA per item, 3 CTAs per SM.  A persistent cp.async-staged variant (like the forward) was measured SLOWER here
 // (910 vs 850 us on the ViT-B/32 set): the 16 shared-memory float atomics per thread compile to ATOMS.CAST.SPIN loops and
-// are the top stall (ncu: 29 % of samples), which a third resident CTA hides better than the staging does.  The spin on the
-// per-tensor counter relies on CTAs being dispatched in blockIdx order (producers first) and on producers never waiting.
+// are the top stall (ncu: 29 % of samples), which a third resident CTA hides better than the staging does.
 __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
   extern __shared__ float ff_smem[];
   float* s = ff_smem;
   float* bins = ff_smem + kFfTile;
-  const int2 it = a.items[blockIdx.x];
+  // Work items are handed out by an atomic TICKET, not by blockIdx: a CTA that spins on a per-tensor counter only ever waits
+  // for items with LOWER tickets, and those were taken by CTAs that are already running (producers never wait) — so forward
+  // progress does not depend on the order in which the hardware happens to dispatch thread blocks (MPS, preemption, debugger).
+  __shared__ int s_ticket;
+  if (threadIdx.x == 0) s_ticket = atomicAdd(a.counters + a.T, 1);
+  __syncthreads();
+  const int2 it = a.items[s_ticket];
   const peft_ff_tensor t = a.tensors[it.x];
   const int tid = threadIdx.x;
   const int tile = it.y & 0x3fffffff;

@@ -112,7 +112,7 @@ class FastfoodPlan:
         self.bsign = bsign.to(dev)
         mk = lambda items: torch.tensor(items, dtype=torch.int32).reshape(-1, 2).contiguous().to(dev)
         self.items_fwd, self.items_bwd, self.n_items = mk(fwd_items), mk(bwd_items), len(fwd_items)
-        self.counters = torch.zeros(T, dtype=torch.int32, device=dev)
+        self.counters = torch.zeros(T + 1, dtype=torch.int32, device=dev)      # per-tensor completion counters + the backward's item ticket
         self.scratch = torch.empty(off_ll, dtype=torch.float32, device=dev)
         self.wu = torch.zeros(T, self.wn, dtype=torch.float32, device=dev)
         self.theta0 = torch.zeros(off_dd, dtype=torch.float32, device=dev)
