@@ -91,7 +91,7 @@ def bench_reduce(M=50432):
     print(f"tn_reduce I=32 J=768  M={M}: {t:7.1f} us  {(M * (768 + 32) * 2) / t / 1e3:7.1f} GB/s")
 
 
-def bench_gemm(M=50432, iters=20, only=None):
+def bench_gemm(M=50432, iters=20, only=None, warm=2):
     cases = [("qkv   [x|p][W|Up]^T+b", 2304, 800, ops.EPI_STORE), ("proj  +resid f32", 768, 768, ops.EPI_RESID_F32),
              ("fc1   +GELU (h, act)", 3072, 768, ops.EPI_GELU), ("fc2   +resid f32", 768, 3072, ops.EPI_RESID_F32),
              ("fc2^T *gelu'(h)", 3072, 768, ops.EPI_DGELU), ("fc1^T store", 768, 3072, ops.EPI_STORE),
@@ -110,7 +110,7 @@ def bench_gemm(M=50432, iters=20, only=None):
             aux = torch.randn(M, N, device="cuda")
         elif epi == ops.EPI_DGELU:
             aux = torch.randn(M, N, device="cuda").to(torch.bfloat16)
-        t = timeit(lambda: ops.gemm(a, b, out, bias=bias, epilogue=epi, out2=out2, aux=aux), iters=iters, warm=2)
+        t = timeit(lambda: ops.gemm(a, b, out, bias=bias, epilogue=epi, out2=out2, aux=aux), iters=iters, warm=warm)
         print(f"gemm {name:24s} M={M} N={N} K={K}: {t:7.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TFLOP/s", flush=True)
 
 
@@ -349,6 +349,30 @@ if __name__ == "__main__":
             ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)
         bench_ln()
         bench_reduce()
+        torch.cuda.synchronize()
+    if what == "prof_once":   # exactly ONE launch of each hot kernel at the C3 shapes, for `ncu --set full -k regex:peft`
+        bench_gemm(iters=1, warm=0)
+        B, H, L = 256, 12, 197
+        D = H * 64
+        qkv = torch.randn(B * L, 3 * D, device="cuda").to(torch.bfloat16)
+        o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+        d_o = torch.randn(B * L, D, device="cuda").to(torch.bfloat16)
+        dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+        lse2 = torch.empty(B * H * L, device="cuda")
+        delta = torch.empty(B * H * L, device="cuda")
+        ops.attention_fwd(qkv, o, lse2, B, H, L, 0.125)
+        ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)
+        M = B * L
+        x = torch.randn(M, D, device="cuda"); gamma = torch.ones(D, device="cuda"); beta = torch.zeros(D, device="cuda")
+        y = torch.empty(M, D, device="cuda", dtype=torch.bfloat16); mean = torch.empty(M, device="cuda"); rstd = torch.empty(M, device="cuda")
+        ops.layernorm_fwd(x, gamma, beta, y, mean, rstd, 1e-6)
+        g32 = torch.randn(M, D, device="cuda"); gb = torch.empty(M, D, device="cuda", dtype=torch.bfloat16)
+        ops.layernorm_bwd_f32g(d_o, x, mean, rstd, gamma, g32, g32, gb)
+        wide = torch.randn(M, 800, device="cuda").to(torch.bfloat16)
+        out = torch.zeros(32, 2304, device="cuda")
+        ops.tn_reduce(wide[:, 768:800], dqkv, out)
+        out2 = torch.zeros(32, 768, device="cuda")
+        ops.tn_reduce(dqkv[:, :32], wide[:, :768], out2)
         torch.cuda.synchronize()
     if what in ("fold", "all"):
         bench_phm_fold()
