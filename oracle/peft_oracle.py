@@ -84,6 +84,7 @@ def gelu_new(x):
 # separates "the kernels compute the wrong gradient" from "a pre-activation within bf16 noise of 0 flipped its gate".
 GATE_RECORD = None
 GATE_OVERRIDE = {}
+GATE_CALLS = {}
 
 
 def houlsby_adapter(h, sd, pfx, eps=1e-5):
@@ -92,8 +93,12 @@ def houlsby_adapter(h, sd, pfx, eps=1e-5):
     z = F.layer_norm(h, (D,), sd[pfx + "adapter_norm_before.weight"], sd[pfx + "adapter_norm_before.bias"], eps)
     pre = F.linear(z, sd[pfx + "adapter_down.1.weight"], sd[pfx + "adapter_down.1.bias"])
     if GATE_RECORD is not None:
-        GATE_RECORD[pfx] = pre.detach()
+        GATE_RECORD.setdefault(pfx, []).append(pre.detach())      # one entry per application (AdapterDrop schedules apply twice)
     gate = GATE_OVERRIDE.get(pfx)
+    if isinstance(gate, list):                                    # masks per application, consumed in call order
+        n = GATE_CALLS.get(pfx, 0)
+        GATE_CALLS[pfx] = n + 1
+        gate = gate[n]
     z = F.relu(pre) if gate is None else pre * gate.to(pre.dtype)
     z = F.linear(z, sd[pfx + "adapter_up.weight"], sd[pfx + "adapter_up.bias"])
     return z + h
@@ -153,14 +158,19 @@ def drop_path(x, keep, keep_prob):
     return x.div(keep_prob) * keep.view(-1, 1, 1).to(x.dtype)
 
 
-def timm_block(x, sd, pfx, cfg: VitCfg, drop=None):
+def timm_block(x, sd, pfx, cfg: VitCfg, drop=None, use_adapter=None):
     """FS/kadaptation.py:273-277 (pre-norm branch); Houlsby variant FS/adapter.py (adapter after the MLP).
     drop = (keep_attn [B], keep_mlp [B], keep_prob) applies stochastic depth to the two branches (training mode)."""
     D = x.shape[-1]
     a = timm_attention(F.layer_norm(x, (D,), sd[pfx + "norm1.weight"], sd[pfx + "norm1.bias"], cfg.ln_eps), sd, pfx + "attn.", cfg)
     x = x + (a if drop is None else drop_path(a, drop[0], drop[2]))
     h = timm_mlp(F.layer_norm(x, (D,), sd[pfx + "norm2.weight"], sd[pfx + "norm2.bias"], cfg.ln_eps), sd, pfx + "mlp.")
-    if cfg.adapter == "houlsby":
+    layer = int(pfx.split(".")[-2])
+    if use_adapter is None:
+        use_adapter = not cfg.adapter_layers or layer in cfg.adapter_layers
+    if not use_adapter:
+        pass        # AdapterDrop (FS/adapterdrop.py:585-588): `blk(x, False, prev)` — the block's adapter is not applied
+    elif cfg.adapter == "houlsby":
         h = houlsby_adapter(h, sd, pfx + "adapter.", 1e-5)
     elif cfg.adapter == "compacter":
         h = compacter_adapter(h, sd, pfx + "compacter.", 1e-5)
@@ -177,7 +187,11 @@ def timm_forward_features(images, sd, cfg: VitCfg, drop_keep=None, drop_path_rat
     x = torch.cat((sd["cls_token"].expand(B, -1, -1), x), dim=1)
     x = x + sd["pos_embed"]
     dpr = [v.item() for v in torch.linspace(0, drop_path_rate, cfg.depth)]
-    for i in range(cfg.depth):
+    if cfg.block_schedule:
+        # FS/adapterdrop.py:582-588 as committed: every block is applied twice (see adapterdrop_reference_schedule)
+        for b, use in cfg.block_schedule:
+            x = timm_block(x, sd, f"blocks.{b}.", cfg, None, use_adapter=bool(use))
+    for i in range(0 if cfg.block_schedule else cfg.depth):
         drop = None if drop_keep is None else (drop_keep[i, 0], drop_keep[i, 1], 1.0 - dpr[i])
         x = timm_block(x, sd, f"blocks.{i}.", cfg, drop)
     x = F.layer_norm(x, (cfg.width,), sd["norm.weight"], sd["norm.bias"], cfg.ln_eps)
@@ -228,7 +242,10 @@ def clip_block(x, sd, pfx, cfg: VitCfg):
     x = x + clip_attention(F.layer_norm(x, (D,), sd[pfx + "ln_1.weight"], sd[pfx + "ln_1.bias"], 1e-5), sd, pfx + "attn.", cfg)
     h = F.layer_norm(x, (D,), sd[pfx + "ln_2.weight"], sd[pfx + "ln_2.bias"], 1e-5)
     h = F.linear(quick_gelu(F.linear(h, sd[pfx + "mlp.c_fc.weight"], sd[pfx + "mlp.c_fc.bias"])), sd[pfx + "mlp.c_proj.weight"], sd[pfx + "mlp.c_proj.bias"])
-    if cfg.adapter == "houlsby":
+    layer = int(pfx.split(".")[-2])
+    if cfg.adapter_layers and layer not in cfg.adapter_layers:
+        pass
+    elif cfg.adapter == "houlsby":
         h = houlsby_adapter(h, sd, pfx + "adapter.", 1e-5)
     elif cfg.adapter == "compacter":
         h = compacter_adapter(h, sd, pfx + "compacter.", 1e-5)

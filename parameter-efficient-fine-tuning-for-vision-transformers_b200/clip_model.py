@@ -121,6 +121,8 @@ class VisionTransformer(nn.Module):
         extra = dict(rank=lowrank_rank(blocks[0].attn, self.adapter_kind),
                      out_dim=(self.output_dim if getattr(self, "proj", None) is not None else 0),
                      **bottleneck_cfg(blocks[0], self.adapter_kind))
+        if getattr(self, "adapter_layers", None) is not None and extra.get("bottleneck"):
+            extra["bottleneck_layers"] = tuple(sorted(int(i) for i in self.adapter_layers))      # AdapterDrop: see timm_vit.py
         if self.adapter_kind == "kron" and kron_is_dense(blocks[0].attn):
             extra["dense_delta"] = True          # large-n KAdaptation (the committed phm_dim = 768 through FS/model.py:170-193)
         return run_tower(self, x, "clip", self._geom, extra,

@@ -39,6 +39,7 @@ class EngineCfg:
     out_dim: int = 0      # clip: visual projection width (0 = no projection)
     rank: int = 0         # low-rank q/v adapter columns r' (0 = no q/v adapter)
     bottleneck: int = 0   # Houlsby / Compacter bottleneck width after the MLP (0 = none; 64 in the reference)
+    bottleneck_layers: tuple = ()   # AdapterDrop (FS/adapterdrop.py:585-588): blocks that USE the bottleneck adapter; () = every block
     bn_act: str = "relu"  # "relu" (Houlsby, FS/adapter_model.py:304-311) | "gelu_tanh" (Compacter gelu_new, FS/compacter_model.py:376)
     dense_delta: bool = False  # q/v update given as dense H_q, H_v [D, D] (large-n KAdaptation "fold" variant):
                                # rank == width, Dn is the identity (not trainable) and UpT = [H_q | 0 | H_v]
@@ -61,6 +62,9 @@ class EngineCfg:
     @property
     def patch_k(self):
         return (3 * self.patch * self.patch + 7) // 8 * 8
+
+    def has_bn(self, i):
+        return bool(self.bottleneck) and (not self.bottleneck_layers or i in self.bottleneck_layers)
 
     @property
     def rank_pad(self):
@@ -387,7 +391,7 @@ class VitEngine:
             act = w.act_l[i] if cfg.train_all else w.act
             ops.layernorm_fwd(w.x1[i], self.ln2_w[i], self.ln2_b[i], xn2, w.mean2[i], w.rstd2[i], cfg.eps)
             ops.gemm(xn2, self.wfc1[i], w.h[i], bias=self.bfc1[i], epilogue=self.act_fwd, out2=act)
-            if not m:
+            if not cfg.has_bn(i):
                 ops.gemm(act, self.wfc2[i], w.x0[i + 1], bias=self.bfc2[i], epilogue=ops.EPI_RESID_F32, aux=w.x1[i], rowscale=rs(i, 1))
             else:
                 # x_{i+1} = x1 + h + up(act(down(LN_a(h)))),  h = mlp(ln2(x1))     (adapter_model.py:330-334 computed once, Q6)
@@ -492,7 +496,7 @@ class VitEngine:
             bn_dact = ops.EPI_DRELU if cfg.bn_act == "relu" else ops.EPI_DGELU_TANH
         for i in reversed(range(dep)):
             gmlp = w.gb                  # gradient w.r.t. the MLP output h (bf16 operand)
-            if m:
+            if cfg.has_bn(i):
                 # bottleneck adapter backward; g = dL/dx_{i+1} is also dL/dx1 (residual) and part of dL/dh
                 z, ones = w.zext[i][:, :m], w.zext[i][:, m:m + 16]
                 bsum = (lambda x, o16: ops.tn_reduce(ones, x, o16)) if cfg.precision == "fp32" else (lambda x, o16: ops.colsum(x, o16[0]))

@@ -41,6 +41,8 @@ class VitCfg:
     compacter_n_down: int = 32
     compacter_n_up: int = 4
     num_classes: int = 10
+    adapter_layers: tuple = ()     # AdapterDrop: blocks whose bottleneck adapter is applied (() = all)
+    block_schedule: tuple = ()     # ((block, adapter applied), ...) per block application; () = every block once
 
     @property
     def seq(self) -> int:
@@ -168,10 +170,14 @@ def trainable_names(cfg: VitCfg, sd: dict, train_rule: bool = True) -> list:
             out.append(k)
         elif cfg.adapter == "kron" and (".W_left" in k or ".W_right" in k or (train_rule and k.endswith("phm_rule"))):
             out.append(k)
-        elif cfg.adapter == "houlsby" and ".adapter." in k:
-            out.append(k)
-        elif cfg.adapter == "compacter" and ".compacter." in k:
-            out.append(k)
+        elif cfg.adapter in ("houlsby", "compacter") and (".adapter." in k or ".compacter." in k):
+            # AdapterDrop trains only the adapters that are applied (FS/adapterdrop.py:689: 'blocks.11.adapter' in n)
+            layer = int(k.split(".adapter.")[0].split(".compacter.")[0].split(".")[-1])
+            if cfg.block_schedule:
+                if layer == cfg.depth - 1:          # FS/adapterdrop.py:689: only 'blocks.11.adapter' is trainable
+                    out.append(k)
+            elif not cfg.adapter_layers or layer in cfg.adapter_layers:
+                out.append(k)
     return out
 
 

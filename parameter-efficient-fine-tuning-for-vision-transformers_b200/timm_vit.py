@@ -367,12 +367,40 @@ def sample_drop_path(model, B, L, device):
     return (keep / keep_prob).repeat_interleave(L, dim=2).contiguous()
 
 
+def adapterdrop_reference_schedule(depth=12, last=11):
+    """The block schedule of the COMMITTED FS/adapterdrop.py:582-588 (like Q1-Q8): its loop runs every block
+    TWICE — `x = blk(x, add_adapter=True)` and then `blk(x, True)` for block 11 / `blk(x, False)` for the others — so the
+    tower has 2 x depth block applications with shared weights, the first of each pair with the adapter.  Returns
+    [(block index, adapter applied)] for `VisionTransformer(block_schedule=...)`; `adapter_layers=(11,)` gives the intended
+    AdapterDrop (each block once, adapter in block 11 only)."""
+    out = []
+    for i in range(depth):
+        out += [(i, True), (i, i == last)]
+    return out
+
+
+def expand_schedule(tensors, schedule):
+    """[(reference key, tensor)] -> the same list with every `blocks.{b}.` entry repeated for each application j of block b,
+    renamed `blocks.{j}.` (the engine sees a tower of len(schedule) layers; shared tensors appear several times and autograd
+    sums their gradients)."""
+    out = []
+    for k, t in tensors:
+        if k.startswith("blocks."):
+            b, rest = k[len("blocks."):].split(".", 1)
+            out += [(f"blocks.{j}.{rest}", t) for j, (bb, _) in enumerate(schedule) if bb == int(b)]
+        else:
+            out.append((k, t))
+    return out
+
+
 def run_tower(model, x, dialect, geom, extra_cfg, lowrank, bottleneck, drop=None):
     """Shared forward of both dialects' VisionTransformer: picks the PEFT engine (frozen tower, adapters trainable) or the
     full engine (any tower tensor requires grad: full fine-tuning, bias/LayerNorm tuning, Fastfood)."""
     if not x.is_cuda:
         raise RuntimeError("peft_b200 VisionTransformer runs on CUDA only (no CPU fallback)")
     tensors = tower_tensors(model, model._tower_keys)
+    if getattr(model, "block_schedule", None):
+        tensors = expand_schedule(tensors, model.block_schedule)
     grad = torch.is_grad_enabled()
     trainable = [(k, t) for k, t in tensors if t.requires_grad]
     with_adapter = model.adapter_kind != "none"
@@ -417,8 +445,15 @@ class VisionTransformer(nn.Module):
     def __init__(self, img_size=224, patch_size=16, in_chans=3, num_classes=1000, embed_dim=768, depth=12, num_heads=12,
                  mlp_ratio=4., qkv_bias=False, qk_scale=None, drop_rate=0., attn_drop_rate=0., drop_path_rate=0.,
                  hybrid_backbone=None, norm_layer=None, use_cls_tocken=True, norm_embed=False, pre_norm=True,
-                 res_score=False, init='trunc_norm', adapter="kron", **adapter_kw):
+                 res_score=False, init='trunc_norm', adapter="kron", adapter_layers=None, block_schedule=None, **adapter_kw):
         super().__init__()
+        # AdapterDrop (FS/adapterdrop.py:585-588,689: every block owns an adapter, only block 11 calls and trains it):
+        # indices of the blocks whose bottleneck adapter is applied; None = all blocks
+        self.adapter_layers = None if adapter_layers is None else tuple(sorted(int(i) for i in adapter_layers))
+        # [(block index, adapter applied)] per block APPLICATION; None = every block once (see adapterdrop_reference_schedule)
+        self.block_schedule = None if block_schedule is None else [(int(b), bool(u)) for b, u in block_schedule]
+        if self.block_schedule is not None and self.adapter_layers is not None:
+            raise ValueError("give either adapter_layers or block_schedule")
         if hybrid_backbone is not None or norm_embed or not use_cls_tocken or in_chans != 3:
             raise NotImplementedError("hybrid backbone / norm_embed / no-cls-token / in_chans != 3 are not supported")
         if drop_rate != 0.:
@@ -445,8 +480,8 @@ class VisionTransformer(nn.Module):
         eps = self.norm.eps
         if abs(eps - 1e-6) > 1e-12:
             raise NotImplementedError("timm dialect uses LayerNorm eps 1e-6")
-        self._cfg = dict(img=img_size, patch=patch_size, width=embed_dim, depth=depth, heads=num_heads,
-                         mlp=int(embed_dim * mlp_ratio))
+        self._cfg = dict(img=img_size, patch=patch_size, width=embed_dim, heads=num_heads, mlp=int(embed_dim * mlp_ratio),
+                         depth=depth if self.block_schedule is None else len(self.block_schedule))
         self._engine = None
         self._engine_full = None
         self._frozen_sig = None
@@ -483,14 +518,17 @@ class VisionTransformer(nn.Module):
     def _rank(self):
         return lowrank_rank(self.blocks[0].attn, self.adapter_kind)
 
+    def _applied_blocks(self):
+        return list(self.blocks) if self.block_schedule is None else [self.blocks[b] for b, _ in self.block_schedule]
+
     def lowrank_operands(self):
         """Dn [depth, r', D], UpT [depth, r', 3D] built differentiably from the reference-named parameters."""
-        return lowrank_operands([b.attn for b in self.blocks], self.adapter_kind)
+        return lowrank_operands([b.attn for b in self._applied_blocks()], self.adapter_kind)
 
     def bottleneck_operands(self):
         """(Wd [dep,m,D], bd [dep,m], Wu [dep,D,m], bu [dep,D], ln_g [dep,D], ln_b [dep,D]) built differentiably from the
         reference-named Houlsby / Compacter parameters; None when the model has no bottleneck adapter."""
-        return bottleneck_operands(list(self.blocks), self.adapter_kind)
+        return bottleneck_operands(self._applied_blocks(), self.adapter_kind)
 
     def _bottleneck_cfg(self):
         return bottleneck_cfg(self.blocks[0], self.adapter_kind)
@@ -502,6 +540,10 @@ class VisionTransformer(nn.Module):
 
     def forward_features(self, x):
         extra = dict(rank=self._rank(), **self._bottleneck_cfg())
+        if self.adapter_layers is not None and extra.get("bottleneck"):
+            extra["bottleneck_layers"] = self.adapter_layers
+        if self.block_schedule is not None and extra.get("bottleneck"):
+            extra["bottleneck_layers"] = tuple(j for j, (_, use) in enumerate(self.block_schedule) if use)
         if self.adapter_kind == "kron" and kron_is_dense(self.blocks[0].attn):
             extra["dense_delta"] = True
         drop = sample_drop_path(self, x.shape[0], self.patch_embed.num_patches + 1, x.device)

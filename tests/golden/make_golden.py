@@ -196,6 +196,13 @@ def main():
     cfg = VitCfg(dialect="timm", adapter="houlsby", **small)
     run_model_case("timm_houlsby", adp.VisionTransformer(**vit_kw), cfg, 4, out)
 
+    # AdapterDrop as COMMITTED: FS/adapterdrop.py:582-588 runs every block twice (adapter on the first pass; on the second
+    # pass only in block 11) and trains 'blocks.11.adapter' (:689) -> depth 12, 24 block applications
+    adrop = load_ref(os.path.join(FS, "adapterdrop.py"), "vb.evaluation.adapterdrop", "vb.evaluation")
+    sched = tuple((i, True) if half == 0 else (i, i == 11) for i in range(12) for half in (0, 1))
+    cfg = VitCfg(dialect="timm", adapter="houlsby", block_schedule=sched, img=64, patch=32, width=768, depth=12, heads=12)
+    run_model_case("timm_adapterdrop", adrop.VisionTransformer(**dict(vit_kw, depth=12)), cfg, 3, out)
+
     # ------------------------------------------------------------------ CLIP dialect
     clip_lora = load_ref(os.path.join(FS, "model.py"), "ref_clip_model")
     clip_lora2 = load_ref(os.path.join(FS, "lora_model.py"), "ref_clip_lora_model")

@@ -15,16 +15,20 @@ from oracle import peft_oracle as O
 
 
 def engine_gate_masks(model, cfg, B):
-    """{oracle adapter prefix: 0/1 mask shaped like the oracle's pre-activation} from the engine's saved ReLU outputs."""
+    """{oracle adapter prefix: [0/1 mask per application, shaped like the oracle's pre-activation]} from the engine's saved
+    ReLU outputs (engine layer j = j-th block application; AdapterDrop schedules apply a block more than once)."""
     ws = model._engine.ws[B]
     m, L = cfg.bottleneck, cfg.seq
     masks = {}
-    for i in range(cfg.depth):
-        z = (ws.zext[i][:, :m] > 0).cpu()                       # rows b*L + l
+    sched = list(cfg.block_schedule) if cfg.block_schedule else [(i, (not cfg.adapter_layers) or i in cfg.adapter_layers) for i in range(cfg.depth)]
+    for j, (b, use) in enumerate(sched):
+        if not use:
+            continue                                            # this application does not call the adapter
+        z = (ws.zext[j][:, :m] > 0).cpu()                       # rows b*L + l
         if cfg.dialect == "timm":
-            masks[f"blocks.{i}.adapter."] = z.view(B, L, m)
+            masks.setdefault(f"blocks.{b}.adapter.", []).append(z.view(B, L, m))
         else:
-            masks[f"transformer.resblocks.{i}.adapter."] = z.view(B, L, m).permute(1, 0, 2).contiguous()   # LND
+            masks.setdefault(f"transformer.resblocks.{b}.adapter.", []).append(z.view(B, L, m).permute(1, 0, 2).contiguous())   # LND
     return masks
 
 
@@ -39,17 +43,19 @@ def oracle_with_engine_gates(images, sd_o, cfg, masks, cotangent):
         O.GATE_RECORD = None
     flipped = total = 0
     worst = 0.0
-    for pfx, mask in masks.items():
-        p = pre[pfx]
-        diff = mask != (p > 0)
-        flipped += int(diff.sum())
-        total += diff.numel()
-        if diff.any():
-            worst = max(worst, float(p[diff].abs().max() / p.std()))
+    for pfx, mlist in masks.items():
+        for mask, p in zip(mlist, pre[pfx]):
+            diff = mask != (p > 0)
+            flipped += int(diff.sum())
+            total += diff.numel()
+            if diff.any():
+                worst = max(worst, float(p[diff].abs().max() / p.std()))
     O.GATE_OVERRIDE = masks
+    O.GATE_CALLS = {}
     try:
         feat = O.visual_forward(images, sd_o, cfg)
         (feat * cotangent).sum().backward()
     finally:
         O.GATE_OVERRIDE = {}
+        O.GATE_CALLS = {}
     return feat, dict(flip_frac=flipped / max(1, total), worst_flip_sigma=worst)

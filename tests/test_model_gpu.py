@@ -30,6 +30,10 @@ def build_timm(cfg: VitCfg, sd):
         kw = dict(lora_attn_dim=cfg.lora_r, lora_attn_alpha=cfg.lora_alpha)
     elif cfg.adapter in ("houlsby", "compacter"):
         kw = dict(bottleneck=cfg.bottleneck, compacter_n_down=cfg.compacter_n_down, compacter_n_up=cfg.compacter_n_up)
+    if getattr(cfg, "adapter_layers", ()):
+        kw["adapter_layers"] = cfg.adapter_layers
+    if getattr(cfg, "block_schedule", ()):
+        kw["block_schedule"] = cfg.block_schedule
     m = VisionTransformer(img_size=cfg.img, patch_size=cfg.patch, num_classes=cfg.num_classes, embed_dim=cfg.width,
                           depth=cfg.depth, num_heads=cfg.heads, mlp_ratio=cfg.mlp_ratio, qkv_bias=True,
                           adapter=cfg.adapter, **kw)
@@ -56,7 +60,7 @@ def run_step(model, cfg, batch, names):
     return feat, logits, loss, grads, hg
 
 
-@pytest.mark.parametrize("name", ["timm_kron_n4", "timm_kron_n8_r2", "timm_lora", "timm_houlsby"])
+@pytest.mark.parametrize("name", ["timm_kron_n4", "timm_kron_n8_r2", "timm_lora", "timm_houlsby", "timm_adapterdrop"])
 def test_features_match_reference_golden(golden, name):
     """Forward features against the committed outputs of the unmodified reference modules."""
     c = golden[name]
@@ -85,6 +89,14 @@ BACKBONE_CASES = {
     # the COMMITTED hyper-parameters (phm_dim = 768 = D, K = P = 1): peft_phm_fold path, phm_rule frozen as in few_shot
     "kron_n768_committed": (VitCfg(dialect="timm", adapter="kron", phm_dim=768, img=64, patch=32, depth=1), 2),
     "kron_n4_L50_d12": (VitCfg(dialect="timm", adapter="kron", phm_dim=4, img=224, patch=32, depth=12), 4),
+    # AdapterDrop (FS/adapterdrop.py): the Houlsby adapter is applied and trained in the listed blocks only
+    "adapterdrop_last": (VitCfg(dialect="timm", adapter="houlsby", adapter_layers=(3,), img=64, patch=32, depth=4), 6),
+    "adapterdrop_two": (VitCfg(dialect="timm", adapter="houlsby", adapter_layers=(1, 2), img=224, patch=32, depth=3), 4),
+    "compacter_drop": (VitCfg(dialect="timm", adapter="compacter", adapter_layers=(1,), img=64, patch=32, depth=2), 5),
+    # the COMMITTED FS/adapterdrop.py loop: every block applied twice (adapter on the first pass, on the second only in the last
+    # block), only the last block's adapter trainable (pinned by the golden case timm_adapterdrop at depth 12)
+    "adapterdrop_committed": (VitCfg(dialect="timm", adapter="houlsby", img=64, patch=32, depth=3,
+                                     block_schedule=((0, True), (0, False), (1, True), (1, False), (2, True), (2, True))), 6),
 }
 
 
