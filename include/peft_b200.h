@@ -233,6 +233,11 @@ int peft_tn_reduce_f32(const float* x, long long ldx, int I, const float* y, lon
 /* lse[B*H*L] = rowmax + ln(rowsum) of the scaled scores (private to the fp32 kernels) */
 int peft_attention_fwd_f32(const float* qkv, long long ldqkv, float* o, long long ldo, float* lse, int B, int H, int L,
                            float scale, void* stream);
+/* same with an optional causal mask (causal != 0: query l sees keys j <= l) — the text tower of CLIP.encode_text, which the
+ * trainers run once per task to initialise the classifier head from prompt embeddings (FS/model.py:1303-1327,
+ * FS/kadaptation_clip.py:128-138); forward only. */
+int peft_attention_fwd_f32_ex(const float* qkv, long long ldqkv, float* o, long long ldo, float* lse, int B, int H, int L,
+                              float scale, int causal, void* stream);
 int peft_attention_bwd_f32(const float* qkv, long long ldqkv, const float* o, long long ldo, const float* d_o, long long lddo,
                            const float* lse, float* delta, float* dqkv, long long lddqkv, int B, int H, int L, float scale,
                            void* stream);

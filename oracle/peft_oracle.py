@@ -274,6 +274,43 @@ def visual_forward(images, sd, cfg: VitCfg):
 
 
 # --------------------------------------------------------------------------------------------------------------------
+# CLIP text tower  (FS/model.py:1303-1327) and the zero-shot head initialisation (FS/feature.py:351-512)
+# --------------------------------------------------------------------------------------------------------------------
+def clip_encode_text(text, sd, heads=8):
+    """FS/model.py:1311-1327 — token + positional embedding, causal transformer (additive -inf upper-triangular mask,
+    build_attention_mask :1303-1309; blocks as in clip_block without adapter), ln_final, EOT row @ text_projection."""
+    N, L = text.shape
+    W = sd["ln_final.weight"].shape[0]
+    hd = W // heads
+    x = sd["token_embedding.weight"][text] + sd["positional_embedding"]
+    mask = torch.full((L, L), float("-inf")).triu_(1)
+    layers = len({k.split(".")[2] for k in sd if k.startswith("transformer.resblocks.")})
+    for i in range(layers):
+        p = f"transformer.resblocks.{i}."
+        y = F.layer_norm(x, (W,), sd[p + "ln_1.weight"], sd[p + "ln_1.bias"], 1e-5)
+        q, k, v = F.linear(y, sd[p + "attn.in_proj_weight"], sd[p + "attn.in_proj_bias"]).chunk(3, dim=-1)
+        q, k, v = [t.reshape(N, L, heads, hd).transpose(1, 2) for t in (q, k, v)]
+        a = torch.softmax(q @ k.transpose(-1, -2) / math.sqrt(hd) + mask, dim=-1) @ v
+        x = x + F.linear(a.transpose(1, 2).reshape(N, L, W), sd[p + "attn.out_proj.weight"], sd[p + "attn.out_proj.bias"])
+        y = F.layer_norm(x, (W,), sd[p + "ln_2.weight"], sd[p + "ln_2.bias"], 1e-5)
+        x = x + F.linear(quick_gelu(F.linear(y, sd[p + "mlp.c_fc.weight"], sd[p + "mlp.c_fc.bias"])), sd[p + "mlp.c_proj.weight"], sd[p + "mlp.c_proj.bias"])
+    x = F.layer_norm(x, (W,), sd["ln_final.weight"], sd["ln_final.bias"], 1e-5)
+    return x[torch.arange(N), text.argmax(dim=-1)] @ sd["text_projection"]
+
+
+def zeroshot_weights(class_token_batches, sd, heads=8):
+    """FS/feature.py:497-503 — per class: normalise the prompt embeddings, mean, normalise; stacked [classes, E] (the
+    reference stacks along dim 1 and transposes at FS/kadaptation_clip.py:137)."""
+    rows = []
+    for toks in class_token_batches:
+        e = clip_encode_text(toks, sd, heads)
+        e = e / e.norm(dim=-1, keepdim=True)
+        m = e.mean(dim=0)
+        rows.append(m / m.norm())
+    return torch.stack(rows, dim=0)
+
+
+# --------------------------------------------------------------------------------------------------------------------
 # classifier head, loss, one training step
 # --------------------------------------------------------------------------------------------------------------------
 def classifier_logits(feature, head, training=True, bn_eps=1e-5):

@@ -52,6 +52,7 @@ SIGNATURES = {
     "peft_gemm_f32": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
     "peft_tn_reduce_f32": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp],
     "peft_attention_fwd_f32": [_vp, _c_ll, _vp, _c_ll, _vp, C.c_int, C.c_int, C.c_int, C.c_float, _vp],
+    "peft_attention_fwd_f32_ex": [_vp, _c_ll, _vp, _c_ll, _vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, _vp],
     "peft_attention_bwd_f32": [_vp, _c_ll, _vp, _c_ll, _vp, _c_ll, _vp, _vp, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, _vp],
     "peft_clip_delta_f32": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, _vp],
     "peft_im2col_patches_f32": [_vp, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp],

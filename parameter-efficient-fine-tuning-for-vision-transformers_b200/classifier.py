@@ -26,6 +26,19 @@ class Classifier(nn.Module):
             self.channel_bn = nn.BatchNorm1d(feat_dim, affine=False)
         self.layers = nn.Sequential(nn.Linear(feat_dim, num_classes))
 
+    @torch.no_grad()
+    def init_head_with_text_encoder(self, zeroshot_weights, logit_scale=None):
+        """TRAIN.INIT_HEAD_WITH_TEXT_ENCODER (every *_clip.sh script sets it; FS/kadaptation_clip.py:128-138,154-155): the
+        Linear head starts from the zero-shot classifier — `zeroshot_weights` [classes, E] from
+        `CLIP.zeroshot_head_weights(...)`, bias 0, optionally scaled by exp(logit_scale) (INIT_HEAD_WITH_LOGIT_SCALE)."""
+        lin = self.layers[0]
+        if tuple(zeroshot_weights.shape) != tuple(lin.weight.shape):
+            raise ValueError(f"zeroshot_weights must be {tuple(lin.weight.shape)}, got {tuple(zeroshot_weights.shape)}")
+        lin.weight.copy_(zeroshot_weights.to(lin.weight.dtype))
+        lin.bias.fill_(0.0)
+        if logit_scale is not None:
+            lin.weight.mul_(torch.as_tensor(logit_scale, dtype=lin.weight.dtype, device=lin.weight.device).exp())
+
     def forward(self, img):
         feature = self.backbone(img).to(img.dtype)
         return self.layers(self.channel_bn(feature))

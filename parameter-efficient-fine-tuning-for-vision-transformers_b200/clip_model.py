@@ -79,7 +79,7 @@ class Transformer(nn.Module):
 
     def __init__(self, width, layers, heads, attn_mask=None, **adapter_kw):
         super().__init__()
-        self.width, self.layers = width, layers
+        self.width, self.layers, self.heads = width, layers, heads
         self.resblocks = nn.Sequential(*[ResidualAttentionBlock(width, heads, attn_mask, **adapter_kw) for _ in range(layers)])
 
     forward = _no_eager
@@ -131,7 +131,10 @@ class VisionTransformer(nn.Module):
 
 
 class CLIP(nn.Module):
-    """FS/model.py:1222-1375 — visual tower only; the text tower is out of scope for the hot path."""
+    """FS/model.py:1222-1375.  The visual tower is the hot path (CUDA engine, forward + backward); the text tower
+    (`encode_text`, :1311-1327) runs once per task, without gradients, to initialise the classifier head from prompt
+    embeddings — it goes through the fp32 C-ABI kernels (LayerNorm, SGEMM with fused bias / QuickGELU / residual epilogues,
+    attention with the causal mask of build_attention_mask :1303-1309)."""
 
     def __init__(self, embed_dim, image_resolution, vision_layers, vision_width, vision_patch_size, context_length=77,
                  vocab_size=49408, transformer_width=512, transformer_heads=8, transformer_layers=12, adapter="none",
@@ -143,20 +146,31 @@ class CLIP(nn.Module):
         self.visual = VisionTransformer(input_resolution=image_resolution, patch_size=vision_patch_size, width=vision_width,
                                         layers=vision_layers, heads=vision_width // 64, output_dim=embed_dim,
                                         adapter=adapter, **adapter_kw)
+        # text tower parameters, reference names (FS/model.py:1262-1274); no adapter (the LoRA factors model.py also gives
+        # the text blocks start at zero and are never trained: the tower is only used under no_grad)
+        self.transformer = Transformer(transformer_width, transformer_layers, transformer_heads, adapter="none")
+        self.vocab_size = vocab_size
+        self.token_embedding = nn.Embedding(vocab_size, transformer_width)
+        self.positional_embedding = nn.Parameter(torch.empty(context_length, transformer_width))
+        self.ln_final = LayerNorm(transformer_width)
+        self.text_projection = nn.Parameter(torch.empty(transformer_width, embed_dim))
         self.logit_scale = nn.Parameter(torch.ones([]) * 2.6592)
         self.initialize_parameters()
 
     def initialize_parameters(self):
-        """FS/model.py:1278-1305 (visual part)."""
-        t = self.visual.transformer
-        proj_std = (t.width ** -0.5) * ((2 * t.layers) ** -0.5)
-        attn_std = t.width ** -0.5
-        fc_std = (2 * t.width) ** -0.5
-        for block in t.resblocks:
-            nn.init.normal_(block.attn.in_proj_weight, std=attn_std)
-            nn.init.normal_(block.attn.out_proj.weight, std=proj_std)
-            nn.init.normal_(block.mlp.c_fc.weight, std=fc_std)
-            nn.init.normal_(block.mlp.c_proj.weight, std=proj_std)
+        """FS/model.py:1278-1305."""
+        nn.init.normal_(self.token_embedding.weight, std=0.02)
+        nn.init.normal_(self.positional_embedding, std=0.01)
+        for t in (self.visual.transformer, self.transformer):
+            proj_std = (t.width ** -0.5) * ((2 * t.layers) ** -0.5)
+            attn_std = t.width ** -0.5
+            fc_std = (2 * t.width) ** -0.5
+            for block in t.resblocks:
+                nn.init.normal_(block.attn.in_proj_weight, std=attn_std)
+                nn.init.normal_(block.attn.out_proj.weight, std=proj_std)
+                nn.init.normal_(block.mlp.c_fc.weight, std=fc_std)
+                nn.init.normal_(block.mlp.c_proj.weight, std=proj_std)
+        nn.init.normal_(self.text_projection, std=self.transformer.width ** -0.5)
 
     @property
     def dtype(self):
@@ -165,8 +179,57 @@ class CLIP(nn.Module):
     def encode_image(self, image):
         return self.visual(image.type(self.dtype))
 
+    @torch.no_grad()
     def encode_text(self, text):
-        raise NotImplementedError("the CLIP text tower is outside the hot path built here (SURVEY §8f rank 3)")
+        """FS/model.py:1311-1327: token + positional embedding -> causal transformer -> ln_final -> the EOT row (argmax of the
+        token ids) @ text_projection.  text: CUDA int64 [N, context_length].  Forward only (the reference freezes the text
+        tower, FS/kadaptation_clip.py:98-104, and calls this once per task under no_grad)."""
+        from . import _lib, ops
+        if not text.is_cuda:
+            raise RuntimeError("peft_b200 CLIP.encode_text runs on CUDA only (no CPU fallback)")
+        N, L = text.shape
+        if L != self.context_length:
+            raise ValueError(f"text must be [N, {self.context_length}]")
+        t = self.transformer
+        W, H = t.width, t.heads
+        if W // H != 64 or W % 128:
+            raise NotImplementedError("text tower kernels need head_dim 64 and width % 128 == 0")
+        dev, f32 = text.device, torch.float32
+        e = lambda *sh: torch.empty(*sh, device=dev, dtype=f32)
+        f = lambda p: p.detach().to(dev, f32).contiguous()
+        x = (self.token_embedding.weight.detach().to(dev, f32)[text] + f(self.positional_embedding)).reshape(N * L, W).contiguous()
+        xn, qkv, o, x1, lse = e(N * L, W), e(N * L, 3 * W), e(N * L, W), e(N * L, W), e(N * H * L)
+        h, act = e(N * L, 4 * W), e(N * L, 4 * W)
+        stream = torch.cuda.current_stream().cuda_stream
+        for blk in t.resblocks:
+            ops.layernorm_fwd(x, f(blk.ln_1.weight), f(blk.ln_1.bias), xn, None, None, 1e-5)
+            ops.gemm(xn, f(blk.attn.in_proj_weight), qkv, bias=f(blk.attn.in_proj_bias))
+            _lib.check(_lib.load().peft_attention_fwd_f32_ex(qkv.data_ptr(), qkv.stride(0), o.data_ptr(), o.stride(0), lse.data_ptr(),
+                                                             N, H, L, 64 ** -0.5, 1, stream), "peft_attention_fwd_f32_ex")
+            ops.gemm(o, f(blk.attn.out_proj.weight), x1, bias=f(blk.attn.out_proj.bias), epilogue=ops.EPI_RESID_F32, aux=x)
+            ops.layernorm_fwd(x1, f(blk.ln_2.weight), f(blk.ln_2.bias), xn, None, None, 1e-5)
+            ops.gemm(xn, f(blk.mlp.c_fc.weight), h, bias=f(blk.mlp.c_fc.bias), epilogue=ops.EPI_QUICKGELU, out2=act)
+            ops.gemm(act, f(blk.mlp.c_proj.weight), x, bias=f(blk.mlp.c_proj.bias), epilogue=ops.EPI_RESID_F32, aux=x1)
+        eot = x[torch.arange(N, device=dev) * L + text.argmax(dim=-1)].contiguous()     # LayerNorm is per row: gather first
+        y = e(N, W)
+        ops.layernorm_fwd(eot, f(self.ln_final.weight), f(self.ln_final.bias), y, None, None, 1e-5)
+        out = e(N, self.text_projection.shape[1])
+        ops.gemm(y, f(self.text_projection).t().contiguous(), out, epilogue=ops.EPI_STORE_F32)
+        return out
+
+    @torch.no_grad()
+    def zeroshot_head_weights(self, class_token_batches):
+        """The classifier initialisation of FS/feature.py:351-512 (extract_text_features) after tokenisation: per class, the
+        prompt embeddings are L2-normalised, averaged and normalised again; returns [classes, embed_dim] — what
+        FS/kadaptation_clip.py:136-138 stores (transposed there) into `layers[0].weight`.  class_token_batches: iterable of CUDA
+        int64 [n_prompts, context_length] tensors, one per class (tokenising is CPU text processing outside this library)."""
+        rows = []
+        for toks in class_token_batches:
+            emb = self.encode_text(toks)
+            emb = emb / emb.norm(dim=-1, keepdim=True)
+            m = emb.mean(dim=0)
+            rows.append(m / m.norm())
+        return torch.stack(rows, dim=0)
 
     def forward(self, image, text=None):
         if text is not None:
@@ -184,7 +247,13 @@ def _build(state_dict: dict, adapter: str, **adapter_kw):
     grid_size = round((state_dict["visual.positional_embedding"].shape[0] - 1) ** 0.5)
     image_resolution = vision_patch_size * grid_size
     embed_dim = state_dict["visual.proj"].shape[1]
-    model = CLIP(embed_dim, image_resolution, vision_layers, vision_width, vision_patch_size, adapter=adapter, **adapter_kw)
+    text_kw = {}
+    if "text_projection" in state_dict:           # text geometry, FS/model.py:1395-1401
+        tw = state_dict["ln_final.weight"].shape[0]
+        text_kw = dict(context_length=state_dict["positional_embedding"].shape[0], vocab_size=state_dict["token_embedding.weight"].shape[0],
+                       transformer_width=tw, transformer_heads=tw // 64,
+                       transformer_layers=len({k.split(".")[2] for k in state_dict if k.startswith("transformer.resblocks.")}))
+    model = CLIP(embed_dim, image_resolution, vision_layers, vision_width, vision_patch_size, adapter=adapter, **text_kw, **adapter_kw)
     sd = {k: v for k, v in state_dict.items() if k not in ("input_resolution", "context_length", "vocab_size")}
     model.load_state_dict(sd, strict=False)
     return model.eval()

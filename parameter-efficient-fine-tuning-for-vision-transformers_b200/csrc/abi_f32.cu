@@ -52,9 +52,14 @@ extern "C" int peft_tn_reduce_f32(const float* x, long long ldx, int I, const fl
 
 extern "C" int peft_attention_fwd_f32(const float* qkv, long long ldqkv, float* o, long long ldo, float* lse, int B, int H,
                                       int L, float scale, void* stream) {
+  return peft_attention_fwd_f32_ex(qkv, ldqkv, o, ldo, lse, B, H, L, scale, 0, stream);
+}
+
+extern "C" int peft_attention_fwd_f32_ex(const float* qkv, long long ldqkv, float* o, long long ldo, float* lse, int B, int H,
+                                         int L, float scale, int causal, void* stream) {
   PEFT_REQUIRE(B > 0 && H > 0 && L > 0 && qkv && o && lse, "peft_attention_fwd_f32: bad shape B=%d H=%d L=%d", B, H, L);
   PEFT_REQUIRE(al16(qkv) && al16(o) && ldqkv % 4 == 0 && ldo % 4 == 0 && ldqkv >= 3ll * H * 64, "peft_attention_fwd_f32: 16-byte aligned rows required");
-  f32::attn_fwd_kernel<<<dim3((L + 127) / 128, B * H), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(qkv, ldqkv, o, ldo, lse, B, H, L, scale);
+  f32::attn_fwd_kernel<<<dim3((L + 127) / 128, B * H), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(qkv, ldqkv, o, ldo, lse, B, H, L, scale, causal);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

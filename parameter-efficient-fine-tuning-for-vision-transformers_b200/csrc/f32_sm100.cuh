@@ -149,7 +149,10 @@ __device__ __forceinline__ void store64(float* p, const float (&r)[64], float mu
 }
 
 __global__ void __launch_bounds__(128) attn_fwd_kernel(const float* __restrict__ qkv, long long ld, float* __restrict__ o,
-                                                      long long ldo, float* __restrict__ lse, int B, int H, int L, float scale) {
+                                                      long long ldo, float* __restrict__ lse, int B, int H, int L, float scale,
+                                                      int causal = 0) {
+  // causal != 0: query l attends to keys j <= l only (the additive -inf upper-triangular mask of the CLIP text tower,
+  // FS/model.py:1303-1309 build_attention_mask)
   __shared__ __align__(16) float Ks[kAttnChunk][64];
   __shared__ __align__(16) float Vs[kAttnChunk][64];
   const int bh = blockIdx.y, b = bh / H, h = bh % H, D = H * 64;
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const float* __restrict__
     float cmax = -INFINITY;
 #pragma unroll
     for (int jj = 0; jj < kAttnChunk; ++jj) {
-      s[jj] = jj < nk ? dot64(q, Ks[jj]) : -INFINITY;
+      s[jj] = (jj < nk && (!causal || j0 + jj <= l)) ? dot64(q, Ks[jj]) : -INFINITY;
       cmax = fmaxf(cmax, s[jj]);
     }
     const float mn = fmaxf(m, cmax);

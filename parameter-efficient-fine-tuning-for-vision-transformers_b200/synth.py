@@ -198,3 +198,41 @@ def make_batch(cfg: VitCfg, batch: int, seed_img: int = 1234, seed_lbl: int = 12
     images = torch.randn((batch, 3, cfg.img, cfg.img), generator=gi, dtype=torch.float32)
     labels = torch.randint(0, cfg.num_classes, (batch,), generator=gl)
     return images, labels
+
+
+def make_text_state_dict(width=512, layers=2, vocab=1000, context=77, embed_dim=512, seed=21) -> dict:
+    """Reference-named text-tower tensors of CLIP (FS/model.py:1262-1274) with the standard deviations of its
+    initialize_parameters (:1278-1305); LayerNorm gains / biases and linear biases are perturbed so that parity tests see them."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {"token_embedding.weight": _n(g, (vocab, width), 0.02), "positional_embedding": _n(g, (context, width), 0.01)}
+    proj_std = (width ** -0.5) * ((2 * layers) ** -0.5)
+    for i in range(layers):
+        b = f"transformer.resblocks.{i}."
+        sd[b + "ln_1.weight"] = 1.0 + _n(g, (width,), 0.1)
+        sd[b + "ln_1.bias"] = _n(g, (width,), 0.05)
+        sd[b + "attn.in_proj_weight"] = _n(g, (3 * width, width), width ** -0.5)
+        sd[b + "attn.in_proj_bias"] = _n(g, (3 * width,), 0.02)
+        sd[b + "attn.out_proj.weight"] = _n(g, (width, width), proj_std)
+        sd[b + "attn.out_proj.bias"] = _n(g, (width,), 0.02)
+        sd[b + "ln_2.weight"] = 1.0 + _n(g, (width,), 0.1)
+        sd[b + "ln_2.bias"] = _n(g, (width,), 0.05)
+        sd[b + "mlp.c_fc.weight"] = _n(g, (4 * width, width), (2 * width) ** -0.5)
+        sd[b + "mlp.c_fc.bias"] = _n(g, (4 * width,), 0.02)
+        sd[b + "mlp.c_proj.weight"] = _n(g, (width, 4 * width), proj_std)
+        sd[b + "mlp.c_proj.bias"] = _n(g, (width,), 0.02)
+    sd["ln_final.weight"] = 1.0 + _n(g, (width,), 0.1)
+    sd["ln_final.bias"] = _n(g, (width,), 0.05)
+    sd["text_projection"] = _n(g, (width, embed_dim), width ** -0.5)
+    return sd
+
+
+def make_tokens(n, vocab=1000, context=77, seed=31):
+    """[n, context] int64 prompts: random ids, one EOT (= vocab - 1, the largest id, which encode_text locates by argmax) at a
+    random position >= 3, zero padding after it — the shape of SimpleTokenizer output."""
+    g = torch.Generator().manual_seed(seed)
+    toks = torch.randint(1, vocab - 1, (n, context), generator=g)
+    ends = torch.randint(3, context, (n,), generator=g)
+    for i in range(n):
+        toks[i, ends[i]] = vocab - 1
+        toks[i, ends[i] + 1:] = 0
+    return toks

@@ -218,6 +218,26 @@ def main():
     cfg = VitCfg(dialect="clip", adapter="compacter", **small)
     run_model_case("clip_compacter", clip_cmp.VisionTransformer(**clip_kw), cfg, 4, out)
 
+    # ------------------------------------------------------------------ CLIP text tower (FS/model.py CLIP.encode_text)
+    tcfg = dict(width=512, layers=2, vocab=1000, context=77, embed_dim=512)
+    ref_clip = clip_lora.CLIP(embed_dim=512, image_resolution=64, vision_layers=1, vision_width=768, vision_patch_size=32,
+                              context_length=77, vocab_size=1000, transformer_width=512, transformer_heads=8, transformer_layers=2)
+    tsd = synth.make_text_state_dict(**tcfg)
+    missing, unexpected = ref_clip.load_state_dict(tsd, strict=False)
+    assert not unexpected, unexpected
+    ref_clip.eval()
+    toks = synth.make_tokens(12, vocab=1000, context=77)
+    with torch.no_grad():
+        feats = ref_clip.encode_text(toks)
+        zs = []
+        for c in range(3):                                 # FS/feature.py:497-503 on 3 classes x 4 prompts
+            e = ref_clip.encode_text(toks[4 * c:4 * c + 4])
+            e = e / e.norm(dim=-1, keepdim=True)
+            m = e.mean(dim=0)
+            zs.append(m / m.norm())
+    out["clip_text"] = {"cfg": tcfg, "n_tokens": 12, "features": feats.clone(), "zeroshot": torch.stack(zs, dim=1).clone()}
+    print(f"[golden] clip_text: |feat|={float(feats.norm()):.4f}")
+
     # ------------------------------------------------------------------ Fastfood
     ff = load_ref(os.path.join(FL, "intrinsic/fastfood.py"), "ref_fastfood")
     g = torch.Generator().manual_seed(5)
