@@ -216,6 +216,17 @@ int peft_allreduce_sgd(const void* const* peer_grads, void* const* peer_pads, in
                        float* momentum, long long n, const float* lr, float mu, float weight_decay, int zero_grad,
                        int pad_base, int pad_slots, void* stream);
 
+/* CLIP input pipeline on a decoded uint8 RGB image [H, W, 3] in device memory: Resize(n, BICUBIC) -> CenterCrop(n) -> ToTensor ->
+ * Normalize(mean, std), bit-identical to the reference's torchvision-on-PIL transform.
+ * replaces: `_transform(n_px)` of few_shot/vision_benchmark/evaluation/clip_load.py:80-87 (Pillow's two-pass 8-bit resampler:
+ * 22-bit fixed-point coefficients, horizontal pass rounded to uint8, then vertical).  hb / vb: int32 [out, 2] (first input index,
+ * count) and hk / vk: int32 [out, ksize] fixed-point coefficients of the horizontal / vertical axis (built by the host,
+ * peft_b200/preprocess.py); top / left: crop origin in the resized image; rows [r0, r1) of the input are the ones the cropped
+ * output needs; tmp: uint8 [(r1 - r0), n, 3] scratch; out: fp32 [3, n, n]. */
+int peft_preprocess_clip(const uint8_t* img, int H, int W, const int* hb, const int* hk, int hksize, const int* vb, const int* vk,
+                         int vksize, int top, int left, int n, int r0, int r1, const float* mean, const float* stdv, uint8_t* tmp,
+                         float* out, void* stream);
+
 /* ---- fp32 verification mode ("within 1e-5 relative for fp32 mode", BASELINE.json north_star) -------------------------
  * Plain CUDA-core fp32 counterparts of the entry points above: same operand layouts (row pitches in elements), same
  * epilogue semantics with every bf16 tensor replaced by fp32, IEEE expf/erff/tanhf.  The Python engine selects them

@@ -48,6 +48,8 @@ SIGNATURES = {
     "peft_fastfood_fwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "peft_fastfood_bwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "peft_allreduce_sgd": [_vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _c_ll, _vp, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, _vp],
+    "peft_preprocess_clip": [_vp, C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                             _vp, _vp, _vp, _vp, _vp],
     # fp32 verification mode
     "peft_gemm_f32": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
     "peft_tn_reduce_f32": [_vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp, _c_ll, C.c_int, _vp],

@@ -4,6 +4,7 @@
 #include "clip_delta_sm100.cuh"
 #include "fastfood_sm100.cuh"
 #include "allreduce_sgd_sm100.cuh"
+#include "preprocess_sm100.cuh"
 
 using namespace peft;
 
@@ -190,6 +191,25 @@ extern "C" int peft_allreduce_sgd(const void* const* peer_grads, void* const* pe
   a.grad = grad; a.param = param; a.momentum = momentum; a.lr = lr; a.n = n; a.rank = rank; a.world = world;
   a.mu = mu; a.weight_decay = weight_decay; a.zero_grad = zero_grad; a.pad_base = pad_base;
   allreduce_sgd_kernel<<<(unsigned)blocks, kArThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int peft_preprocess_clip(const uint8_t* img, int H, int W, const int* hb, const int* hk, int hksize, const int* vb,
+                                    const int* vk, int vksize, int top, int left, int n, int r0, int r1, const float* mean,
+                                    const float* stdv, uint8_t* tmp, float* out, void* stream) {
+  PEFT_REQUIRE(img && hb && hk && vb && vk && mean && stdv && tmp && out, "peft_preprocess_clip: null operand");
+  PEFT_REQUIRE(H > 0 && W > 0 && n > 0 && hksize > 0 && vksize > 0 && top >= 0 && left >= 0 && r0 >= 0 && r1 > r0 && r1 <= H,
+               "peft_preprocess_clip: bad geometry H=%d W=%d n=%d rows [%d, %d)", H, W, n, r0, r1);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long t1 = (long long)(r1 - r0) * n * 3, t2 = (long long)n * n * 3;
+  const int cap = sm_count() * 8;
+  long long b1 = (t1 + 255) / 256, b2 = (t2 + 255) / 256;
+  if (b1 > cap) b1 = cap;
+  if (b2 > cap) b2 = cap;
+  pp_horizontal_kernel<<<(unsigned)b1, 256, 0, s>>>(img, W, hb, hk, hksize, left, n, r0, r1, tmp);
+  PEFT_LAUNCH_CHECK();
+  pp_vertical_kernel<<<(unsigned)b2, 256, 0, s>>>(tmp, vb, vk, vksize, top, n, r0, mean, stdv, out);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

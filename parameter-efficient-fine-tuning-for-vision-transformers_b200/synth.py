@@ -236,3 +236,12 @@ def make_tokens(n, vocab=1000, context=77, seed=31):
         toks[i, ends[i]] = vocab - 1
         toks[i, ends[i] + 1:] = 0
     return toks
+
+
+def make_image_u8(h, w, seed=41):
+    """Synthetic decoded RGB image uint8 [h, w, 3]: smooth random field + noise (so that resampling sees real gradients)."""
+    g = torch.Generator().manual_seed(seed + 1000 * h + w)
+    low = torch.rand((1, 3, max(2, h // 16), max(2, w // 16)), generator=g)
+    img = torch.nn.functional.interpolate(low, size=(h, w), mode="bilinear", align_corners=False)[0]
+    img = (img + 0.25 * torch.rand((3, h, w), generator=g)).clamp(0, 1.2) / 1.2
+    return (img * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous()

@@ -44,6 +44,8 @@ from oracle.synth import VitCfg  # noqa: E402
 
 def _install_shims():
     import transformers.activations  # noqa: F401  (must be imported before the timm stub exists)
+    import torchvision.transforms  # noqa: F401  (inspect.getmodule walks sys.modules: import before the stub packages exist)
+    import PIL.Image  # noqa: F401
     orig = torch._C._add_docstr
 
     def tolerant(obj, doc):
@@ -237,6 +239,21 @@ def main():
             zs.append(m / m.norm())
     out["clip_text"] = {"cfg": tcfg, "n_tokens": 12, "features": feats.clone(), "zeroshot": torch.stack(zs, dim=1).clone()}
     print(f"[golden] clip_text: |feat|={float(feats.norm()):.4f}")
+
+    # ------------------------------------------------------------------ input pipeline: clip_load._transform (FS/clip_load.py:80-87)
+    # built here from the same torchvision calls on a PIL image (importing clip_load.py itself pulls in the whole trainer)
+    from PIL import Image
+    from torchvision.transforms import CenterCrop, Compose, Normalize, Resize, ToTensor
+    from torchvision.transforms import InterpolationMode
+
+    def ref_transform(n_px):
+        return Compose([Resize(n_px, interpolation=InterpolationMode.BICUBIC), CenterCrop(n_px), lambda im: im.convert("RGB"), ToTensor(),
+                        Normalize((0.48145466, 0.4578275, 0.40821073), (0.26862954, 0.26130258, 0.27577711))])
+
+    for (h, w, n_px) in ((300, 400, 96), (500, 375, 128), (150, 200, 224), (97, 97, 64), (640, 481, 96)):
+        img = synth.make_image_u8(h, w)
+        out[f"preprocess_{h}x{w}_{n_px}"] = {"h": h, "w": w, "n_px": n_px, "out": ref_transform(n_px)(Image.fromarray(img.numpy())).clone()}
+    print("[golden] preprocess: 5 cases through torchvision-on-PIL")
 
     # ------------------------------------------------------------------ Fastfood
     ff = load_ref(os.path.join(FL, "intrinsic/fastfood.py"), "ref_fastfood")
