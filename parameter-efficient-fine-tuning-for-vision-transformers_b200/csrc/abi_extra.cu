@@ -14,11 +14,11 @@ inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) =
 // persistent grid: occupancy x SMs CTAs, launched cooperatively so that every CTA is resident (the in-kernel waits rely on it)
 template <typename K>
 int ff_launch(K kernel, FfArgs a, cudaStream_t s) {
-  static int dev_smem = 0;
+  static DeviceMax dev_smem;
   const int smem = ff_smem_bytes(a.wn);
-  if (dev_smem < smem) {   // raise the opt-in limit once
+  if (dev_smem.get() < smem) {   // raise the opt-in limit once per device
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ff_smem_bytes(kFfMaxWn)));
-    dev_smem = ff_smem_bytes(kFfMaxWn);
+    dev_smem.set(ff_smem_bytes(kFfMaxWn));
   }
   int occ = 0;
   PEFT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kFfThreads, smem));
@@ -161,10 +161,10 @@ extern "C" int peft_fastfood_bwd(const float* dtheta, int d, int wn, const peft_
   FfArgs a{};
   a.tensors = tensors; a.items = reinterpret_cast<const int2*>(items); a.pi_lo = pi_lo; a.gg = gg; a.u = wu; a.scratch = scratch;
   a.dtheta = dtheta; a.counters = counters; a.wn = wn; a.T = T; a.n_items = n_items;
-  static bool bwd_attr = false;
-  if (!bwd_attr) {
+  static DeviceOnce bwd_attr;
+  if (bwd_attr.needs()) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(ff_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (kFfTile + kFfMaxWn) * 4));
-    bwd_attr = true;
+    bwd_attr.done();
   }
   ff_bwd_kernel<<<n_items, kFfThreads, (kFfTile + wn) * 4, s>>>(a);
   PEFT_LAUNCH_CHECK();

@@ -10,10 +10,10 @@ template <int BN, int EPI>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
   auto kern = gemm_bf16_tcgen05_kernel<BN, EPI>;
-  static bool configured = false;  // per (BN,EPI) instantiation
-  if (!configured) {
+  static DeviceOnce configured;  // per (BN,EPI) instantiation
+  if (configured.needs()) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured = true;
+    configured.done();
   }
   const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
   const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
@@ -118,10 +118,10 @@ template <int EPI, bool TN = false>
 static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& to2,
                         const CUtensorMap& tx, const GemmParams& p, cudaStream_t stream) {
   auto kern = gemm2_bf16_tcgen05_kernel<EPI, TN>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.needs()) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2SmemBytes));
-    configured = true;
+    configured.done();
   }
   const int num_tiles = ((p.M + 2 * kBM - 1) / (2 * kBM)) * ((p.N + kG2BN - 1) / kG2BN) * (p.ksplit > 1 ? p.ksplit : 1);
   const int max_clusters = sm_count() / 2;

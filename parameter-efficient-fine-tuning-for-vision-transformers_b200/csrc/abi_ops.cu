@@ -193,10 +193,10 @@ static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long
   rc = make_tmap_bf16_3d(&to, o, B, L, 1ull * H * 64, ldo, 128);
   if (rc) return rc;
   auto kern = attn2_fwd_kernel<NK>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.needs()) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    configured = true;
+    configured.done();
   }
   Attn2Params p{};
   p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
@@ -223,10 +223,10 @@ extern "C" int peft_attention_fwd(const void* qkv, long long ldqkv, void* o, lon
   }
   const int Lp = attn_lp(L);
   const int smem = (64 + 2 * Lp) * 128;
-  static int configured = 0;
-  if (configured < smem) {
+  static DeviceMax configured;
+  if (configured.get() < smem) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = smem;
+    configured.set(smem);
   }
   dim3 grid((L + 63) / 64, B * H);
   attn_fwd_kernel<<<grid, kAttnThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(p, Lp);
@@ -250,11 +250,11 @@ static int launch_attn2_bwd(const void* qkv, long long ldqkv, const void* o, lon
   if ((rc = make_tmap_bf16_3d(&tout, dqkv, B, L, 3 * D, lddqkv, 128))) return rc;
   auto kdq = attn2_bwd_dq_kernel<NKC, NCH>;
   auto kdkv = attn2_bwd_dkv_kernel<NKC, NCH>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.needs()) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kdq, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kDqSmemBytes));
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(kdkv, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kDkvSmemBytes));
-    configured = true;
+    configured.done();
   }
   Attn2Params p{};
   p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale;
@@ -288,14 +288,14 @@ extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* 
   const int Lp = attn_lp(L);
   const int smem_dq = (128 + 2 * Lp) * 128;
   const int smem_dkv = (128 + 2 * Lp) * 128 + 2 * Lp * 4;
-  static int conf_dq = 0, conf_dkv = 0;
-  if (conf_dq < smem_dq) {
+  static DeviceMax conf_dq, conf_dkv;
+  if (conf_dq.get() < smem_dq) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq));
-    conf_dq = smem_dq;
+    conf_dq.set(smem_dq);
   }
-  if (conf_dkv < smem_dkv) {
+  if (conf_dkv.get() < smem_dkv) {
     PEFT_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv));
-    conf_dkv = smem_dkv;
+    conf_dkv.set(smem_dkv);
   }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   dim3 grid((L + 63) / 64, B * H);

@@ -63,15 +63,35 @@ inline std::atomic<unsigned long long>& kind_counter(int k) {
     if (!(cond)) return ::peft::fail(PEFT_ERR_INVALID, __VA_ARGS__); \
   } while (0)
 
-inline int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-  }
-  return n;
+inline int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return 0;
+  return dev & 63;
 }
+// SM count of the CURRENT device (cached per device: one process may drive several GPUs)
+inline int sm_count() {
+  static std::atomic<int> n[64];
+  const int dev = current_device();
+  int v = n[dev].load(std::memory_order_relaxed);
+  if (v == 0) {
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    n[dev].store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+// One-time per-DEVICE configuration of a kernel (cudaFuncSetAttribute is per device, not per process).  The guarded action is
+// idempotent, so two threads racing through needs() on the same device is harmless.
+struct DeviceOnce {
+  std::atomic<unsigned long long> mask{0};
+  bool needs() const { return !(mask.load(std::memory_order_acquire) & (1ull << current_device())); }
+  void done() { mask.fetch_or(1ull << current_device(), std::memory_order_release); }
+};
+// same for a configured maximum (dynamic shared memory raised on demand)
+struct DeviceMax {
+  std::atomic<int> v[64];
+  int get() const { return v[current_device()].load(std::memory_order_acquire); }
+  void set(int x) { v[current_device()].store(x, std::memory_order_release); }
+};
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -131,7 +151,8 @@ inline int make_tmap_2d(CUtensorMap* tm, const void* ptr, bool f32, unsigned lon
   if (r != CUDA_SUCCESS) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   {
     std::lock_guard<std::mutex> g(mu);
-    if (cache.size() > 16384) cache.clear();
+    if (cache.size() > 262144) cache.clear();     // ~34 MB of descriptors: far above what persistent workspaces produce; a
+                                                  // caller that streams fresh pointers through the library just re-encodes
     cache.emplace(key, *tm);
   }
   return 0;
@@ -164,7 +185,8 @@ inline int make_tmap_bf16_3d(CUtensorMap* tm, const void* ptr, unsigned long lon
   if (r != CUDA_SUCCESS) return fail(PEFT_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed with CUresult %d", (int)r);
   {
     std::lock_guard<std::mutex> g(mu);
-    if (cache.size() > 16384) cache.clear();
+    if (cache.size() > 262144) cache.clear();     // ~34 MB of descriptors: far above what persistent workspaces produce; a
+                                                  // caller that streams fresh pointers through the library just re-encodes
     cache.emplace(key, *tm);
   }
   return 0;
