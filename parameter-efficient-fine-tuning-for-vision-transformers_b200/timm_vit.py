@@ -3,8 +3,10 @@ few_shot/vision_benchmark/evaluation/{kadaptation,lora,adapter}.py (= full_shot/
 
 Same class names, constructor arguments, parameter names and shapes (so `state_dict()` / `load_state_dict()` and the
 trainers' name filters — `'W' in name`, `'adapter' in name` — work unchanged), but `VisionTransformer.forward` runs the
-whole tower through the CUDA engine (engine.py) instead of ATen.  The sub-modules only hold parameters; they have no
-eager forward — calling one raises, there is no fallback path.
+whole tower through the CUDA engine (engine.py) instead of ATen.  `Mlp`, the adapter-free `Attention`, `Adapter`, `Block` and
+`PatchEmbed` also have stand-alone forwards (eager.py: one autograd node each over the same C-ABI kernels, used by the per-
+component intrinsic-dimension model, intrinsic_vit.py); the q/v-adapted attention and the PHM modules run inside the engine
+only and raise when called alone.  There is no PyTorch-math fallback path anywhere.
 
 Adapter hyper-parameters are constructor kwargs with the reference's values as defaults where the reference is
 usable: LoRA r=4, alpha=128 (FS/lora.py); KAdaptation phm_rank=1, init 0.01, and phm_dim=4 instead of the committed
@@ -18,6 +20,7 @@ from functools import partial
 import torch
 import torch.nn as nn
 
+from . import eager, ops
 from .engine import EngineCfg, VitEngine, backbone, backbone_full
 
 
@@ -38,8 +41,13 @@ class Mlp(nn.Module):
         self.fc1 = nn.Linear(in_features, hidden_features)
         self.act = act_layer()
         self.fc2 = nn.Linear(hidden_features, out_features)
+        self.fp32 = False
 
-    forward = _no_eager
+    def forward(self, x):
+        """Stand-alone forward (eager.py): one autograd node, weights read through attribute access on every call so that a
+        FastfoodWrap around this module works (FL/lib/models/cls_intrinsic_dimension.py:470-473)."""
+        act = ops.EPI_GELU if isinstance(self.act, nn.GELU) else ops.EPI_QUICKGELU
+        return eager.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias, act, self.fp32)
 
 
 class Attention(nn.Module):
@@ -81,8 +89,16 @@ class Attention(nn.Module):
             self.v_proj_adapter2.weight.data.zero_()
         elif adapter not in ("none", "houlsby", "compacter"):
             raise ValueError(adapter)
+        self.fp32 = False
 
-    forward = _no_eager
+    def forward(self, x, prev=None):
+        """Stand-alone forward of the adapter-free attention (FL/lib/models/cls_intrinsic_dimension.py:466-469 wraps exactly
+        this); the q/v-adapted variants run inside the whole-tower engine only."""
+        if self.adapter_kind in ("kron", "lora"):
+            raise RuntimeError("Attention with a q/v adapter has no stand-alone forward in peft_b200: run the enclosing "
+                               "VisionTransformer (CUDA engine)")
+        return eager.attention(x, self.qkv.weight, self.qkv.bias, self.proj.weight, self.proj.bias, self.num_heads, self.scale,
+                               self.fp32)
 
 
 class Adapter(nn.Module):
@@ -102,8 +118,16 @@ class Adapter(nn.Module):
             for lin in (self.adapter_down[1], self.adapter_up):
                 nn.init.normal_(lin.weight, std=0.02)
                 nn.init.zeros_(lin.bias)
+        self.fp32 = False
 
-    forward = _no_eager
+    def forward(self, x, residual_input=None):
+        """(output, down, None): output = adapter_up(adapter_down(x)) + residual_input (default x, as in the copy of
+        FL/lib/models/cls_intrinsic_dimension.py:340-359); `down` = the post-ReLU bottleneck activations (compute dtype, not
+        differentiable).  The reference's third value `up` is read by no caller (`[0]` everywhere) and is not materialised."""
+        ln, down = self.adapter_norm_before, self.adapter_down[1]
+        out, z = eager.adapter(x, x if residual_input is None else residual_input, ln.weight, ln.bias, down.weight, down.bias,
+                               self.adapter_up.weight, self.adapter_up.bias, ln.eps, 1.0, self.fp32)
+        return out, z, None
 
 
 class PHMLinear(nn.Module):
@@ -162,8 +186,26 @@ class Block(nn.Module):
             self.adapter = Adapter(dim, down_sample=bottleneck)
         elif kind == "compacter":
             self.compacter = HyperComplexAdapter(dim, down_sample=bottleneck, n_down=compacter_n_down, n_up=compacter_n_up)
+        self.fp32 = False
 
-    forward = _no_eager
+    def _norm(self, ln, x):
+        return eager.layer_norm(x, ln.weight, ln.bias, ln.eps)
+
+    def forward(self, x, prev=None):
+        """Stand-alone block forward composed of the sub-module nodes (FS/kadaptation.py:273-277; with the Houlsby adapter
+        FS/adapter.py:452-456).  For throughput run the enclosing VisionTransformer: the engine fuses the same arithmetic."""
+        if self.drop_path_rate > 0. and self.training:
+            raise RuntimeError("stochastic depth runs inside the whole-tower engine only")
+        if hasattr(self, "compacter"):
+            raise RuntimeError("the Compacter block has no stand-alone forward in peft_b200 (whole-tower engine only)")
+        for m in (self.attn, self.mlp):
+            m.fp32 = self.fp32
+        x = x + self.attn(self._norm(self.norm1, x))
+        h = self.mlp(self._norm(self.norm2, x))
+        if hasattr(self, "adapter"):
+            self.adapter.fp32 = self.fp32
+            h = self.adapter(h, h)[0]
+        return x + h
 
 
 class PatchEmbed(nn.Module):
@@ -175,8 +217,11 @@ class PatchEmbed(nn.Module):
         self.patch_size = (patch_size, patch_size)
         self.num_patches = (img_size // patch_size) ** 2
         self.proj = nn.Conv2d(in_chans, embed_dim, kernel_size=patch_size, stride=patch_size)
+        self.fp32 = False
 
-    forward = _no_eager
+    def forward(self, x):
+        """[B, 3, S, S] -> [B, num_patches, D]: im2col + tensor-core product (no cuDNN convolution)."""
+        return eager.patch_embed(x, self.proj.weight, self.proj.bias, self.fp32)
 
 
 def lowrank_factors_kron(rule, w_left, w_right):
