@@ -47,6 +47,11 @@ unsigned long long peft_kernel_count(int kind);
 /* tuning / test knob: which tensor-core GEMM kernel peft_gemm_bf16 uses — 0 = automatic (2-CTA cta_group::2 kernel when
  * the problem fills the 74 SM pairs, else the 1-CTA kernel), 1 = always 1-CTA, 2 = always 2-CTA. */
 int peft_set_gemm_algo(int algo);
+/* programmatic dependent launch (cudaLaunchAttributeProgrammaticStreamSerialization) of the hot-path kernels: the prologue of a
+ * kernel (barrier init, TMEM allocation, tensor-map fetch) overlaps the tail of its predecessor on the stream; every such kernel
+ * executes griddepcontrol.wait before its first global-memory access.  1 = on (default; PEFT_PDL=0 in the environment turns it
+ * off), 0 = fully serialised launches (A/B measurements). */
+int peft_set_pdl(int enabled);
 /* stream-K scheduling of the 2-CTA GEMM (long contractions whose tile count leaves the last wave mostly empty, e.g. 75 tiles
  * on 74 SM pairs at M = 6304): 0 = off, 1 = automatic (default), 2 = whenever the shape allows it (tests).  Partial tiles
  * travel through ONE per-device workspace, so stream-K products of one device must be issued on one stream at a time. */

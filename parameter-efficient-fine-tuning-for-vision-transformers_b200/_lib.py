@@ -23,6 +23,7 @@ SIGNATURES = {
     "peft_launch_count": [],
     "peft_kernel_count": [C.c_int],
     "peft_set_gemm_algo": [C.c_int],
+    "peft_set_pdl": [C.c_int],
     "peft_set_gemm_streamk": [C.c_int],
     "peft_debug_gemm_stats": [_vp, C.c_int],
     "peft_debug_attn_stats": [_vp, C.c_int],

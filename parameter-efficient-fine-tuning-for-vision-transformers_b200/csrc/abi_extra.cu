@@ -64,9 +64,9 @@ extern "C" int peft_clip_delta(void* qkv, long long ldqkv, void* delta, long lon
   if (blocks > sm_count() * 16) blocks = sm_count() * 16;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (backward)
-    clip_delta_kernel<true><<<(int)blocks, 256, 0, s>>>((__nv_bfloat16*)qkv, ldqkv, (__nv_bfloat16*)delta, ldd, B, H, L, mult_q, mult_v);
+    (void)launch_pdl(PDL_MISC, clip_delta_kernel<true>, dim3((int)blocks), dim3(256), 0, s, (__nv_bfloat16*)qkv, ldqkv, (__nv_bfloat16*)delta, ldd, B, H, L, mult_q, mult_v);
   else
-    clip_delta_kernel<false><<<(int)blocks, 256, 0, s>>>((__nv_bfloat16*)qkv, ldqkv, (__nv_bfloat16*)delta, ldd, B, H, L, mult_q, mult_v);
+    (void)launch_pdl(PDL_MISC, clip_delta_kernel<false>, dim3((int)blocks), dim3(256), 0, s, (__nv_bfloat16*)qkv, ldqkv, (__nv_bfloat16*)delta, ldd, B, H, L, mult_q, mult_v);
   PEFT_LAUNCH_CHECK();
   return 0;
 }
@@ -83,12 +83,12 @@ static int transpose_impl(const void* in, long long ldin, int rows, int cols, vo
   if (vec) {
     dim3 grid((cols + 255) / 256, (rows + 63) / 64);
     if (colsum)
-      transpose_bf16_vec_kernel<true><<<grid, 256, 0, s>>>((const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout, colsum);
+      (void)launch_pdl(PDL_MISC, transpose_bf16_vec_kernel<true>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout, colsum);
     else
-      transpose_bf16_vec_kernel<false><<<grid, 256, 0, s>>>((const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout, nullptr);
+      (void)launch_pdl(PDL_MISC, transpose_bf16_vec_kernel<false>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout, nullptr);
   } else {
     dim3 grid((cols + 63) / 64, (rows + 63) / 64);
-    transpose_bf16_kernel<<<grid, 256, 0, s>>>((const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout);
+    (void)launch_pdl(PDL_MISC, transpose_bf16_kernel, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)in, ldin, rows, cols, (__nv_bfloat16*)out, ldout);
   }
   PEFT_LAUNCH_CHECK();
   return 0;
@@ -111,7 +111,7 @@ extern "C" int peft_colsum_bf16(const void* in, long long ldin, int rows, int co
   int gy = (2 * sm_count() + colblocks - 1) / colblocks;       // ~2 CTAs per SM in total; each walks nrb / gy row blocks
   if (gy > nrb) gy = nrb;
   if (gy < 1) gy = 1;
-  colsum_bf16_kernel<<<dim3(colblocks, gy), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>((const __nv_bfloat16*)in, ldin, rows,
+  (void)launch_pdl(PDL_MISC, colsum_bf16_kernel, dim3(dim3(colblocks, gy)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), (const __nv_bfloat16*)in, ldin, rows,
                                                                                              cols, colsum);
   PEFT_LAUNCH_CHECK();
   return 0;

@@ -17,7 +17,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   }
   const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
   const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, p);
+  (void)launch_pdl(PDL_GEMM1, kern, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, ta, tb, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_GEMM_1CTA);
   return 0;
 }
@@ -131,13 +131,15 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
   cfg.blockDim = dim3(kG2Threads, 1, 1);
   cfg.dynamicSmemBytes = kG2SmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // PDL, see common.cuh
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = (pdl_mode().load(std::memory_order_relaxed) & PDL_GEMM2) ? 2 : 1;
   PEFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, to, to2, tx, p));
   PEFT_LAUNCH_CHECK_KIND(TN ? KIND_GEMM_TN : KIND_GEMM_2CTA);
   return 0;
@@ -290,6 +292,11 @@ extern "C" int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, lo
 extern "C" int peft_set_gemm_streamk(int mode) {
   PEFT_REQUIRE(mode >= 0 && mode <= 2, "peft_set_gemm_streamk: mode must be 0 (off), 1 (automatic) or 2 (whenever possible)");
   streamk_mode().store(mode);
+  return 0;
+}
+
+extern "C" int peft_set_pdl(int enabled) {
+  peft::pdl_mode().store(enabled ? (int)peft::PDL_ALL : 0);
   return 0;
 }
 

@@ -47,13 +47,13 @@ extern "C" int peft_layernorm_fwd(const void* x, long long ldx, int x_is_bf16, c
   const int grid = ln_grid(M);
   LN_DISPATCH_NV(D / 128, {
     if (!x_is_bf16 && !y_is_f32)
-      ln_fwd_kernel<NV, float, __nv_bfloat16><<<grid, 256, 0, s>>>((const float*)x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps);
+      (void)launch_pdl(PDL_LN, ln_fwd_kernel<NV, float, __nv_bfloat16>, dim3(grid), dim3(256), 0, s, (const float*)x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps, nullptr, 0, nullptr, 0);
     else if (!x_is_bf16 && y_is_f32)
-      ln_fwd_kernel<NV, float, float><<<grid, 256, 0, s>>>((const float*)x, ldx, gamma, beta, (float*)y, ldy, mean, rstd, M, eps);
+      (void)launch_pdl(PDL_LN, ln_fwd_kernel<NV, float, float>, dim3(grid), dim3(256), 0, s, (const float*)x, ldx, gamma, beta, (float*)y, ldy, mean, rstd, M, eps, nullptr, 0, nullptr, 0);
     else if (x_is_bf16 && !y_is_f32)
-      ln_fwd_kernel<NV, __nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps);
+      (void)launch_pdl(PDL_LN, ln_fwd_kernel<NV, __nv_bfloat16, __nv_bfloat16>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps, nullptr, 0, nullptr, 0);
     else
-      ln_fwd_kernel<NV, __nv_bfloat16, float><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, ldx, gamma, beta, (float*)y, ldy, mean, rstd, M, eps);
+      (void)launch_pdl(PDL_LN, ln_fwd_kernel<NV, __nv_bfloat16, float>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)x, ldx, gamma, beta, (float*)y, ldy, mean, rstd, M, eps, nullptr, 0, nullptr, 0);
   });
   PEFT_LAUNCH_CHECK();
   return 0;
@@ -72,7 +72,7 @@ extern "C" int peft_layernorm_fwd_add(const float* x, long long ldx, const float
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int grid = ln_grid(M);
   LN_DISPATCH_NV(D / 128, {
-    ln_fwd_kernel<NV, float, __nv_bfloat16><<<grid, 256, 0, s>>>(x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps,
+    (void)launch_pdl(PDL_LN, ln_fwd_kernel<NV, float, __nv_bfloat16>, dim3(grid), dim3(256), 0, s, x, ldx, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, M, eps,
                                                                add_in, ldai, add_out, ldao);
   });
   PEFT_LAUNCH_CHECK();
@@ -93,7 +93,7 @@ extern "C" int peft_layernorm_bwd(const void* dy, long long lddy, int dy_is_f32,
   const int grid = ln_grid(M, pg);
   using bf = __nv_bfloat16;
 #define LN_BWD_LAUNCH(DYT, XT, PG) \
-  ln_bwd_kernel<NV, DYT, XT, bf, PG><<<grid, 256, 0, s>>>((const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, (const bf*)g_in, ldgi, (bf*)g_out, ldgo, dgamma, dbeta, M)
+  (void)launch_pdl(PDL_LN, ln_bwd_kernel<NV, DYT, XT, bf, PG>, dim3(grid), dim3(256), 0, s, (const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, (const bf*)g_in, ldgi, (bf*)g_out, ldgo, dgamma, dbeta, M, nullptr, 0)
   LN_DISPATCH_NV(D / 128, {
     if (dy_is_f32) {
       if (x_is_bf16) { if (pg) LN_BWD_LAUNCH(float, bf, true); else LN_BWD_LAUNCH(float, bf, false); }
@@ -126,7 +126,7 @@ extern "C" int peft_layernorm_bwd_f32g(const void* dy, long long lddy, int dy_is
   const int grid = ln_grid(M, pg);
   using bf = __nv_bfloat16;
 #define LN_BWD_LAUNCH32(DYT, XT, PG) \
-  ln_bwd_kernel<NV, DYT, XT, float, PG><<<grid, 256, 0, s>>>((const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, g_in, ldgi, g_out, ldgo, dgamma, dbeta, M, (bf*)g_copy, ldgc)
+  (void)launch_pdl(PDL_LN, ln_bwd_kernel<NV, DYT, XT, float, PG>, dim3(grid), dim3(256), 0, s, (const DYT*)dy, lddy, (const XT*)x, ldx, mean, rstd, gamma, g_in, ldgi, g_out, ldgo, dgamma, dbeta, M, (bf*)g_copy, ldgc)
   LN_DISPATCH_NV(D / 128, {
     if (dy_is_f32) {
       if (x_is_bf16) { if (pg) LN_BWD_LAUNCH32(float, bf, true); else LN_BWD_LAUNCH32(float, bf, false); }
@@ -202,7 +202,7 @@ static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long
   p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
   p.stats = attn_stats_buffer();
   const int grid = B * H < sm_count() ? B * H : sm_count();
-  kern<<<grid, kA2Threads, C::kSmemBytes, s>>>(tq, tkv, to, p);
+  (void)launch_pdl(PDL_ATTN, kern, dim3(grid), dim3(kA2Threads), C::kSmemBytes, s, tq, tkv, to, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_FWD);
   return 0;
 }
@@ -259,9 +259,9 @@ static int launch_attn2_bwd(const void* qkv, long long ldqkv, const void* o, lon
   Attn2Params p{};
   p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale;
   const int grid = B * H < sm_count() ? B * H : sm_count();
-  kdq<<<grid, kA2Threads, C::kDqSmemBytes, s>>>(t128, tchunk, tdo128, to128, tout, p);
+  (void)launch_pdl(PDL_ATTN, kdq, dim3(grid), dim3(kA2Threads), C::kDqSmemBytes, s, t128, tchunk, tdo128, to128, tout, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
-  kdkv<<<grid, kA2Threads, C::kDkvSmemBytes, s>>>(t128, tchunk, tdochunk, tout, p);
+  (void)launch_pdl(PDL_ATTN, kdkv, dim3(grid), dim3(kA2Threads), C::kDkvSmemBytes, s, t128, tchunk, tdochunk, tout, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
   return 0;
 }
@@ -347,9 +347,9 @@ extern "C" int peft_tn_reduce(const void* x, long long ldx, int I, const void* y
   dim3 grid(jt, my);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const __nv_bfloat16* X = (const __nv_bfloat16*)x; const __nv_bfloat16* Y = (const __nv_bfloat16*)y;
-  if (I == 16) tn_reduce_kernel<1><<<grid, kRedThreads, 0, s>>>(X, ldx, Y, ldy, out, ldout, M, rows);
-  else if (I == 32) tn_reduce_kernel<2><<<grid, kRedThreads, 0, s>>>(X, ldx, Y, ldy, out, ldout, M, rows);
-  else tn_reduce_kernel<4><<<grid, kRedThreads, 0, s>>>(X, ldx, Y, ldy, out, ldout, M, rows);
+  if (I == 16) (void)launch_pdl(PDL_REDUCE, tn_reduce_kernel<1>, dim3(grid), dim3(kRedThreads), 0, s, X, ldx, Y, ldy, out, ldout, M, rows);
+  else if (I == 32) (void)launch_pdl(PDL_REDUCE, tn_reduce_kernel<2>, dim3(grid), dim3(kRedThreads), 0, s, X, ldx, Y, ldy, out, ldout, M, rows);
+  else (void)launch_pdl(PDL_REDUCE, tn_reduce_kernel<4>, dim3(grid), dim3(kRedThreads), 0, s, X, ldx, Y, ldy, out, ldout, M, rows);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

@@ -162,6 +162,7 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                            // PDL (common.cuh): no global-memory access above this line
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
@@ -349,6 +350,7 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   }
   ptx::tcgen05_fence_before();
   __syncthreads();
+  pdl_trigger();                                         // PDL: late on purpose (see gemm2_sm100.cuh)
   if (warp == 2) ptx::tmem_dealloc<C::kDqTmemCols>(tmem_base);
 }
 
@@ -409,6 +411,7 @@ attn2_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                            // PDL (common.cuh): no global-memory access above this line
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
@@ -587,6 +590,7 @@ attn2_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
   }
   ptx::tcgen05_fence_before();
   __syncthreads();
+  pdl_trigger();                                         // PDL: late on purpose (see gemm2_sm100.cuh)
   if (warp == 2) ptx::tmem_dealloc<C::kDkvTmemCols>(tmem_base);
 }
 

@@ -236,6 +236,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                            // no global-memory access above this line
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
@@ -482,6 +483,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   }
   ptx::tcgen05_fence_before();
   __syncthreads();
+  pdl_trigger();                                         // PDL: late on purpose (see gemm2_sm100.cuh)
   if (warp == 2) ptx::tmem_dealloc<C::kTmemCols>(tmem_base);
 }
 

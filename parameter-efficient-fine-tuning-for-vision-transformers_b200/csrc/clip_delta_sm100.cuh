@@ -14,6 +14,7 @@
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
+#include "pdl_sm100.cuh"
 
 namespace peft {
 
@@ -21,6 +22,8 @@ template <bool BWD>
 __global__ void __launch_bounds__(256) clip_delta_kernel(__nv_bfloat16* __restrict__ qkv, long long ldqkv,
                                                         __nv_bfloat16* __restrict__ delta, long long ldd, int B, int H,
                                                         int L, float mult_q, float mult_v) {
+  pdl_trigger();                     // PDL (common.cuh)
+  pdl_wait();
   const long long chunks = (long long)B * H * L;      // 64-element chunks per tensor (q or v)
   const long long total = chunks * 2 * 8;             // x {q, v} x 8 vectors of 8 bf16
   const int D = H * 64;
@@ -77,6 +80,8 @@ __global__ void __launch_bounds__(256) clip_delta_kernel(__nv_bfloat16* __restri
 __global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows,
                                                             int cols, __nv_bfloat16* __restrict__ out, long long ldout) {
   __shared__ __nv_bfloat16 tile[64][66];
+  pdl_trigger();                     // PDL (common.cuh)
+  pdl_wait();
   const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;
   const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
   // load: 8 warps x 8 passes, each warp reads one 64-element row as 32 x bf16x2
@@ -129,6 +134,8 @@ template <bool COLSUM, bool STORE = true>
 __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows,
                                                                 int cols, __nv_bfloat16* __restrict__ out, long long ldout,
                                                                 float* __restrict__ colsum) {
+  pdl_trigger();                     // PDL (common.cuh)
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cg = lane & 3, rg = lane >> 2;
   const int r0 = blockIdx.y * 64 + rg * 8;
@@ -195,6 +202,8 @@ __global__ void __launch_bounds__(256) transpose_bf16_vec_kernel(const __nv_bflo
 // spent more time serialising same-address atomics in L2 than streaming: 23 us for [12800, 3072]).
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldin, int rows, int cols,
                                                          float* __restrict__ colsum) {
+  pdl_trigger();                     // PDL (common.cuh)
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cg = lane & 3, rg = lane >> 2;
   const int c0 = blockIdx.x * 256 + warp * 32 + cg * 8;

@@ -7,9 +7,11 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
+#include <utility>
 #include "../../include/peft_b200.h"
 
 namespace peft {
@@ -92,6 +94,42 @@ struct DeviceMax {
   int get() const { return v[current_device()].load(std::memory_order_acquire); }
   void set(int x) { v[current_device()].store(x, std::memory_order_release); }
 };
+
+// ---------------------------------------------------------------- programmatic dependent launch (PDL)
+// A step is ~290 dependent launches on one stream; with full stream serialisation every boundary costs the drain of the
+// previous grid + the launch latency + the prologue (barrier init, TMEM allocation, tensor-map fetch, cluster sync) of the
+// next one.  Kernels launched through launch_pdl() carry cudaLaunchAttributeProgrammaticStreamSerialization: their CTAs may
+// be scheduled once every CTA of the predecessor has executed pdl_trigger() (pdl_sm100.cuh) and an SM has room, run their
+// prologue, and block in pdl_wait() until the predecessor grid has COMPLETED and its memory is visible.  Rules every PDL
+// kernel in this library follows: no global-memory access of any kind before pdl_wait(), and every CTA calls it — so
+// completion of a grid still implies completion of everything before it.  Captured by CUDA graphs as programmatic edges.
+// WHERE the trigger sits matters (measured, r02): the tensor-core kernels (one CTA per SM, CTAs finish at different times)
+// trigger at their very END — with an early trigger the grid-stride CTAs of a following LayerNorm / token reduction were
+// placed on the SMs that happened to be free first (up to 8 per SM) instead of evenly, which cost 12 us per such launch
+// (+0.7 ms per C3 step); the small kernels, whose CTAs are spread evenly, trigger at their start.  Effect on C3 (graph replay,
+// same box): B = 256 28.07 -> 27.93 ms, B = 32 (the 8-GPU split) 4.94 -> 4.81 ms; GEMM launch floor 7.4 -> 6.4 us.
+// PEFT_PDL=0 (or peft_set_pdl(0)) launches everything fully serialised; PEFT_PDL=<mask> enables single kernel families.
+// kernel families (bit mask in PEFT_PDL / peft_set_pdl: A/B measurements per family)
+enum { PDL_GEMM2 = 1, PDL_GEMM1 = 2, PDL_ATTN = 4, PDL_LN = 8, PDL_REDUCE = 16, PDL_MISC = 32, PDL_ALL = 63 };
+inline std::atomic<int>& pdl_mode() {
+  static std::atomic<int> m{[] { const char* e = getenv("PEFT_PDL"); return e ? atoi(e) : (int)PDL_ALL; }()};
+  return m;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int family, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl_mode().load(std::memory_order_relaxed) & family) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

@@ -431,6 +431,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   ptx::cluster_sync();               // peer barriers initialised + peer TMEM allocated before any cross-CTA traffic
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                        // everything above overlapped the predecessor's tail; global memory only from here on
 
   const int num_mp = (p.M + 2 * kBM - 1) / (2 * kBM);     // 256-row pair tiles
   const int num_n = (p.N + kG2BN - 1) / kG2BN;
@@ -807,6 +808,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   }
   ptx::tcgen05_fence_before();
   __syncthreads();
+  pdl_trigger();                          // PDL: late on purpose — an early trigger lets grid-stride dependents (LayerNorm, token
+                                          // reductions) pile onto the SMs that finish first instead of spreading over all of them
   ptx::cluster_sync();                    // the peer may still be multicasting into / reading from this CTA
   if (warp == 2) ptx::tmem_dealloc_2sm<512>(tmem_base);
 }

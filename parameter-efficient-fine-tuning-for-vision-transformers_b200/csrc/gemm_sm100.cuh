@@ -260,6 +260,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                        // PDL (common.cuh): no global-memory access above this line
 
   const int num_m = (p.M + kBM - 1) / kBM;
   const int num_n = (p.N + BN - 1) / BN;
@@ -359,6 +360,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   }
   ptx::tcgen05_fence_before();
   __syncthreads();
+  pdl_trigger();                     // PDL: late on purpose (see gemm2_sm100.cuh)
   if (warp == 2) ptx::tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 

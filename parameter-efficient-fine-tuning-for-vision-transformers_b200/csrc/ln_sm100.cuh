@@ -48,6 +48,8 @@ ln_fwd_kernel(const InT* __restrict__ x, long long ldx, const float* __restrict_
               OutT* __restrict__ y, long long ldy, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M,
               float eps, const float* __restrict__ add_in = nullptr, long long ldai = 0, float* __restrict__ add_out = nullptr,
               long long ldao = 0) {
+  pdl_trigger();                     // PDL (common.cuh): CTAs become resident during the predecessor's tail ...
+  pdl_wait();                        // ... and read nothing before it has completed
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
   const int D = NV * 128;
@@ -120,6 +122,8 @@ ln_bwd_kernel(const DyT* __restrict__ dy, long long lddy, const XT* __restrict__
               const GT* __restrict__ g_in, long long ldgi, GT* __restrict__ g_out, long long ldgo,
               float* __restrict__ dgamma, float* __restrict__ dbeta, int M,
               __nv_bfloat16* __restrict__ g_copy = nullptr, long long ldgc = 0) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;

@@ -2,6 +2,7 @@
 // tcgen05 (alloc / mma / commit / ld / fences), plus the legacy warp-level mma.sync + ldmatrix used by the
 // skinny adapter-gradient reductions and attention v1.  Nothing here is a library call.
 #pragma once
+#include "pdl_sm100.cuh"
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>

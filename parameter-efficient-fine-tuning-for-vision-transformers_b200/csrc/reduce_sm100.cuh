@@ -31,6 +31,8 @@ tn_reduce_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const __nv_
   __shared__ __align__(128) uint8_t sY[2][kYBytes];
   __shared__ float sRed[I * 64];
 
+  pdl_trigger();                     // PDL (common.cuh)
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int j0 = blockIdx.x * 64;
   const long long m_begin = (long long)blockIdx.y * rows_per_cta;
