@@ -85,6 +85,18 @@ int peft_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, i
 int peft_gemm_bf16_rs(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
                       const float* bias, void* out, long long ldo, void* out2, long long ldo2,
                       const void* aux, long long ldaux, int epilogue, const float* rowscale, void* stream);
+/* Allocation-free variant of peft_gemm_bf16 (2-CTA tcgen05 kernel, stream-K whenever the shape allows it).  It has no
+ * counterpart in the reference and was added: for callers that may not call cudaMalloc
+ * (code under CUDA-graph capture without a warm-up call, tight serving loops, harnesses that forbid allocation).  The stream-K
+ * fix-up scratch (one 256 x 256 fp32 partial-tile slot per SM pair + per-warp flags) lives in a file-scope
+ * `static __device__ __align__(256)` array of 80 slots = 20 MiB (+ 5 KiB of flags) that every GPU loading the library holds
+ * until exit; the call performs no cudaMalloc / cudaFree / allocating library call.  Limits: devices with more than 80 SM pairs
+ * (160 SMs) and products of more than 2^24 output tiles are rejected with PEFT_ERR_INVALID and a message.  All calls on a device
+ * share the one array (it keeps the last call's partial sums; the flags are cleared on the stream before every launch): calls
+ * whose kernels overlap on the GPU race — issue them on one stream.  Same arguments, epilogues and results as peft_gemm_bf16. */
+int peft_gemm_bf16_noalloc(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
+                           const float* bias, void* out, long long ldo, void* out2, long long ldo2,
+                           const void* aux, long long ldaux, int epilogue, void* stream);
 
 /* LayerNorm over the last dimension, one warp per token row, D % 128 == 0.
  * replaces: nn.LayerNorm / CLIP LayerNorm forward — FS/kadaptation.py:274-276,538 (eps 1e-6), FS/model.py:156-162,1156-1157,1208,1214 (eps 1e-5).

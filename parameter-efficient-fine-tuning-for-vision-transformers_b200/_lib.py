@@ -29,6 +29,7 @@ SIGNATURES = {
     "peft_debug_attn_stats": [_vp, C.c_int],
     "peft_set_attention_algo": [C.c_int],
     "peft_gemm_bf16": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
+    "peft_gemm_bf16_noalloc": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
     "peft_gemm_bf16_rs": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp, _vp],
     "peft_gemm_f32_rs": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp, _vp],
     "peft_layernorm_fwd": [_vp, _c_ll, C.c_int, _vp, _vp, _vp, _c_ll, C.c_int, _vp, _vp, C.c_int, C.c_int, C.c_float, _vp],

@@ -337,3 +337,116 @@ extern "C" int peft_debug_gemm_stats(unsigned long long* host_out, int n_ctas) {
   PEFT_CUDA_CHECK(cudaMemcpy(host_out, buf, (size_t)n_ctas * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return 0;
 }
+
+namespace peft {
+// ---------------------------------------------------------------- allocation-free stream-K product
+// peft_gemm_bf16_noalloc: the 2-CTA product of peft_gemm_bf16 for callers that may not allocate device memory (code under
+// CUDA-graph capture that never ran a warm-up call, serving loops, harnesses that forbid cudaMalloc).  The stream-K fix-up
+// scratch — one [256 x 256] fp32 partial-tile slot per SM pair + the per-warp flags — lives in the file-scope device arrays
+// below instead of the cudaMalloc'ed per-device workspace of sk_workspace(): kNoAllocMaxClusters slots = 20 MiB + 5 KiB,
+// held by every GPU that loads the library until the process exits.  No counterpart in the
+// reference.
+//   * In host code `g_noalloc_ws` is only a stand-in for the symbol: its device address is taken once per device, with that
+//     device current, through cudaGetSymbolAddress (noalloc_scratch below) and handed to the kernel in GemmParams.
+//   * All calls on a device share the one array: two calls whose kernels overlap on the GPU (different streams, or graph
+//     branches) race.  Serialise them on one stream.  The array keeps the last call's partial sums — every slot is fully
+//     written before its flag is raised, so nothing but the flags must start at zero; they are cleared on the stream before
+//     every launch (a launch that was aborted by the watchdog trap cannot poison the next one).
+constexpr int kNoAllocMaxClusters = 80;                                       // B200: 148 SMs = 74 pairs
+constexpr size_t kNoAllocSlotF4 = (size_t)2 * kEpiWarps * 1024;               // float4 per cluster slot (256 KiB)
+static __device__ __align__(256) float4 g_noalloc_ws[kNoAllocMaxClusters * kNoAllocSlotF4];
+static __device__ __align__(256) int g_noalloc_flags[kNoAllocMaxClusters * 2 * kEpiWarps];
+
+struct NoAllocScratch { float4* ws = nullptr; int* flags = nullptr; };
+static int noalloc_scratch(NoAllocScratch* out) {
+  static std::mutex mu;
+  static NoAllocScratch per_dev[64];
+  int dev = 0;
+  PEFT_CUDA_CHECK(cudaGetDevice(&dev));
+  PEFT_REQUIRE(dev >= 0 && dev < 64, "peft_gemm_bf16_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> g(mu);
+  NoAllocScratch& s = per_dev[dev];
+  if (s.ws == nullptr) {                      // once per device, with that device current
+    void* pw = nullptr;
+    void* pf = nullptr;
+    PEFT_CUDA_CHECK(cudaGetSymbolAddress(&pw, g_noalloc_ws));
+    PEFT_CUDA_CHECK(cudaGetSymbolAddress(&pf, g_noalloc_flags));
+    PEFT_REQUIRE(pw != nullptr && pf != nullptr, "peft_gemm_bf16_noalloc: cudaGetSymbolAddress returned a null address");
+    s.flags = reinterpret_cast<int*>(pf);
+    s.ws = reinterpret_cast<float4*>(pw);
+  }
+  *out = s;
+  return 0;
+}
+
+}  // namespace peft
+
+extern "C" int peft_gemm_bf16_noalloc(const void* a, long long lda, const void* b, long long ldb, int M, int N, int K,
+                                      const float* bias, void* out, long long ldo, void* out2, long long ldo2,
+                                      const void* aux, long long ldaux, int epilogue, void* stream) {
+  PEFT_REQUIRE(M > 0 && N > 0 && K > 0, "peft_gemm_bf16_noalloc: empty problem M=%d N=%d K=%d", M, N, K);
+  PEFT_REQUIRE(a && b && out, "peft_gemm_bf16_noalloc: null operand");
+  PEFT_REQUIRE(epilogue >= 0 && epilogue <= EPI_RESID_BF16, "peft_gemm_bf16_noalloc: unknown epilogue %d", epilogue);
+  PEFT_REQUIRE(K % 8 == 0, "peft_gemm_bf16_noalloc: K must be a multiple of 8 (got %d)", K);
+  PEFT_REQUIRE(lda >= K && ldb >= K, "peft_gemm_bf16_noalloc: pitch smaller than K");
+  const int clusters = sm_count() / 2;
+  PEFT_REQUIRE(clusters <= kNoAllocMaxClusters,
+               "peft_gemm_bf16_noalloc: this device has %d SM pairs, the static stream-K scratch holds %d slots (20 MiB); use "
+               "peft_gemm_bf16", clusters, kNoAllocMaxClusters);
+  const long long tiles = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  PEFT_REQUIRE(tiles <= (1 << 24), "peft_gemm_bf16_noalloc: %lld output tiles exceed the supported maximum of %d", tiles, 1 << 24);
+  const bool f32out = (epilogue == EPI_RESID_F32 || epilogue == EPI_STORE_F32);
+  const int oelt = f32out ? 4 : 2;
+  PEFT_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (ldo * oelt) % 16 == 0,
+               "peft_gemm_bf16_noalloc: out must be 16-byte aligned with a 16-byte-multiple pitch");
+  const bool needs_out2 = (epilogue == EPI_GELU || epilogue == EPI_QUICKGELU || epilogue == EPI_GELU_TANH);
+  if (needs_out2)
+    PEFT_REQUIRE(out2 && (reinterpret_cast<uintptr_t>(out2) & 15) == 0 && (ldo2 * 2) % 16 == 0,
+                 "peft_gemm_bf16_noalloc: activation epilogue needs an aligned out2");
+  const bool needs_aux = (epilogue == EPI_RESID_F32 || epilogue == EPI_DGELU || epilogue == EPI_DQUICKGELU ||
+                          epilogue == EPI_DRELU || epilogue == EPI_DGELU_TANH || epilogue == EPI_RESID_BF16);
+  if (needs_aux) {
+    const int aelt = (epilogue == EPI_RESID_F32) ? 4 : 2;
+    PEFT_REQUIRE(aux && (reinterpret_cast<uintptr_t>(aux) & 15) == 0 && (ldaux * aelt) % 16 == 0,
+                 "peft_gemm_bf16_noalloc: epilogue %d needs an aligned aux operand", epilogue);
+  }
+  if (bias) PEFT_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "peft_gemm_bf16_noalloc: bias must be 16-byte aligned");
+
+  NoAllocScratch sc;
+  int rc = noalloc_scratch(&sc);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K; p.bias = bias; p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2;
+  p.aux = aux; p.ldaux = ldaux;
+  p.ksplit = 1;
+  // stream-K whenever the shape allows it (the rule of decide_streamk's mode 2): all but the last full wave stay data-parallel,
+  // the k-blocks of the rest are dealt out evenly; otherwise a plain data-parallel launch that touches no scratch at all
+  p.sk_dp_tiles = -1;
+  const int KB = (K + kBK - 1) / kBK;
+  const long long dp = tiles >= clusters ? (tiles / clusters - 1) * clusters : 0;
+  if (KB >= 2 && (tiles - dp) * KB >= 4LL * clusters) {
+    p.sk_dp_tiles = (int)dp;
+    p.sk_ws = sc.ws;
+    p.sk_flags = sc.flags;
+    PEFT_CUDA_CHECK(cudaMemsetAsync(sc.flags, 0, sizeof(int) * kNoAllocMaxClusters * 2 * kEpiWarps, s));
+  }
+  CUtensorMap ta, tb, to, to2, tx;
+  rc = make_tmap_2d(&ta, a, false, (unsigned long long)M, (unsigned long long)K, (unsigned long long)lda, kBM, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tb, b, false, (unsigned long long)N, (unsigned long long)K, (unsigned long long)ldb, kG2BN / 2, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d(&to, out, f32out, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldo, 32, f32out ? 32 : 64);
+  if (rc) return rc;
+  to2 = to; tx = to;
+  if (needs_out2) {
+    rc = make_tmap_2d(&to2, out2, false, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldo2, 32, 64);
+    if (rc) return rc;
+  }
+  if (needs_aux) {
+    const bool af32 = (epilogue == EPI_RESID_F32);
+    rc = make_tmap_2d(&tx, aux, af32, (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldaux, 32, af32 ? 32 : 64);
+    if (rc) return rc;
+  }
+  return dispatch_gemm2(epilogue, ta, tb, to, to2, tx, p, s);
+}
