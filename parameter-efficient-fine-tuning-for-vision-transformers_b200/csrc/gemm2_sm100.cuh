@@ -493,7 +493,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
       }
     }
-    if (p.stats && lane == 0) { p.stats[blockIdx.x * 8 + 0] = t_wait; p.stats[blockIdx.x * 8 + 1] = clock64() - t_begin; }
+    if (p.stats && !(p.dbg & 128) && lane == 0) { p.stats[blockIdx.x * 8 + 0] = t_wait; p.stats[blockIdx.x * 8 + 1] = clock64() - t_begin; }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA; one elected lane issues) =====================
     if (leader) {
@@ -547,7 +547,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
-      if (p.stats && lane == 0) {
+      if (p.stats && !(p.dbg & 128) && lane == 0) {
         p.stats[blockIdx.x * 8 + 2] = t_wfull; p.stats[blockIdx.x * 8 + 3] = t_wtmem; p.stats[blockIdx.x * 8 + 4] = clock64() - t_begin;
       }
     }
@@ -565,6 +565,11 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     int acc = 0;
     uint32_t acc_phase = 0;
     long long t_wacc = 0, t_begin = clock64();
+    // diagnostics (PEFT_GEMM_STATS + PEFT_GEMM_DBG bit 7): cycles of epilogue warp 0 per phase — 0 TMEM load, 1 bias / row scale,
+    // 2 slot or aux wait (+ aux math), 3 pack + st.shared + fence + store issue, 4 activation math
+    const bool ph = p.stats != nullptr && (p.dbg & 128);
+    long long tp[5] = {0, 0, 0, 0, 0}, tc = 0;
+    auto tick = [&](int i) { if (ph) { const long long n = clock64(); tp[i] += n - tc; tc = n; } };
     TileSched sched(p, num_tiles_mn, num_kb, cluster_id, num_clusters);
     // stream-K workspace of this warp inside cluster c's slot: [2 CTAs][8 warps][1024 float4], unit-major then 16-byte chunk
     // then lane (coalesced); sk_flags[(c * 2 + cta) * 8 + warp] = 1 once that warp's part of the partial tile is visible
@@ -622,6 +627,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         const int colu = col0 + u * T::kUnitCols;
         constexpr int NP = T::kUnitCols / 2;     // the unit as fp32 PAIRS: all arithmetic below is packed (FFMA2 / FMUL2 / FADD2)
         float2 v[NP];
+        if (ph) tc = clock64();
         {
           uint32_t r[32];
           ptx::tmem_ld_32x32b_x32(taddr0 + u * T::kUnitCols, r);
@@ -640,6 +646,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             for (int j = 0; j < 16; ++j) v[j] = make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
           }
         }
+        tick(0);
         if (u == T::kUnits - 1) {
           // all of this warp's accumulator reads are done: hand the TMEM buffer back to the MMA issuer
           ptx::tcgen05_fence_before();
@@ -689,6 +696,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 #pragma unroll
           for (int j = 0; j < NP; ++j) v[j] = mul2(v[j], rs);
         }
+        tick(1);
         // ---- slot availability / auxiliary operand
         if constexpr (T::kAux) {
           ptx::mbar_wait(&abar[s], (aux_phase >> s) & 1u);
@@ -729,6 +737,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 #pragma unroll
           for (int j = 0; j < NP; ++j) { v[j].x = fmaxf(v[j].x, 0.f); v[j].y = fmaxf(v[j].y, 0.f); }
         }
+        tick(2);
         // ---- registers -> swizzled slot
         if constexpr (T::kF32Out) {
 #pragma unroll
@@ -750,17 +759,26 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               ptx::tma_store_2d(&tmap_out, slot_ptr(0), colu, row0);
               ptx::bulk_commit();
             }
+            tick(3);
             // the activation is evaluated on the fp32 pre-activation (its bf16 copy goes to `out` for the backward pass: the
             // two differ by one bf16 rounding of h, 2^-9 relative, far inside the activation's own bf16 output rounding)
+            // (the diagnostic switch sits OUTSIDE the unrolled loop: a branch per pair splits it into 32 basic blocks, and each
+            // pair's mul -> fma -> fma -> MUFU -> fma -> pack chain then runs at full latency with nothing to overlap — measured
+            // 77 clk per pair per warp, 2.5 k clk per 64 columns, r02 gemm_phases)
+            if (p.dbg & 32) {                                                              // diagnostic: no activation math
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float2 a;
-              if (p.dbg & 32) { pk[j] = ptx::pack_bf16x2(v[j].y, v[j].x); continue; }   // diagnostic: no activation math
-              if constexpr (EPI == EPI_GELU) a = gelu_erf2(v[j]);
-              else if constexpr (EPI == EPI_QUICKGELU) a = quickgelu2(v[j]);
-              else a = gelu_tanh2(v[j]);
-              pk[j] = ptx::pack_bf16x2(a.x, a.y);
+              for (int j = 0; j < 32; ++j) pk[j] = ptx::pack_bf16x2(v[j].y, v[j].x);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                float2 a;
+                if constexpr (EPI == EPI_GELU) a = gelu_erf2(v[j]);
+                else if constexpr (EPI == EPI_QUICKGELU) a = quickgelu2(v[j]);
+                else a = gelu_tanh2(v[j]);
+                pk[j] = ptx::pack_bf16x2(a.x, a.y);
+              }
             }
+            tick(4);
             if (lane == 0) ptx::bulk_wait_read<1>();   // slot 1's previous store has been read (only the h store above is younger)
             __syncwarp();
 #pragma unroll
@@ -788,6 +806,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             }
           }
         }
+        __syncwarp();
+        tick(3);
       }
       if (kind == kSegPartial) {
         __syncwarp();                         // every lane's partial-sum stores are ordered before lane 0's fence + flag
@@ -804,7 +824,10 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       if (acc == 0) acc_phase ^= 1;
     }
     if (lane == 0) ptx::bulk_wait<0>();   // all global writes of this warp are complete before the CTA exits
-    if (p.stats && ew == 0 && lane == 0) { p.stats[blockIdx.x * 8 + 5] = t_wacc; p.stats[blockIdx.x * 8 + 6] = clock64() - t_begin; }
+    if (p.stats && ew == 0 && lane == 0) {
+      p.stats[blockIdx.x * 8 + 5] = t_wacc; p.stats[blockIdx.x * 8 + 6] = clock64() - t_begin;
+      if (ph) for (int i = 0; i < 5; ++i) p.stats[blockIdx.x * 8 + i] = tp[i];
+    }
   }
   ptx::tcgen05_fence_before();
   __syncthreads();

@@ -326,6 +326,30 @@ if __name__ == "__main__":
     if what == "gemm_probe":
         print("PEFT_GEMM_DBG =", os.environ.get("PEFT_GEMM_DBG", "0"), flush=True)
         gemm_scaling_probe()
+    if what == "gemm_phases":   # PEFT_GEMM_STATS=1 PEFT_GEMM_DBG=128(+...): cycles of epilogue warp 4 per phase
+        import ctypes
+        M = 50432
+        buf = (ctypes.c_ulonglong * (148 * 8))()
+        for name, N, K, epi in [("qkv store", 2304, 784, ops.EPI_STORE), ("fc1 +GELU", 3072, 768, ops.EPI_GELU), ("fc2 +resid f32", 768, 3072, ops.EPI_RESID_F32),
+                                ("fc2^T *gelu'", 3072, 768, ops.EPI_DGELU)]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+            bias = torch.randn(N, device="cuda")
+            f32 = epi == ops.EPI_RESID_F32
+            out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
+            out2 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16) if epi == ops.EPI_GELU else None
+            aux = torch.randn(M, N, device="cuda") if f32 else (torch.randn(M, N, device="cuda").to(torch.bfloat16) if epi == ops.EPI_DGELU else None)
+            if os.environ.get("NOBIAS"):
+                bias = None
+            run = lambda: ops.gemm(a, b, out, bias=bias, epilogue=epi, out2=out2, aux=aux)
+            t = timeit(run, iters=5, warm=2)
+            run()
+            _lib.check(_lib.load().peft_debug_gemm_stats(buf, 148))
+            v = torch.tensor(list(buf), dtype=torch.float64).view(148, 8).mean(0)
+            units = ((M + 255) // 256) * ((N + 255) // 256) / 74.0 * (4 if f32 else 2)
+            names = ["tmem ld", "bias", "slot/aux", "pack+st+store", "act math"]
+            print(f"{name:16s} {t:7.1f} us | epilogue warp total {v[6]:9.0f} clk, wait-acc {100 * v[5] / v[6]:4.1f}% | per unit: " +
+                  ", ".join(f"{n} {v[i] / units:6.0f}" for i, n in enumerate(names)), flush=True)
     if what == "gemm_stats":
         gemm_stats(50432)
         gemm_stats(6304)
