@@ -64,6 +64,10 @@ int peft_debug_gemm_stats(unsigned long long* host_out, int n_ctas);
 /* same for the tcgen05 attention forward (PEFT_ATTN_STATS=1): host_out[(cta*2 + warpgroup)*8 + {0: wait S, 1: max pass,
  * 2: exp pass, 3: wait O, 4: O epilogue + store, 5: total}] of the first softmax warp of each warpgroup. */
 int peft_debug_attn_stats(unsigned long long* host_out, int n_ctas);
+/* diagnostics: one CTA issues `reps` tcgen05.mma (M = 128, N = n, K = 16, bf16; ts != 0: A operand from TMEM) that rotate over
+ * `nacc` accumulators (nacc = 1: a fully dependent chain); host_out[0] = cycles to issue them, host_out[1] = cycles until the
+ * last one has completed.  Measures the dependent-accumulate latency that paces the attention kernels. */
+int peft_debug_mma_probe(int n, int nacc, int ts, int reps, unsigned long long* host_out);
 /* same for the attention kernels: 0 = automatic (tcgen05/TMEM kernels for L <= 272), 1 = mma.sync kernels, 2 = tcgen05 */
 int peft_set_attention_algo(int algo);
 

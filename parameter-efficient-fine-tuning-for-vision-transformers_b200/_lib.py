@@ -27,6 +27,7 @@ SIGNATURES = {
     "peft_set_gemm_streamk": [C.c_int],
     "peft_debug_gemm_stats": [_vp, C.c_int],
     "peft_debug_attn_stats": [_vp, C.c_int],
+    "peft_debug_mma_probe": [C.c_int, C.c_int, C.c_int, C.c_int, _vp],
     "peft_set_attention_algo": [C.c_int],
     "peft_gemm_bf16": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],
     "peft_gemm_bf16_noalloc": [_vp, _c_ll, _vp, _c_ll, C.c_int, C.c_int, C.c_int, _vp, _vp, _c_ll, _vp, _c_ll, _vp, _c_ll, C.c_int, _vp],

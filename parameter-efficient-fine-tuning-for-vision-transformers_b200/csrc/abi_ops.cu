@@ -5,6 +5,7 @@
 #include "attention_sm100.cuh"
 #include "attention2_sm100.cuh"
 #include "attention2_bwd_sm100.cuh"
+#include "attention3_bwd_sm100.cuh"
 #include "reduce_sm100.cuh"
 
 using namespace peft;
@@ -142,6 +143,12 @@ extern "C" int peft_layernorm_bwd_f32g(const void* dy, long long lddy, int dy_is
 }
 
 static int attn_lp(int L) { return ((L + 63) / 64) * 64; }
+static int attn_prefetch() {
+  // measured r02 (bench_ops.py attn, B = 256, H = 12, L = 197): no gain (fwd 84.8 -> 87.6 us, bwd 330 -> 337 us), so it is OFF by
+  // default and kept as a switch: the kernels are not bound by the latency of their operand loads
+  static const int v = [] { const char* e = getenv("PEFT_ATTN_PREFETCH"); return e ? atoi(e) : 0; }();
+  return v;
+}
 
 static int attn_check(const AttnParams& p) {
   PEFT_REQUIRE(p.B > 0 && p.H > 0 && p.L > 0, "attention: empty problem");
@@ -152,11 +159,13 @@ static int attn_check(const AttnParams& p) {
 }
 
 static std::atomic<int>& attn_algo() {
-  static std::atomic<int> a{0};   // 0 = auto (tcgen05 kernels), 1 = mma.sync v1 kernels, 2 = tcgen05 kernels
+  // 0 = auto (tcgen05 kernels, pipelined backward), 1 = mma.sync v1 kernels, 2 = tcgen05 kernels with the round-1 backward
+  // (attention2_bwd_sm100.cuh: tensor core and exp pipes take turns), 3 = same as auto
+  static std::atomic<int> a{[] { const char* e = getenv("PEFT_ATTN_ALGO"); const int v = e ? atoi(e) : 0; return (v >= 0 && v <= 3) ? v : 0; }()};
   return a;
 }
 extern "C" int peft_set_attention_algo(int algo) {
-  PEFT_REQUIRE(algo >= 0 && algo <= 2, "peft_set_attention_algo: algo must be 0 (auto), 1 (mma.sync) or 2 (tcgen05)");
+  PEFT_REQUIRE(algo >= 0 && algo <= 3, "peft_set_attention_algo: algo must be 0 (auto), 1 (mma.sync), 2 (tcgen05, unpipelined backward) or 3 (tcgen05, pipelined backward)");
   attn_algo().store(algo);
   return 0;
 }
@@ -166,7 +175,7 @@ static unsigned long long* attn_stats_buffer() {
   static unsigned long long* buf = [] {
     const char* e = getenv("PEFT_ATTN_STATS");
     unsigned long long* p = nullptr;
-    if (e && atoi(e) > 0 && cudaMalloc(&p, 256 * 16 * sizeof(unsigned long long)) == cudaSuccess) cudaMemset(p, 0, 256 * 16 * sizeof(unsigned long long));
+    if (e && atoi(e) > 0 && cudaMalloc(&p, 512 * 16 * sizeof(unsigned long long)) == cudaSuccess) cudaMemset(p, 0, 512 * 16 * sizeof(unsigned long long));
     else p = nullptr;
     return p;
   }();
@@ -175,7 +184,7 @@ static unsigned long long* attn_stats_buffer() {
 extern "C" int peft_debug_attn_stats(unsigned long long* host_out, int n_ctas) {
   unsigned long long* buf = attn_stats_buffer();
   PEFT_REQUIRE(buf != nullptr, "peft_debug_attn_stats: set PEFT_ATTN_STATS=1 before the first attention call");
-  PEFT_REQUIRE(host_out && n_ctas > 0 && n_ctas <= 256, "peft_debug_attn_stats: bad arguments");
+  PEFT_REQUIRE(host_out && n_ctas > 0 && n_ctas <= 512, "peft_debug_attn_stats: bad arguments");
   PEFT_CUDA_CHECK(cudaDeviceSynchronize());
   PEFT_CUDA_CHECK(cudaMemcpy(host_out, buf, (size_t)n_ctas * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return 0;
@@ -199,7 +208,7 @@ static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long
     configured.done();
   }
   Attn2Params p{};
-  p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
+  p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale; p.prefetch = attn_prefetch();
   p.stats = attn_stats_buffer();
   const int grid = B * H < sm_count() ? B * H : sm_count();
   (void)launch_pdl(PDL_ATTN, kern, dim3(grid), dim3(kA2Threads), C::kSmemBytes, s, tq, tkv, to, p);
@@ -257,11 +266,47 @@ static int launch_attn2_bwd(const void* qkv, long long ldqkv, const void* o, lon
     configured.done();
   }
   Attn2Params p{};
-  p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale;
+  p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale; p.prefetch = attn_prefetch();
   const int grid = B * H < sm_count() ? B * H : sm_count();
   (void)launch_pdl(PDL_ATTN, kdq, dim3(grid), dim3(kA2Threads), C::kDqSmemBytes, s, t128, tchunk, tdo128, to128, tout, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
   (void)launch_pdl(PDL_ATTN, kdkv, dim3(grid), dim3(kA2Threads), C::kDkvSmemBytes, s, t128, tchunk, tdochunk, tout, p);
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
+  return 0;
+}
+
+// software-pipelined backward (attention3_bwd_sm100.cuh)
+template <int NKT>
+static int launch_attn3_bwd(const void* qkv, long long ldqkv, const void* o, long long ldo, const void* d_o, long long lddo,
+                            const float* lse2, float* delta, void* dqkv, long long lddqkv, int B, int H, int L, float scale,
+                            cudaStream_t s) {
+  using C = Attn3Cfg<NKT>;
+  const unsigned long long D = 64ull * H;
+  CUtensorMap t128, thead, tdo128, tdohead, to128;
+  int rc;
+  if ((rc = make_tmap_bf16_3d(&t128, qkv, B, L, 3 * D, ldqkv, 128))) return rc;
+  if ((rc = make_tmap_bf16_3d(&thead, qkv, B, L, 3 * D, ldqkv, C::kBox))) return rc;
+  if ((rc = make_tmap_bf16_3d(&tdo128, d_o, B, L, D, lddo, 128))) return rc;
+  if ((rc = make_tmap_bf16_3d(&tdohead, d_o, B, L, D, lddo, C::kBox))) return rc;
+  if ((rc = make_tmap_bf16_3d(&to128, o, B, L, D, ldo, 128))) return rc;
+  auto kdq = attn3_bwd_dq_kernel<NKT>;
+  auto kdkv = attn3_bwd_dkv_kernel<NKT>;
+  static DeviceOnce configured;
+  if (configured.needs()) {
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kdq, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kDqSmemBytes));
+    PEFT_CUDA_CHECK(cudaFuncSetAttribute(kdkv, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kDkvSmemBytes));
+    configured.done();
+  }
+  Attn3Params p{};
+  p.lse2 = lse2; p.delta_in = delta; p.delta_out = delta; p.dqkv = (__nv_bfloat16*)dqkv; p.lddqkv = lddqkv;
+  p.B = B; p.H = H; p.L = L; p.scale = scale; p.prefetch = attn_prefetch();
+  p.stats = attn_stats_buffer();
+  static const int a3_flags = [] { const char* e = getenv("PEFT_ATTN3_FLAGS"); return e ? atoi(e) : 0; }();
+  p.flags = a3_flags;
+  const int grid = B * H < sm_count() ? B * H : sm_count();
+  (void)launch_pdl(PDL_ATTN, kdq, dim3(grid), dim3(kA2Threads), C::kDqSmemBytes, s, t128, thead, tdo128, to128, p);
+  PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
+  (void)launch_pdl(PDL_ATTN, kdkv, dim3(grid), dim3(kA2Threads), C::kDkvSmemBytes, s, t128, thead, tdohead, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);
   return 0;
 }
@@ -279,6 +324,16 @@ extern "C" int peft_attention_bwd(const void* qkv, long long ldqkv, const void* 
   PEFT_REQUIRE(o && d_o && lse2 && delta && dqkv, "peft_attention_bwd: null operand");
   PEFT_REQUIRE(ldo % 8 == 0 && lddo % 8 == 0 && lddqkv % 8 == 0 && aligned16(o) && aligned16(d_o) && aligned16(dqkv),
                "peft_attention_bwd: operands must be 16-byte aligned with pitch % 8 == 0");
+  // pipelined backward: measured faster for one-tile heads (L <= 64: 98 vs 106 us at B = 256, H = 12, L = 50) and slower for the
+  // longer ones (L = 197: 432 vs 331 us) — there both variants are bound by the delivery rate of the head-strided operand rows,
+  // not by the tensor / exp overlap it adds — so automatic mode takes it for L <= 64 only; algo 3 forces it
+  const int algo = attn_algo().load();
+  if ((algo == 3 || (algo == 0 && L <= 64)) && L <= 272) {
+    cudaStream_t s2 = reinterpret_cast<cudaStream_t>(stream);
+    if (L <= 64) return launch_attn3_bwd<64>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
+    if (L <= 208) return launch_attn3_bwd<208>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
+    return launch_attn3_bwd<272>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
+  }
   if (attn_algo().load() != 1 && L <= 288) {
     cudaStream_t s2 = reinterpret_cast<cudaStream_t>(stream);
     if (L <= 64) return launch_attn2_bwd<64, 1>(qkv, ldqkv, o, ldo, d_o, lddo, lse2, delta, dqkv, lddqkv, B, H, L, scale, s2);
@@ -351,5 +406,22 @@ extern "C" int peft_tn_reduce(const void* x, long long ldx, int I, const void* y
   else if (I == 32) (void)launch_pdl(PDL_REDUCE, tn_reduce_kernel<2>, dim3(grid), dim3(kRedThreads), 0, s, X, ldx, Y, ldy, out, ldout, M, rows);
   else (void)launch_pdl(PDL_REDUCE, tn_reduce_kernel<4>, dim3(grid), dim3(kRedThreads), 0, s, X, ldx, Y, ldy, out, ldout, M, rows);
   PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+// diagnostics: cycles of a chain of `reps` tcgen05.mma (M = 128, N = n, K = 16) rotating over `nacc` accumulators; out[0] = issue
+// cycles, out[1] = cycles until the last one has completed (host memory, 2 values)
+extern "C" int peft_debug_mma_probe(int n, int nacc, int ts, int reps, unsigned long long* host_out) {
+  PEFT_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0 && nacc >= 1 && nacc * n <= 256 && reps > 0 && host_out, "peft_debug_mma_probe: bad arguments");
+  unsigned long long* d = nullptr;
+  PEFT_CUDA_CHECK(cudaMalloc(&d, 16));
+  const int smem = 2 * 32768 + 1024;
+  PEFT_REQUIRE(nacc == 1 || nacc == 2 || nacc == 4, "peft_debug_mma_probe: nacc must be 1, 2 or 4");
+  auto kern = nacc == 1 ? mma_probe_kernel<1> : (nacc == 2 ? mma_probe_kernel<2> : mma_probe_kernel<4>);
+  PEFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  kern<<<1, 128, smem>>>(n, ts, reps, d);
+  PEFT_CUDA_CHECK(cudaDeviceSynchronize());
+  PEFT_CUDA_CHECK(cudaMemcpy(host_out, d, 16, cudaMemcpyDeviceToHost));
+  cudaFree(d);
   return 0;
 }

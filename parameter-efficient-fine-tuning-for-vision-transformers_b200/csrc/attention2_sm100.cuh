@@ -26,6 +26,15 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* t
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// L2 prefetch of a 3-D box (no shared memory, no barrier): issued tiles ahead of the real load, which then completes from L2.
+// Built to test whether the attention kernels (2.5 - 2.8 TB/s of operand traffic in every one of them) are bound by the latency
+// of their one or two operand boxes in flight per SM.  They are not: measured no gain (abi_ops.cu: attn_prefetch), so it stays
+// a switch (PEFT_ATTN_PREFETCH=1).
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(c0),
+               "r"(c1), "r"(c2)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* tm, const void* smem_src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(tm)),
@@ -116,6 +125,7 @@ struct Attn2Params {
   int B, H, L;
   float scale;
   unsigned long long* stats;   // diagnostics (PEFT_ATTN_STATS=1): cycles per phase of the first softmax warp of each CTA
+  int prefetch;                // L2 prefetch of the operand boxes ahead of their loads (env PEFT_ATTN_PREFETCH=1; off by default: measured no gain)
 };
 
 
@@ -240,10 +250,31 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
+    // L2 prefetch of the operands of tile g2 (the head's K / V with its first tile)
+    auto prefetch = [&](int g2) {
+      if (g2 >= G || !p.prefetch) return;
+      const int hl2 = g2 / TQ, t2 = g2 % TQ;
+      const int bh2 = (int)blockIdx.x + hl2 * (int)gridDim.x;
+      const int b2 = bh2 / H, h2 = bh2 % H;
+      if (ptx::elect_one()) {
+        if (t2 == 0) {
+#pragma unroll
+          for (int r = 0; r < NK; r += C::kKVBox) {
+            ptx::tma_prefetch_3d(&tmap_kv, D + h2 * 64, r, b2);
+            ptx::tma_prefetch_3d(&tmap_kv, 2 * D + h2 * 64, r, b2);
+          }
+        }
+        ptx::tma_prefetch_3d(&tmap_q, h2 * 64, t2 * 128, b2);
+      }
+      __syncwarp();
+    };
+    prefetch(2);
+    prefetch(3);
     for (int g = 0; g < G; ++g) {
       const int hl = g / TQ, t = g % TQ;
       const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
       const int b = bh / H, h = bh % H;
+      prefetch(g + 4);
       if (t == 0) {
         const int kvb = hl & 1;
         ptx::mbar_wait(&kv_empty[kvb], ((hl >> 1) & 1) ^ 1);

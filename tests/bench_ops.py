@@ -36,7 +36,7 @@ def bench_attn(B=256, H=12, L=197):
     delta = torch.empty(B * H * L, device="cuda")
     scale = 64 ** -0.5
     flops_f = 4.0 * B * H * L * L * 64
-    for algo in (1, 2):
+    for algo in (2, 3):          # 1 = mma.sync kernels, 2 = tcgen05 with the unpipelined backward, 3 = pipelined backward (default)
         _lib.check(_lib.load().peft_set_attention_algo(algo))
         tf = timeit(lambda: ops.attention_fwd(qkv, o, lse2, B, H, L, scale))
         tb = timeit(lambda: ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, scale))
@@ -321,6 +321,45 @@ if __name__ == "__main__":
             names = ["wait S", "max pass", "exp pass", "wait O", "epilogue"]
             print(f"attn fwd B={B} H={H} L={L}: {t:.1f} us; softmax warp total {tot:.0f} clk per CTA ({B * H / 148:.1f} heads): " +
                   ", ".join(f"{n} {100 * float(v[:, :, i].mean() / tot):.1f}%" for i, n in enumerate(names)), flush=True)
+    if what == "attn_bwd_stats":   # PEFT_ATTN_STATS=1: cycle counters of the pipelined backward (attention3_bwd_sm100.cuh)
+        import ctypes
+        for (B, H, L) in ((256, 12, 197), (128, 16, 257), (256, 12, 50)):
+            D = H * 64
+            qkv = torch.randn(B * L, 3 * D, device="cuda").to(torch.bfloat16)
+            o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+            d_o = torch.randn(B * L, D, device="cuda").to(torch.bfloat16)
+            dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+            lse2 = torch.empty(B * H * L, device="cuda")
+            delta = torch.empty(B * H * L, device="cuda")
+            ops.attention_fwd(qkv, o, lse2, B, H, L, 0.125)
+            t = timeit(lambda: ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125), iters=5, warm=2)
+            buf = (ctypes.c_ulonglong * (512 * 16))()
+            _lib.check(_lib.load().peft_debug_attn_stats(buf, 512))
+            v = torch.tensor(list(buf), dtype=torch.float64).view(2, 256, 16)[:, :148]
+            tiles = B * H * ((L + 127) // 128) / 148
+            print(f"attn bwd B={B} H={H} L={L}: {t:.1f} us both kernels, {tiles:.1f} tiles per CTA", flush=True)
+            for k, nm in enumerate(("dQ ", "dKV")):
+                m = v[k].mean(0)
+                print(f"  {nm} MMA warp: total {m[0]:.0f} clk = {m[0] / tiles:.0f} per tile; in issue_ss (operand waits) {100 * m[1] / m[0]:.1f}%, "
+                      f"wait dS {100 * m[2] / m[0]:.1f}%, wait accumulator free {100 * m[3] / m[0]:.1f}%")
+                for w in range(2):
+                    c = m[4 + 6 * w:10 + 6 * w]
+                    print(f"  {nm} warpgroup {w}: total {c[0]:.0f} clk; delta/lse {100 * c[1] / c[0]:.1f}%, wait S/dP {100 * c[2] / c[0]:.1f}%, "
+                          f"math {100 * c[3] / c[0]:.1f}%, epilogue {100 * c[4] / c[0]:.1f}%")
+    if what == "mma_probe":        # dependent-accumulate latency of tcgen05.mma: clk per instruction vs number of accumulators
+        import ctypes
+        buf = (ctypes.c_ulonglong * 2)()
+        for ts in (0, 1):
+            for n in (16, 64, 128, 208, 256):
+                row = []
+                for nacc in (1, 2, 4):
+                    if nacc * n > 256:
+                        continue
+                    _lib.check(_lib.load().peft_debug_mma_probe(n, nacc, ts, 256, buf))
+                    row.append(f"nacc={nacc}: {buf[1] / 256:6.1f} clk/mma (issue {buf[0] / 256:5.1f})")
+                print(f"{'TS' if ts else 'SS'} M=128 N={n:3d} K=16 (floor {n / 2:5.1f} clk): " + "; ".join(row), flush=True)
+    if what == "gemm_once":        # one launch of each of the 8 products of a C3 layer: the command ncu --set full captures
+        bench_gemm(iters=1, warm=0)   # (tools/ncu_traffic.py -> profiles/gemm_traffic.json)
     if what == "fixed":
         bench_fixed_costs()
     if what == "gemm_probe":

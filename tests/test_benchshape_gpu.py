@@ -196,6 +196,42 @@ def test_attention_many_tiles(ops, lib, B, H, L):
             assert rel(dqkv[rows, i * D:(i + 1) * D], ref_d[:, i * D:(i + 1) * D]) < 2e-2, (nm, b0_)
 
 
+@pytest.mark.parametrize("B,H,L", [(26, 12, 197), (3, 12, 197), (10, 16, 257), (20, 12, 50), (256, 12, 50), (2, 12, 100), (30, 12, 100)])
+def test_attention_pipelined_backward(ops, lib, B, H, L):
+    """The software-pipelined backward (attention3_bwd_sm100.cuh, peft_set_attention_algo(3); automatic for L <= 64) against fp32
+    torch at every instantiation (<64>, <208>, <272>), with one and with many heads per persistent CTA — (256, 12, 50) walks 21
+    one-item heads per CTA (the case that needs the early tile-slot release to be deadlock-free), L = 100 has one tile of four
+    items per head."""
+    D = H * 64
+    qkv = _r(B * L, 3 * D, scale=1.0, dtype=torch.bfloat16, seed=3)
+    o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * L, device="cuda")
+    scale = 64 ** -0.5
+    ops.attention_fwd(qkv, o, lse2, B, H, L, scale)
+    d_o = _r(B * L, D, dtype=torch.bfloat16, seed=4)
+    dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+    delta = torch.empty(B * H * L, device="cuda")
+    lib.check(lib.load().peft_set_attention_algo(3))
+    try:
+        for _ in range(2):          # twice: barriers, TMEM and the per-head lse / delta copies start clean on every launch
+            ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, scale)
+        torch.cuda.synchronize()
+    finally:
+        lib.load().peft_set_attention_algo(0)
+    step = 32
+    for b0_ in range(0, B, step):
+        b1_ = min(B, b0_ + step)
+        nb = b1_ - b0_
+        rows = slice(b0_ * L, b1_ * L)
+        t = qkv[rows].float().reshape(nb, L, 3, H, 64).permute(2, 0, 3, 1, 4).clone().requires_grad_(True)
+        s = (t[0] @ t[1].transpose(-2, -1)) * scale
+        ref = (F.softmax(s, dim=-1) @ t[2]).transpose(1, 2).reshape(nb * L, D)
+        ref.backward(d_o[rows].float())
+        ref_d = t.grad.permute(1, 3, 0, 2, 4).reshape(nb * L, 3 * D)
+        for i, nm in enumerate("qkv"):
+            assert rel(dqkv[rows, i * D:(i + 1) * D], ref_d[:, i * D:(i + 1) * D]) < 2e-2, (nm, b0_)
+
+
 # ---------------------------------------------------------------------------------------------------------------- whole tower
 def _build(cfg, sd):
     if cfg.dialect == "timm":
