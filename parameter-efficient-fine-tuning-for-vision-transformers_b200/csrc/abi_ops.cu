@@ -393,7 +393,12 @@ extern "C" int peft_tn_reduce(const void* x, long long ldx, int I, const void* y
   PEFT_REQUIRE(M > 0 && (I == 16 || I == 32 || I == 64) && J > 0 && J % 64 == 0, "peft_tn_reduce: need I in {16,32,64}, J %% 64 == 0 (I=%d J=%d)", I, J);
   PEFT_REQUIRE(aligned16(x) && aligned16(y) && ldx % 8 == 0 && ldy % 8 == 0, "peft_tn_reduce: operands must be 16-byte aligned with pitch %% 8 == 0");
   const int jt = J / 64;
-  int target_ctas = sm_count() * 2;      // every CTA ends in I x 64 global atomics: few, long CTAs (>= 4 stages of 64 rows each)
+  // every CTA ends in I x 64 global atomics: few, long CTAs (>= 4 stages of 64 rows each); long reductions take four CTAs per
+  // SM so that enough cp.async stages are in flight to cover the DRAM latency
+  // (measured r02 at M = 50 432, J = 2304 / 768: x3 65.9 / 27.8 us, x4 68.4 / 25.1, x6 61.7 / 29.0, x8 65.8 / 30.3; two-stage ring
+  // with x2, the round-1 form: 103.5 / 41.9 us)
+  static const int red_mult = [] { const char* e = getenv("PEFT_RED_CTAS"); return e ? atoi(e) : 6; }();
+  int target_ctas = sm_count() * (M >= 16384 ? red_mult : 2);
   int my = (target_ctas + jt - 1) / jt;
   int rows = (M + my - 1) / my;
   rows = ((rows + 63) / 64) * 64;

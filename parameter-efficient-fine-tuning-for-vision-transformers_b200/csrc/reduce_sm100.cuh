@@ -11,6 +11,10 @@ namespace peft {
 
 constexpr int kRedThreads = 128;
 constexpr int kRedRowsPerStage = 64;   // token rows per pipeline stage (16 per warp)
+// cp.async ring: three (I = 64: two) stages in flight while one is multiplied — what fits 48 KB of static shared memory.  r02:
+// with a two-stage ring and two CTAs per SM only ~24 KB per SM were in flight and the kernel ran at the latency of its loads
+// (2.3 TB/s at M = 50 432; 3.6 - 3.8 TB/s with the deeper ring and 4 - 6 CTAs per SM).
+template <int IT> struct RedStages { static constexpr int value = IT <= 2 ? 4 : 3; };
 
 __device__ __forceinline__ uint32_t sw_off_x(int row, int chunk, int chunks_per_row) {
   // rows of 32/64/128 bytes: XOR the 16-byte chunk index so 8 consecutive rows hit 8 distinct bank groups
@@ -27,9 +31,11 @@ tn_reduce_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const __nv_
   constexpr int XCH = I / 8;                       // 16-byte chunks per X row
   constexpr int kXBytes = kRedRowsPerStage * I * 2;
   constexpr int kYBytes = kRedRowsPerStage * 128;
-  __shared__ __align__(128) uint8_t sX[2][kXBytes];
-  __shared__ __align__(128) uint8_t sY[2][kYBytes];
-  __shared__ float sRed[I * 64];
+  constexpr int kRedStages = RedStages<IT>::value;
+  __shared__ __align__(128) uint8_t sX[kRedStages][kXBytes];
+  __shared__ __align__(128) uint8_t sY[kRedStages][kYBytes];
+  static_assert(I * 64 * 4 <= kRedStages * kYBytes, "the combine buffer aliases the Y stages");
+  float* sRed = reinterpret_cast<float*>(&sY[0][0]);      // used after the main loop only (its last barrier frees the stages)
 
   pdl_trigger();                     // PDL (common.cuh)
   pdl_wait();
@@ -40,7 +46,8 @@ tn_reduce_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const __nv_
   if (m_end > M) m_end = M;
   const int nstages = (int)((m_end - m_begin + kRedRowsPerStage - 1) / kRedRowsPerStage);
 
-  auto issue = [&](int st, int buf) {
+  auto issue = [&](int st, int buf) {       // always commits a group (an empty one past the end) so the wait count is uniform
+    if (st >= nstages) { ptx::cp_async_commit(); return; }
     const long long r0 = m_begin + (long long)st * kRedRowsPerStage;
     for (int idx = threadIdx.x; idx < kRedRowsPerStage * XCH; idx += kRedThreads) {
       const int r = idx / XCH, c = idx % XCH;
@@ -61,15 +68,12 @@ tn_reduce_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const __nv_
 #pragma unroll
     for (int n = 0; n < 8; ++n) acc[a][n][0] = acc[a][n][1] = acc[a][n][2] = acc[a][n][3] = 0.f;
 
-  if (nstages > 0) issue(0, 0);
+#pragma unroll
+  for (int st = 0; st < kRedStages - 1; ++st) issue(st, st);
   for (int st = 0; st < nstages; ++st) {
-    const int buf = st & 1;
-    if (st + 1 < nstages) {
-      issue(st + 1, buf ^ 1);
-      ptx::cp_async_wait<1>();
-    } else {
-      ptx::cp_async_wait<0>();
-    }
+    const int buf = st % kRedStages;
+    issue(st + kRedStages - 1, (st + kRedStages - 1) % kRedStages);   // its buffer was released by the barrier that ended stage st - 1
+    ptx::cp_async_wait<kRedStages - 1>();                             // all but the newest kRedStages - 1 groups: stage st has landed
     __syncthreads();
     const uint32_t uX = ptx::smem_u32(sX[buf]), uY = ptx::smem_u32(sY[buf]);
     const int k0 = warp * 16;  // this warp's 16 token rows of the stage
