@@ -68,7 +68,9 @@ int peft_debug_attn_stats(unsigned long long* host_out, int n_ctas);
  * `nacc` accumulators (nacc = 1: a fully dependent chain); host_out[0] = cycles to issue them, host_out[1] = cycles until the
  * last one has completed.  Measures the dependent-accumulate latency that paces the attention kernels. */
 int peft_debug_mma_probe(int n, int nacc, int ts, int reps, unsigned long long* host_out);
-/* same for the attention kernels: 0 = automatic (tcgen05/TMEM kernels for L <= 272), 1 = mma.sync kernels, 2 = tcgen05 */
+/* same for the attention kernels: 0 = automatic (tcgen05/TMEM kernels for L <= 272; backward: the software-pipelined pair of
+ * attention3_bwd_sm100.cuh for L <= 64, the attention2 pair above), 1 = mma.sync kernels, 2 = tcgen05 with the attention2 backward
+ * for every L, 3 = tcgen05 with the pipelined backward for every L <= 272.  Env PEFT_ATTN_ALGO sets the initial value. */
 int peft_set_attention_algo(int algo);
 
 /* C[M,N] = A[M,K] * B[N,K]^T with fused epilogue, bf16 operands, fp32 accumulate in TMEM (tcgen05 + TMA).

@@ -360,6 +360,25 @@ if __name__ == "__main__":
                 print(f"{'TS' if ts else 'SS'} M=128 N={n:3d} K=16 (floor {n / 2:5.1f} clk): " + "; ".join(row), flush=True)
     if what == "gemm_once":        # one launch of each of the 8 products of a C3 layer: the command ncu --set full captures
         bench_gemm(iters=1, warm=0)   # (tools/ncu_traffic.py -> profiles/gemm_traffic.json)
+    if what == "other_once":       # one launch of the non-GEMM kernels of a C3 layer (ncu --set full target)
+        B, H, L, D = 256, 12, 197, 768
+        qkv = torch.randn(B * L, 3 * D, device="cuda").to(torch.bfloat16)
+        o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+        d_o = torch.randn(B * L, D, device="cuda").to(torch.bfloat16)
+        dqkv = torch.zeros(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+        lse2 = torch.empty(B * H * L, device="cuda")
+        delta = torch.empty(B * H * L, device="cuda")
+        ops.attention_fwd(qkv, o, lse2, B, H, L, 0.125)
+        ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)
+        _lib.check(_lib.load().peft_set_attention_algo(3))
+        ops.attention_bwd(qkv, o, d_o, lse2, delta, dqkv, B, H, L, 0.125)
+        _lib.load().peft_set_attention_algo(0)
+        wide = torch.randn(B * L, 800, device="cuda").to(torch.bfloat16)
+        out = torch.zeros(32, 2304, device="cuda")
+        ops.tn_reduce(wide[:, 768:800], dqkv, out)
+        out2 = torch.zeros(32, 768, device="cuda")
+        ops.tn_reduce(dqkv[:, :32], wide[:, :768], out2)
+        torch.cuda.synchronize()
     if what == "fixed":
         bench_fixed_costs()
     if what == "gemm_probe":

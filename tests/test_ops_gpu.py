@@ -186,6 +186,32 @@ def test_attention_fwd_bwd(ops, B, H, L):
         assert rel(dqkv[:, i * D:(i + 1) * D], ref_d[:, i * D:(i + 1) * D]) < 2e-2, nm
 
 
+@pytest.mark.parametrize("B,H,L", [(3, 12, 197), (20, 12, 197), (2, 16, 257), (4, 12, 50)])
+@pytest.mark.parametrize("pattern", ["late_keys", "ramp"])
+def test_attention_fwd_provisional_max(ops, B, H, L, pattern):
+    """The forward takes its softmax maximum provisionally from the first 32 scores of a row and raises it (rescaling the P
+    already written) when a later chunk exceeds it by more than 2^24: scores built so that this happens in many rows — late keys
+    30x larger than the first 32 / key norms ramping up along the sequence — against fp32 torch."""
+    D = H * 64
+    t = _r(B * L, 3 * D, scale=1.0, dtype=torch.float32, seed=5).reshape(B, L, 3, H, 64)
+    if pattern == "late_keys":
+        t[:, 40:, 1] *= 30.0
+    else:
+        t[:, :, 1] *= torch.linspace(0.5, 40.0, L, device="cuda").reshape(1, L, 1, 1)
+    qkv = t.reshape(B * L, 3 * D).to(torch.bfloat16)
+    o = torch.empty(B * L, D, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * L, device="cuda")
+    scale = 64 ** -0.5
+    ops.attention_fwd(qkv, o, lse2, B, H, L, scale)
+    x = qkv.float().reshape(B, L, 3, H, 64).permute(2, 0, 3, 1, 4)
+    s_ = (x[0] @ x[1].transpose(-2, -1)) * scale
+    ref = (F.softmax(s_, dim=-1) @ x[2]).transpose(1, 2).reshape(B * L, D)
+    assert torch.isfinite(o.float()).all() and torch.isfinite(lse2).all()
+    assert rel(o, ref) < 1e-2
+    ref_lse2 = (torch.logsumexp(s_, dim=-1) * math.log2(math.e)).reshape(-1)
+    assert float(((lse2 - ref_lse2).abs() / (1.0 + ref_lse2.abs())).max()) < 1e-2
+
+
 @pytest.mark.parametrize("M,I,J", [(1000, 32, 768), (5000, 16, 2304), (333, 64, 768), (64, 32, 64), (50432, 32, 768)])
 def test_tn_reduce(ops, M, I, J):
     wide = _r(M, 800 if I <= 32 else 832, dtype=torch.bfloat16, seed=1)
