@@ -99,7 +99,9 @@ static void decide_streamk(GemmParams& p, int M, int N, int K) {
   if (C > 128 || T > (1 << 24)) return;
   const long long waves = (T + C - 1) / C;
   const double eff = (double)T / (double)(waves * C);
-  if (mode == 1 && (KB < 16 || eff >= 0.92)) return;
+  // the 16 k-block gate re-measured at per-GPU batch 32 (C3 step, graph replay): gate 16 -> 4.91 ms, 12 -> 5.00 ms, 8 -> 5.08 ms
+  static const int min_kb = [] { const char* e = getenv("PEFT_GEMM_SK_MINKB"); return e ? atoi(e) : 16; }();
+  if (mode == 1 && (KB < min_kb || eff >= 0.92)) return;
   if (mode == 2 && KB < 2) return;
   const long long dp = T >= C ? (T / C - 1) * C : 0;
   if ((T - dp) * KB < 4LL * C) return;          // every cluster must get a non-empty k-block range
