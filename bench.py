@@ -312,7 +312,8 @@ def main():
     head = synth.make_head(cfg)
     model.layers[0].load_state_dict({"weight": head["layers.0.weight"], "bias": head["layers.0.bias"]})
     model.train()
-    trainable = [p for p in model.parameters() if p.requires_grad]
+    from peft_b200.dist import kind_major
+    trainable = kind_major([(n, p) for n, p in model.named_parameters() if p.requires_grad])   # per-layer tensors adjacent: see kind_major
     if args.fused_sgd:
         bucket = FusedSGDBucket(trainable, lr=1e-3, momentum=0.9, weight_decay=0.0)
         opt = None

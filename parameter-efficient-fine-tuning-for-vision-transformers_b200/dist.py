@@ -14,6 +14,25 @@ import torch
 import torch.distributed as dist
 
 
+def kind_major(named_params):
+    """[(name, parameter)] -> parameters ordered so that the same tensor of consecutive layers is adjacent in the bucket
+    (`blocks.0.attn.W_left1, blocks.1.attn.W_left1, ..., blocks.0.attn.W_right1, ...`), kinds in order of first appearance.
+
+    With this order a bucket (and, for FusedSGDBucket, the flat parameter buffer) holds `[depth, ...]` of every per-layer adapter
+    tensor contiguously, which lets `timm_vit.stack_params` hand the tower a zero-copy stacked VIEW in forward and add the stacked
+    gradient to the bucket with ONE kernel in backward, instead of a cat kernel + one AccumulateGrad add per layer and tensor
+    (48 of the ~150 small launches of a KAdaptation step).  Any other order stays correct: stack_params falls back to torch.stack."""
+    import re
+    keyed, first = [], {}
+    for idx, (n, q) in enumerate(named_params):
+        m = re.search(r"\.(\d+)\.", n)
+        kind = n[:m.start()] + ".#." + n[m.end():] if m else n
+        first.setdefault(kind, idx)
+        keyed.append((first[kind], int(m.group(1)) if m else 0, idx, q))
+    keyed.sort(key=lambda k: k[:3])
+    return [k[3] for k in keyed]
+
+
 class GradBucket:
     def __init__(self, params, process_group=None):
         self.params = [p for p in params if p.requires_grad]

@@ -237,6 +237,52 @@ def lowrank_factors_kron(rule, w_left, w_right):
     return Dn, UpT
 
 
+class _StackParams(torch.autograd.Function):
+    """Zero-copy torch.stack of parameters that already lie stacked in memory (see stack_params)."""
+
+    @staticmethod
+    def forward(ctx, pview, gview, *params):
+        ctx.gview = gview
+        ctx.n = len(params)
+        return pview.detach()
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.gview.add_(g)                      # one kernel for all layers; the parameters' own AccumulateGrad nodes get nothing
+        return (None, None) + (None,) * ctx.n
+
+
+STACK_FAST_HITS = 0      # how often stack_params took the zero-copy path (tests)
+
+
+def stack_params(params):
+    """torch.stack(params) — as a VIEW with a fused gradient accumulation when the parameters (and their .grad tensors) are
+    consecutive slices of one buffer each, which is how dist.FusedSGDBucket / GradBucket lay them out under dist.kind_major.
+    Forward then launches nothing and backward adds the stacked gradient to the bucket with one kernel; the result is identical
+    to torch.stack + per-parameter accumulation.  Falls back to torch.stack whenever any condition does not hold."""
+    global STACK_FAST_HITS
+    p0 = params[0]
+    n, k = len(params), p0.numel()
+    ok = n > 1 and p0.is_cuda and p0.dtype == torch.float32 and torch.is_grad_enabled()
+    if ok:
+        d0, st = p0.data_ptr(), p0.untyped_storage().data_ptr()
+        for i, q in enumerate(params):
+            g = q.grad
+            if (not q.requires_grad or g is None or q.shape != p0.shape or not q.is_contiguous() or not g.is_contiguous()
+                    or g.dtype != torch.float32 or q.data_ptr() != d0 + 4 * k * i or q.untyped_storage().data_ptr() != st
+                    or g.data_ptr() != params[0].grad.data_ptr() + 4 * k * i
+                    or g.untyped_storage().data_ptr() != params[0].grad.untyped_storage().data_ptr()):
+                ok = False
+                break
+    if not ok:
+        return torch.stack(list(params))
+    shape, strides = (n,) + tuple(p0.shape), (k,) + tuple(p0.stride())
+    pview = torch.as_strided(p0.detach(), shape, strides)
+    gview = torch.as_strided(p0.grad, shape, strides)
+    STACK_FAST_HITS += 1
+    return _StackParams.apply(pview, gview, *params)
+
+
 def lowrank_operands(attns, kind):
     """Dn [depth, r', D], UpT [depth, r', 3D] from the attention modules' reference-named adapter parameters
     (`phm_rule / W_left{1,2} / W_right{1,2}` or `{q,v}_proj_adapter{1,2}.weight`); shared by both dialects."""
@@ -244,14 +290,14 @@ def lowrank_operands(attns, kind):
         return dense_kron_operands(attns)
     if kind == "kron":
         rule = torch.stack([a.phm_rule for a in attns])
-        dq, uq = lowrank_factors_kron(rule, torch.stack([a.W_left1 for a in attns]), torch.stack([a.W_right1 for a in attns]))
-        dv, uv = lowrank_factors_kron(rule, torch.stack([a.W_left2 for a in attns]), torch.stack([a.W_right2 for a in attns]))
+        dq, uq = lowrank_factors_kron(rule, stack_params([a.W_left1 for a in attns]), stack_params([a.W_right1 for a in attns]))
+        dv, uv = lowrank_factors_kron(rule, stack_params([a.W_left2 for a in attns]), stack_params([a.W_right2 for a in attns]))
     elif kind == "lora":
         s = attns[0].lora_attn_alpha / attns[0].lora_attn_dim
-        dq = torch.stack([a.q_proj_adapter1.weight for a in attns])
-        dv = torch.stack([a.v_proj_adapter1.weight for a in attns])
-        uq = torch.stack([a.q_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
-        uv = torch.stack([a.v_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
+        dq = stack_params([a.q_proj_adapter1.weight for a in attns])
+        dv = stack_params([a.v_proj_adapter1.weight for a in attns])
+        uq = stack_params([a.q_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
+        uv = stack_params([a.v_proj_adapter2.weight for a in attns]).transpose(1, 2) * s
     else:
         return None, None
     z = torch.zeros_like(uq)

@@ -69,3 +69,47 @@ def test_fused_sgd_in_cuda_graph():
     for p, r in zip(ours, ref):
         assert torch.allclose(p, r, rtol=1e-5, atol=1e-6)
     torch.cuda.set_stream(torch.cuda.default_stream())
+
+
+@pytest.mark.parametrize("adapter", ["kron", "lora"])
+def test_stacked_parameter_views_match_per_parameter_accumulation(adapter):
+    """dist.kind_major + timm_vit.stack_params: with the per-layer adapter tensors adjacent in the FusedSGDBucket the tower takes
+    them as zero-copy stacked views and adds their stacked gradient to the bucket with one kernel per tensor kind; the bucket
+    must then hold exactly what torch.stack + one AccumulateGrad per parameter produce, and three training steps must agree."""
+    import torch.nn.functional as F
+    from oracle import synth
+    from oracle.synth import VitCfg
+    from peft_b200 import timm_vit
+    from peft_b200.classifier import Classifier
+    from peft_b200.dist import FusedSGDBucket, kind_major
+    cfg = VitCfg(dialect="timm", adapter=adapter, phm_dim=4, img=64, patch=32, depth=3)
+
+    def build(ordered):
+        sd = synth.make_state_dict(cfg, seed=0, grad_test=True)
+        names = set(synth.trainable_names(cfg, sd))
+        vit = timm_vit.VisionTransformer(img_size=cfg.img, patch_size=cfg.patch, num_classes=10, embed_dim=cfg.width, depth=cfg.depth,
+                                         num_heads=cfg.heads, qkv_bias=True, adapter=cfg.adapter, phm_dim=4, phm_rank=1)
+        vit.load_state_dict(sd, strict=False)
+        model = Classifier(vit, cfg.feat_dim, 10, trainable_filter=lambda n: n in names).cuda()
+        head = synth.make_head(cfg)
+        model.layers[0].load_state_dict({"weight": head["layers.0.weight"], "bias": head["layers.0.bias"]})
+        model.train()
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        params = kind_major(named) if ordered else [p for _, p in named]
+        return model, FusedSGDBucket(params, lr=0.05, momentum=0.9), dict(named)
+
+    batches = [synth.make_batch(cfg, 8, seed_img=300 + i, seed_lbl=400 + i) for i in range(3)]
+    ref_model, ref_bucket, ref_named = build(False)
+    fast_model, fast_bucket, fast_named = build(True)
+    for step, (im, lb) in enumerate(batches):
+        h0 = timm_vit.STACK_FAST_HITS
+        F.cross_entropy(ref_model(im.cuda()), lb.cuda()).backward()
+        assert timm_vit.STACK_FAST_HITS == h0                      # layer-major bucket: plain torch.stack
+        F.cross_entropy(fast_model(im.cuda()), lb.cuda()).backward()
+        assert timm_vit.STACK_FAST_HITS - h0 == 4                  # q / v x down / up factors
+        for n, p in ref_named.items():
+            assert torch.equal(p.grad, fast_named[n].grad), (step, n)
+        ref_bucket.step()
+        fast_bucket.step()
+        for n, p in ref_named.items():
+            assert torch.equal(p, fast_named[n]), (step, n)
