@@ -372,7 +372,8 @@ def lowrank_rank(attn, kind):
 
 
 def bottleneck_operands(blocks, kind):
-    st = torch.stack
+    def st(xs):      # parameters: zero-copy view when they lie stacked in the bucket (stack_params); computed tensors: torch.stack
+        return stack_params(xs) if all(isinstance(x, torch.nn.Parameter) for x in xs) else torch.stack(xs)
     if kind == "houlsby":
         ad = [b.adapter for b in blocks]
         return (st([a.adapter_down[1].weight for a in ad]), st([a.adapter_down[1].bias for a in ad]),
