@@ -208,12 +208,7 @@ static int launch_attn2_fwd(const void* qkv, long long ldqkv, void* o, long long
     configured.done();
   }
   Attn2Params p{};
-  p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale; p.prefetch = attn_prefetch();
-  // single-pass softmax (provisional row maximum, attention2_sm100.cuh): correct (tests/test_ops_gpu.py::
-  // test_attention_fwd_provisional_max passes with it) but measured SLOWER than the two-pass form (94.9 vs 87.3 us at B = 256,
-  // H = 12, L = 197; 212 vs 181 us at L = 257), so it is off unless PEFT_ATTN_SINGLE_PASS=1
-  static const int single_pass = [] { const char* e = getenv("PEFT_ATTN_SINGLE_PASS"); return e ? atoi(e) : 0; }();
-  p.single_pass = single_pass;
+  p.lse2 = lse2; p.B = B; p.H = H; p.L = L; p.scale = scale;
   p.stats = attn_stats_buffer();
   const int grid = B * H < sm_count() ? B * H : sm_count();
   (void)launch_pdl(PDL_ATTN, kern, dim3(grid), dim3(kA2Threads), C::kSmemBytes, s, tq, tkv, to, p);
@@ -271,7 +266,7 @@ static int launch_attn2_bwd(const void* qkv, long long ldqkv, const void* o, lon
     configured.done();
   }
   Attn2Params p{};
-  p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale; p.prefetch = attn_prefetch();
+  p.lse2 = const_cast<float*>(lse2); p.delta_in = delta; p.delta_out = delta; p.B = B; p.H = H; p.L = L; p.scale = scale;
   const int grid = B * H < sm_count() ? B * H : sm_count();
   (void)launch_pdl(PDL_ATTN, kdq, dim3(grid), dim3(kA2Threads), C::kDqSmemBytes, s, t128, tchunk, tdo128, to128, tout, p);
   PEFT_LAUNCH_CHECK_KIND(KIND_ATTN_TC_BWD);

@@ -166,33 +166,10 @@ attn2_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
-    // L2 prefetch of the operands of tile g2 (attention2_sm100.cuh: tma_prefetch_3d), four tiles ahead of their loads
-    auto prefetch = [&](int g2) {
-      if (g2 >= G || !p.prefetch) return;
-      const int hl2 = g2 / TQ, t2 = g2 % TQ;
-      const int bh2 = (int)blockIdx.x + hl2 * (int)gridDim.x;
-      const int b2 = bh2 / H, h2 = bh2 % H;
-      if (ptx::elect_one()) {
-        if (t2 == 0) {
-#pragma unroll
-          for (int r = 0; r < C::kNKT; r += NKC) {
-            ptx::tma_prefetch_3d(&tmap_kv, D + h2 * 64, r, b2);
-            ptx::tma_prefetch_3d(&tmap_kv, 2 * D + h2 * 64, r, b2);
-          }
-        }
-        ptx::tma_prefetch_3d(&tmap_q, h2 * 64, t2 * 128, b2);
-        ptx::tma_prefetch_3d(&tmap_do, h2 * 64, t2 * 128, b2);
-        ptx::tma_prefetch_3d(&tmap_o, h2 * 64, t2 * 128, b2);
-      }
-      __syncwarp();
-    };
-    prefetch(2);
-    prefetch(3);
     for (int g = 0; g < G; ++g) {
       const int hl = g / TQ, t = g % TQ;
       const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
       const int b = bh / H, h = bh % H;
-      prefetch(g + 4);
       if (t == 0) {
         const int kvb = hl % C::kDqKVBufs, n = hl / C::kDqKVBufs;
         ptx::mbar_wait(&kv_empty[kvb], (n & 1) ^ 1);
@@ -438,31 +415,10 @@ attn2_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
-    auto prefetch = [&](int g2) {     // L2 prefetch of tile g2's operands (see the dQ kernel)
-      if (g2 >= G || !p.prefetch) return;
-      const int hl2 = g2 / TK, j2 = g2 % TK;
-      const int bh2 = (int)blockIdx.x + hl2 * (int)gridDim.x;
-      const int b2 = bh2 / H, h2 = bh2 % H;
-      if (ptx::elect_one()) {
-        if (j2 == 0) {
-#pragma unroll
-          for (int r = 0; r < C::kNKT; r += NKC) {
-            ptx::tma_prefetch_3d(&tmap_q, h2 * 64, r, b2);
-            ptx::tma_prefetch_3d(&tmap_do, h2 * 64, r, b2);
-          }
-        }
-        ptx::tma_prefetch_3d(&tmap_kt, D + h2 * 64, j2 * 128, b2);
-        ptx::tma_prefetch_3d(&tmap_kt, 2 * D + h2 * 64, j2 * 128, b2);
-      }
-      __syncwarp();
-    };
-    prefetch(2);
-    prefetch(3);
     for (int g = 0; g < G; ++g) {
       const int hl = g / TK, j = g % TK;
       const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
       const int b = bh / H, h = bh % H;
-      prefetch(g + 4);
       if (j == 0) {
         const int qdb = hl % C::kDkvQDBufs, n = hl / C::kDkvQDBufs;
         ptx::mbar_wait(&qd_empty[qdb], (n & 1) ^ 1);

@@ -26,10 +26,9 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* t
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
-// L2 prefetch of a 3-D box (no shared memory, no barrier): issued tiles ahead of the real load, which then completes from L2.
-// Built to test whether the attention kernels (2.5 - 2.8 TB/s of operand traffic in every one of them) are bound by the latency
-// of their one or two operand boxes in flight per SM.  They are not: measured no gain (abi_ops.cu: attn_prefetch), so it stays
-// a switch (PEFT_ATTN_PREFETCH=1).
+// L2 prefetch of a 3-D box (no shared memory, no barrier).  Built to test whether the attention kernels are bound by the latency
+// of their operand loads: they are not (no gain with every box prefetched four tiles ahead); only the pipelined
+// backward (attention3_bwd_sm100.cuh) still carries the switch (PEFT_ATTN_PREFETCH=1).
 __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(c0),
                "r"(c1), "r"(c2)
@@ -125,8 +124,6 @@ struct Attn2Params {
   int B, H, L;
   float scale;
   unsigned long long* stats;   // diagnostics (PEFT_ATTN_STATS=1): cycles per phase of the first softmax warp of each CTA
-  int single_pass;             // forward: single-pass softmax with a provisional row maximum (env PEFT_ATTN_SINGLE_PASS)
-  int prefetch;                // L2 prefetch of the operand boxes ahead of their loads (env PEFT_ATTN_PREFETCH=1; off by default: measured no gain)
 };
 
 
@@ -191,94 +188,6 @@ struct Attn2Cfg {
   static constexpr int kSmemBytes = 4 * kKVBytes + 2 * kQBytes + 2 * kQBytes + 256 + 1024;
 };
 
-// Single-pass softmax numerator of one query row (TMEM lane): P = exp2(S c - m) with a PROVISIONAL maximum m — the maximum of the
-// row's first 32 scores — instead of a separate max pass over all NK columns, so that S is read from TMEM once, not twice (the
-// hypothesis was that the forward is paced by TMEM reads; measured r02: it is not — this form is 9 % SLOWER than two passes and
-// ncu shows the TMEM pipe 27 % active — so it is kept behind PEFT_ATTN_SINGLE_PASS=1 only).  Softmax is invariant
-// to m; it only has to keep exp2 inside the fp32 / bf16 exponent range, so a later chunk whose maximum exceeds m by more than 24
-// (2^24 still far from overflow) raises m and rescales what has been written so far: the packed P columns [0, c0 / 2) and the
-// running sum are multiplied by 2^(m_old - m_new).  The branch is taken warp-wide (tcgen05.ld / st are warp-collective), lanes that
-// keep their maximum multiply by 1.  On exit: mc = m (log2 domain), sum = row sum; lse2 = mc + log2(sum) as in the two-pass form.
-template <int NK>
-__device__ __forceinline__ void a2_softmax_single_pass(uint32_t tb, int L, float c, float& mc, float& sum) {
-  constexpr int NCHK = (NK + 31) / 32;
-  constexpr bool kTail = (NK % 32) != 0;            // the last chunk is 16 columns wide
-  uint32_t r[2][32];
-  tm_ld32(tb, r[0]);
-  sum = 0.f;
-  mc = 0.f;
-#pragma unroll
-  for (int ci = 0; ci < NCHK; ++ci) {
-    const bool tail = kTail && ci == NCHK - 1;
-    const int W = tail ? 16 : 32;
-    ptx::tmem_ld_wait();
-    if (ci + 1 < NCHK) {
-      if (kTail && ci + 1 == NCHK - 1) tm_ld16(tb + (ci + 1) * 32, r[(ci + 1) & 1]);
-      else tm_ld32(tb + (ci + 1) * 32, r[(ci + 1) & 1]);
-    }
-    const int c0 = ci * 32;
-    const uint32_t* v = r[ci & 1];
-    float cm = -INFINITY;
-    if (c0 + W <= L) {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) if (j < W) cm = fmaxf(cm, __uint_as_float(v[j]));
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) if (j < W) cm = fmaxf(cm, (c0 + j < L) ? __uint_as_float(v[j]) : -INFINITY);
-    }
-    const float cmc = cm * c;
-    if (ci == 0) {
-      mc = cmc;
-    } else {
-      const bool need = cmc > mc + 24.0f;
-      if (__any_sync(0xffffffffu, need)) {          // rare: raise the maximum, rescale what is already in place
-        const float mnew = need ? cmc : mc;
-        const float f = need ? ptx::ex2_approx(mc - mnew) : 1.0f;
-        ptx::tmem_st_wait();
-#pragma unroll 1
-        for (int q = 0; q < (c0 >> 1); q += 16) {
-          uint32_t t[16];
-          tm_ld16(tb + q, t);
-          ptx::tmem_ld_wait();
-#pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            const float2 x = ptx::unpack_bf16x2(t[k]);
-            t[k] = ptx::pack_bf16x2(x.x * f, x.y * f);
-          }
-          tm_st16(tb + q, t);
-        }
-        sum *= f;
-        mc = mnew;
-      }
-    }
-    uint32_t pk[16];
-    if (c0 + W <= L) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        if (j < W) {
-          const float p0 = ptx::ex2_approx(fmaf(__uint_as_float(v[j]), c, -mc));
-          const float p1 = ptx::ex2_approx(fmaf(__uint_as_float(v[j + 1]), c, -mc));
-          sum += p0 + p1;
-          pk[j >> 1] = ptx::pack_bf16x2(p0, p1);
-        }
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        if (j < W) {
-          const float p0 = (c0 + j < L) ? ptx::ex2_approx(fmaf(__uint_as_float(v[j]), c, -mc)) : 0.f;
-          const float p1 = (c0 + j + 1 < L) ? ptx::ex2_approx(fmaf(__uint_as_float(v[j + 1]), c, -mc)) : 0.f;
-          sum += p0 + p1;
-          pk[j >> 1] = ptx::pack_bf16x2(p0, p1);
-        }
-      }
-    }
-    if (tail) tm_st8(tb + (c0 >> 1), pk);
-    else tm_st16(tb + (c0 >> 1), pk);
-  }
-  ptx::tmem_st_wait();
-}
-
 // Forward kernel.  Warpgroup w (warps 4+4w .. 7+4w) owns the tiles g = w, w+2, ...: one thread per query row walks all
 // NK columns (pass 1: row max, pass 2: exp2 / row sum / bf16 P written in place), so no cross-thread reduction exists
 // and the two warpgroups run out of phase, which keeps the MUFU pipe and the tensor core busy at the same time.
@@ -339,31 +248,10 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected lane issues) =====================
-    // L2 prefetch of the operands of tile g2 (the head's K / V with its first tile)
-    auto prefetch = [&](int g2) {
-      if (g2 >= G || !p.prefetch) return;
-      const int hl2 = g2 / TQ, t2 = g2 % TQ;
-      const int bh2 = (int)blockIdx.x + hl2 * (int)gridDim.x;
-      const int b2 = bh2 / H, h2 = bh2 % H;
-      if (ptx::elect_one()) {
-        if (t2 == 0) {
-#pragma unroll
-          for (int r = 0; r < NK; r += C::kKVBox) {
-            ptx::tma_prefetch_3d(&tmap_kv, D + h2 * 64, r, b2);
-            ptx::tma_prefetch_3d(&tmap_kv, 2 * D + h2 * 64, r, b2);
-          }
-        }
-        ptx::tma_prefetch_3d(&tmap_q, h2 * 64, t2 * 128, b2);
-      }
-      __syncwarp();
-    };
-    prefetch(2);
-    prefetch(3);
     for (int g = 0; g < G; ++g) {
       const int hl = g / TQ, t = g % TQ;
       const int bh = (int)blockIdx.x + hl * (int)gridDim.x;
       const int b = bh / H, h = bh % H;
-      prefetch(g + 4);
       if (t == 0) {
         const int kvb = hl & 1;
         ptx::mbar_wait(&kv_empty[kvb], ((hl >> 1) & 1) ^ 1);
@@ -486,9 +374,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       ptx::tcgen05_fence_after();
       if (p.stats) lap(tS);
       float mx = -INFINITY, sum = 0.f, mc = 0.f;
-      if (warp_active && p.single_pass) {
-        a2_softmax_single_pass<NK>(tb, L, c, mc, sum);
-      } else if (warp_active) {
+      if (warp_active) {
         uint32_t r[2][32];
         // ---- pass 1: row maximum
         tm_ld32(tb, r[0]);

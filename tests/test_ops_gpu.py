@@ -189,9 +189,9 @@ def test_attention_fwd_bwd(ops, B, H, L):
 @pytest.mark.parametrize("B,H,L", [(3, 12, 197), (20, 12, 197), (2, 16, 257), (4, 12, 50)])
 @pytest.mark.parametrize("pattern", ["late_keys", "ramp"])
 def test_attention_fwd_provisional_max(ops, B, H, L, pattern):
-    """The forward takes its softmax maximum provisionally from the first 32 scores of a row and raises it (rescaling the P
-    already written) when a later chunk exceeds it by more than 2^24: scores built so that this happens in many rows — late keys
-    30x larger than the first 32 / key norms ramping up along the sequence — against fp32 torch."""
+    """Score ranges that break a softmax whose maximum is not the true row maximum: late keys 30x larger than the first 32 / key
+    norms ramping up along the sequence (written for the single-pass forward with a provisional maximum, DESIGN.md 4.2, which
+    passed it and was removed for being slower; kept as a range test of the two-pass kernel) — against fp32 torch."""
     D = H * 64
     t = _r(B * L, 3 * D, scale=1.0, dtype=torch.float32, seed=5).reshape(B, L, 3, H, 64)
     if pattern == "late_keys":
