@@ -332,6 +332,9 @@ extern "C" int peft_gemm_tn_bf16(const void* x, long long ldx, const void* y, lo
 }
 
 extern "C" int peft_debug_gemm_stats(unsigned long long* host_out, int n_ctas) {
+#if !PEFT_GEMM_DIAG
+  return peft::fail(PEFT_ERR_INVALID, "peft_debug_gemm_stats: the library was built without the in-kernel GEMM diagnostics (make DIAG=1)");
+#endif
   unsigned long long* buf = peft::gemm_stats_buffer();
   PEFT_REQUIRE(buf != nullptr, "peft_debug_gemm_stats: set PEFT_GEMM_STATS=1 before the first GEMM");
   PEFT_REQUIRE(host_out && n_ctas > 0 && n_ctas <= 256, "peft_debug_gemm_stats: bad arguments");

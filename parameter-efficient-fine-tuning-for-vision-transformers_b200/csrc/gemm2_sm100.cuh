@@ -390,6 +390,16 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
                           const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
                           const __grid_constant__ CUtensorMap tmap_aux, const GemmParams p) {
   using T = EpiTraits<EPI>;
+  // Diagnostics (wait-cycle / phase counters, PEFT_GEMM_DBG modes) are compiled in only with -DPEFT_GEMM_DIAG=1 (make DIAG=1): in
+  // the production build the conditions below are compile-time false and the code disappears — a CTA of the fixed-global-batch
+  // split runs one to four tiles, so instruction-cache-cold code is part of its launch floor.
+#if PEFT_GEMM_DIAG
+  unsigned long long* const dstats = p.stats;
+  const int ddbg = p.dbg;
+#else
+  constexpr unsigned long long* dstats = nullptr;
+  constexpr int ddbg = 0;
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* tiles = smem;
@@ -457,10 +467,10 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     int mn, kb0, kb1, kind;
     while (sched.next(mn, kb0, kb1, kind)) {
       const int mp = mn / num_n, n_blk = mn % num_n;
-      const int row_a = (p.dbg & 2) ? (int)cta_rank * kBM : mp * 2 * kBM + (int)cta_rank * kBM;
-      const int row_b = (p.dbg & 2) ? (int)cta_rank * (kG2BN / 2) : n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
+      const int row_a = (ddbg & 2) ? (int)cta_rank * kBM : mp * 2 * kBM + (int)cta_rank * kBM;
+      const int row_b = (ddbg & 2) ? (int)cta_rank * (kG2BN / 2) : n_blk * kG2BN + (int)cta_rank * (kG2BN / 2);
       for (int kb = kb0; kb < kb1; ++kb) {
-        if (p.stats) {
+        if (dstats) {
           const long long t0 = clock64();
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           t_wait += clock64() - t0;
@@ -471,9 +481,9 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         const uint32_t sb = sa + kBM * kBK * 2;
         const uint32_t bar = full0 + stage * 8;
         if (ptx::elect_one()) {
-          if (p.dbg & 8) {                   // diagnostic: no operand loads at all (pure MMA + epilogue on stale smem)
+          if (ddbg & 8) {                   // diagnostic: no operand loads at all (pure MMA + epilogue on stale smem)
             if (leader) ptx::mbar_expect_tx(&full_bar[stage], 0);
-          } else if (!TN && (p.dbg & 1)) {   // diagnostic: A operand only (the B slot keeps stale data)
+          } else if (!TN && (ddbg & 1)) {   // diagnostic: A operand only (the B slot keeps stale data)
             if (leader) ptx::mbar_expect_tx(&full_bar[stage], kG2StageBytes);
             ptx::tma_load_2d_2sm_u32(sa, &tmap_a, bar, kb * kBK, row_a);
           } else {
@@ -493,7 +503,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
       }
     }
-    if (p.stats && !(p.dbg & 128) && lane == 0) { p.stats[blockIdx.x * 8 + 0] = t_wait; p.stats[blockIdx.x * 8 + 1] = clock64() - t_begin; }
+    if (dstats && !(ddbg & 128) && lane == 0) { dstats[blockIdx.x * 8 + 0] = t_wait; dstats[blockIdx.x * 8 + 1] = clock64() - t_begin; }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA; one elected lane issues) =====================
     if (leader) {
@@ -512,7 +522,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       TileSched sched(p, num_tiles_mn, num_kb, cluster_id, num_clusters);
       int mn, kb0, kb1, kind;
       while (sched.next(mn, kb0, kb1, kind)) {
-        if (p.stats) {
+        if (dstats) {
           const long long t0 = clock64();
           ptx::mbar_wait_cluster(&tmem_empty_bar[acc], acc_phase ^ 1);
           t_wtmem += clock64() - t0;
@@ -522,7 +532,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         ptx::tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kG2BN);
         for (int kb = kb0; kb < kb1; ++kb) {
-          if (p.stats) {
+          if (dstats) {
             const long long t0 = clock64();
             ptx::mbar_wait_cluster(&full_bar[stage], phase);
             t_wfull += clock64() - t0;
@@ -547,8 +557,8 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
-      if (p.stats && !(p.dbg & 128) && lane == 0) {
-        p.stats[blockIdx.x * 8 + 2] = t_wfull; p.stats[blockIdx.x * 8 + 3] = t_wtmem; p.stats[blockIdx.x * 8 + 4] = clock64() - t_begin;
+      if (dstats && !(ddbg & 128) && lane == 0) {
+        dstats[blockIdx.x * 8 + 2] = t_wfull; dstats[blockIdx.x * 8 + 3] = t_wtmem; dstats[blockIdx.x * 8 + 4] = clock64() - t_begin;
       }
     }
   } else if (warp >= 4) {
@@ -567,7 +577,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     long long t_wacc = 0, t_begin = clock64();
     // diagnostics (PEFT_GEMM_STATS + PEFT_GEMM_DBG bit 7): cycles of epilogue warp 0 per phase — 0 TMEM load, 1 bias / row scale,
     // 2 slot or aux wait (+ aux math), 3 pack + st.shared + fence + store issue, 4 activation math
-    const bool ph = p.stats != nullptr && (p.dbg & 128);
+    const bool ph = dstats != nullptr && (ddbg & 128);
     long long tp[5] = {0, 0, 0, 0, 0}, tc = 0;
     auto tick = [&](int i) { if (ph) { const long long n = clock64(); tp[i] += n - tc; tc = n; } };
     TileSched sched(p, num_tiles_mn, num_kb, cluster_id, num_clusters);
@@ -597,7 +607,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           }
         }
       }
-      if (p.stats) {
+      if (dstats) {
         const long long t0 = clock64();
         ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
         t_wacc += clock64() - t0;
@@ -653,7 +663,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive_cluster(acc ? tmem_empty_remote1 : tmem_empty_remote0);
         }
-        if constexpr (!T::kAux) { if (p.dbg & 4) continue; }   // diagnostic: drain TMEM only
+        if constexpr (!T::kAux) { if (ddbg & 4) continue; }   // diagnostic: drain TMEM only
         if (kind == kSegPartial) {
           // stream-K: raw fp32 accumulator -> this cluster's workspace slot (L2-resident, read back once by the owner)
           float4* ws = sk_slot(cluster_id) + u * (NP / 2) * 32 + lane;
@@ -755,7 +765,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             // the pre-activation store leaves now, so that its shared-memory read drains under the activation math
             ptx::fence_proxy_async();
             __syncwarp();
-            if (lane == 0 && !(p.dbg & 16)) {
+            if (lane == 0 && !(ddbg & 16)) {
               ptx::tma_store_2d(&tmap_out, slot_ptr(0), colu, row0);
               ptx::bulk_commit();
             }
@@ -765,7 +775,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             // (the diagnostic switch sits OUTSIDE the unrolled loop: a branch per pair splits it into 32 basic blocks, and each
             // pair's mul -> fma -> fma -> MUFU -> fma -> pack chain then runs at full latency with nothing to overlap — measured
             // 77 clk per pair per warp, 2.5 k clk per 64 columns, r02 gemm_phases)
-            if (p.dbg & 32) {                                                              // diagnostic: no activation math
+            if (ddbg & 32) {                                                              // diagnostic: no activation math
 #pragma unroll
               for (int j = 0; j < 32; ++j) pk[j] = ptx::pack_bf16x2(v[j].y, v[j].x);
             } else {
@@ -789,7 +799,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          if (p.dbg & 16) {                          // diagnostic: no output stores
+          if (ddbg & 16) {                          // diagnostic: no output stores
           } else if constexpr (T::kDual) {
             ptx::tma_store_2d(&tmap_out2, slot_ptr(1), colu, row0);
           } else if (EPI == EPI_STORE_F32 && ksplit > 1) {
@@ -824,9 +834,9 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       if (acc == 0) acc_phase ^= 1;
     }
     if (lane == 0) ptx::bulk_wait<0>();   // all global writes of this warp are complete before the CTA exits
-    if (p.stats && ew == 0 && lane == 0) {
-      p.stats[blockIdx.x * 8 + 5] = t_wacc; p.stats[blockIdx.x * 8 + 6] = clock64() - t_begin;
-      if (ph) for (int i = 0; i < 5; ++i) p.stats[blockIdx.x * 8 + i] = tp[i];
+    if (dstats && ew == 0 && lane == 0) {
+      dstats[blockIdx.x * 8 + 5] = t_wacc; dstats[blockIdx.x * 8 + 6] = clock64() - t_begin;
+      if (ph) for (int i = 0; i < 5; ++i) dstats[blockIdx.x * 8 + i] = tp[i];
     }
   }
   ptx::tcgen05_fence_before();

@@ -37,6 +37,10 @@ enum GemmEpilogue : int {
   EPI_RESID_BF16 = 11, // out(bf16)   = aux(bf16) + acc (+ bias)
 };
 
+#ifndef PEFT_GEMM_DIAG
+#define PEFT_GEMM_DIAG 0      // 1: compile the in-kernel diagnostics of the 2-CTA GEMM (make DIAG=1); see gemm2_sm100.cuh
+#endif
+
 struct GemmParams {
   int M, N, K;
   const float* bias;  // [N] fp32 or nullptr
