@@ -182,6 +182,9 @@ static unsigned long long* attn_stats_buffer() {
   return buf;
 }
 extern "C" int peft_debug_attn_stats(unsigned long long* host_out, int n_ctas) {
+#if !PEFT_GEMM_DIAG
+  return fail(PEFT_ERR_INVALID, "peft_debug_attn_stats: the library was built without the in-kernel diagnostics (make DIAG=1)");
+#endif
   unsigned long long* buf = attn_stats_buffer();
   PEFT_REQUIRE(buf != nullptr, "peft_debug_attn_stats: set PEFT_ATTN_STATS=1 before the first attention call");
   PEFT_REQUIRE(host_out && n_ctas > 0 && n_ctas <= 512, "peft_debug_attn_stats: bad arguments");

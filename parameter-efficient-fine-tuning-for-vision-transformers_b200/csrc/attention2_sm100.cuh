@@ -196,6 +196,11 @@ __global__ void __launch_bounds__(kA2Threads, 1)
 attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                  const __grid_constant__ CUtensorMap tmap_o, const Attn2Params p) {
   using C = Attn2Cfg<NK>;
+#if PEFT_GEMM_DIAG        // phase counters only in the diagnostics build (make DIAG=1), see gemm2_sm100.cuh
+  unsigned long long* const dstats = p.stats;
+#else
+  constexpr unsigned long long* dstats = nullptr;
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sKV = smem;                                   // [2 heads][K | V]
@@ -372,7 +377,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const uint32_t tb = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + (uint32_t)(buf * C::kBufCols);
       ptx::mbar_wait(&s_ready[wg], (g >> 1) & 1);
       ptx::tcgen05_fence_after();
-      if (p.stats) lap(tS);
+      if (dstats) lap(tS);
       float mx = -INFINITY, sum = 0.f, mc = 0.f;
       if (warp_active) {
         uint32_t r[2][32];
@@ -401,7 +406,7 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           }
         }
         mc = mx * c;
-        if (p.stats) lap(tP1);
+        if (dstats) lap(tP1);
         // ---- pass 2: P = exp2(S c - m c) -> bf16 in place (ascending: writes only touch columns already consumed)
         tm_ld32(tb, r[0]);
 #pragma unroll
@@ -447,11 +452,11 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
       ptx::tcgen05_fence_before();
       ptx::mbar_arrive(&p_ready[wg]);
-      if (p.stats) lap(tP2);
+      if (dstats) lap(tP2);
       // ---- epilogue: O / rowsum -> bf16 -> staging -> TMA store
       ptx::mbar_wait(&o_ready[wg], (g >> 1) & 1);
       ptx::tcgen05_fence_after();
-      if (p.stats) lap(tO);
+      if (dstats) lap(tO);
       uint32_t o[64];
       if (warp_active) {
         tm_ld32(tb + C::kOOff, o);
@@ -481,11 +486,11 @@ attn2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         ptx::tma_store_3d(&tmap_o, stage, h * 64, t * 128, b);
         ptx::bulk_commit();
       }
-      if (p.stats) lap(tE);
+      if (dstats) lap(tE);
     }
     if (issuer) ptx::bulk_wait<0>();
-    if (p.stats && (cw & 3) == 0 && lane == 0) {
-      unsigned long long* o = p.stats + (blockIdx.x * 2 + wg) * 8;
+    if (dstats && (cw & 3) == 0 && lane == 0) {
+      unsigned long long* o = dstats + (blockIdx.x * 2 + wg) * 8;
       o[0] = tS; o[1] = tP1; o[2] = tP2; o[3] = tO; o[4] = tE; o[5] = clock64() - tbeg;
     }
   }

@@ -160,6 +160,13 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     const __grid_constant__ CUtensorMap tmap_do, const __grid_constant__ CUtensorMap tmap_o, const Attn3Params p) {
   using C = Attn3Cfg<NKT>;
   constexpr int NCH = C::kNCH, NB = C::kNBuf;
+#if PEFT_GEMM_DIAG        // cycle counters and the diagnostic A/B flags only in the diagnostics build (make DIAG=1)
+  unsigned long long* const dstats = p.stats;
+  const int dflags = p.flags;
+#else
+  constexpr unsigned long long* dstats = nullptr;
+  constexpr int dflags = 0;
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sKV = smem;                                          // [kDqKVBufs][K | V]
@@ -314,9 +321,9 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     auto advance = [&](int done) {
       while (next_ss < N && next_ss < done + NB && (next_ss / NCH - 2) * NCH + kRel + 1 <= done &&
              (next_ss / head_items - (C::kDqKVBufs - 1)) * head_items <= done) {      // K / V slot: head hl - kDqKVBufs is finished
-        if (p.stats) tc0 = clock64();
+        if (dstats) tc0 = clock64();
         issue_ss(next_ss);
-        if (p.stats) w_ss += clock64() - tc0;
+        if (dstats) w_ss += clock64() - tc0;
         ++next_ss;
       }
     };
@@ -325,11 +332,11 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const int g = i / NCH, kc = i % NCH;
       const int hl = g / TQ, t = g % TQ;
       const int kvb = hl % C::kDqKVBufs, qb = g & 1, a = g & 1;
-      if (p.stats) tc0 = clock64();
+      if (dstats) tc0 = clock64();
       ptx::mbar_wait(&ds_ready[i % NB], (i / NB) & 1);
-      if (p.stats) { const long long n_ = clock64(); w_ds += n_ - tc0; tc0 = n_; }
+      if (dstats) { const long long n_ = clock64(); w_ds += n_ - tc0; tc0 = n_; }
       if (kc == 0) ptx::mbar_wait(&dq_free[a], ((g >> 1) & 1) ^ 1);
-      if (p.stats) w_free += clock64() - tc0;
+      if (dstats) w_free += clock64() - tc0;
       ptx::tcgen05_fence_after();
       const uint32_t sk = sKV_u32 + kvb * 2 * C::kHeadBytes + kc * 64 * 128;
       const uint32_t tS = tmem_base + (uint32_t)((i % NB) * 128);
@@ -356,8 +363,8 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       __syncwarp();
       advance(i + 1);
     }
-    if (p.stats && lane == 0) {
-      unsigned long long* o = p.stats + blockIdx.x * 16;
+    if (dstats && lane == 0) {
+      unsigned long long* o = dstats + blockIdx.x * 16;
       o[0] = clock64() - tbeg; o[1] = w_ss; o[2] = w_ds; o[3] = w_free;
     }
   } else if (warp >= 4) {
@@ -369,7 +376,7 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     const uint32_t tb = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
     long long c_delta = 0, c_wait = 0, c_math = 0, c_epi = 0, tc0 = clock64();
     const long long tbeg = tc0;
-    auto lap = [&](long long& acc) { if (p.stats) { const long long n_ = clock64(); acc += n_ - tc0; tc0 = n_; } };
+    auto lap = [&](long long& acc) { if (dstats) { const long long n_ = clock64(); acc += n_ - tc0; tc0 = n_; } };
     int cur_g = -1;
     float delta = 0.f, lse = 0.f;
     for (int i = wg; i < N; i += 2) {
@@ -384,7 +391,7 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         cur_g = g;
         ptx::mbar_wait(&t_full[qb], (g >> 1) & 1);
         delta = 0.f; lse = 0.f;
-        if (warp_active && !(p.flags & 4)) {   // diagnostic bit 2: no delta (results wrong)
+        if (warp_active && !(dflags & 4)) {   // diagnostic bit 2: no delta (results wrong)
           const uint8_t* sdo = sT + qb * 3 * C::kTileBytes + C::kTileBytes;
           const uint8_t* so = sdo + C::kTileBytes;
 #pragma unroll
@@ -409,11 +416,11 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       ptx::mbar_wait(&sdp_ready[buf], (i / NB) & 1);
       ptx::tcgen05_fence_after();
       lap(c_wait);
-      if (warp_active && !(p.flags & 2)) {   // diagnostic bit 1: no math (results wrong)
+      if (warp_active && !(dflags & 2)) {   // diagnostic bit 1: no math (results wrong)
         const uint32_t tS = tb + (uint32_t)(buf * 128);
         const int valid = L - kc * 64;
         if (C::kWLast == 64 || kc != NCH - 1) {
-          if (p.flags & 1) {
+          if (dflags & 1) {
             dq_chunk<32>(tS, tS + 64, tS, valid, c, lse, delta);
             dq_chunk<32>(tS + 32, tS + 96, tS + 16, valid - 32, c, lse, delta);
           } else {
@@ -457,8 +464,8 @@ attn3_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         lap(c_epi);
       }
     }
-    if (p.stats && (warp & 3) == 0 && lane == 0) {
-      unsigned long long* o = p.stats + blockIdx.x * 16 + 4 + 6 * wg;
+    if (dstats && (warp & 3) == 0 && lane == 0) {
+      unsigned long long* o = dstats + blockIdx.x * 16 + 4 + 6 * wg;
       o[0] = clock64() - tbeg; o[1] = c_delta; o[2] = c_wait; o[3] = c_math; o[4] = c_epi;
     }
   }
@@ -477,6 +484,13 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
                      const __grid_constant__ CUtensorMap tmap_do, const Attn3Params p) {
   using C = Attn3Cfg<NKT>;
   constexpr int NCH = C::kNCH, NB = C::kNBuf;
+#if PEFT_GEMM_DIAG        // cycle counters and the diagnostic A/B flags only in the diagnostics build (make DIAG=1)
+  unsigned long long* const dstats = p.stats;
+  const int dflags = p.flags;
+#else
+  constexpr unsigned long long* dstats = nullptr;
+  constexpr int dflags = 0;
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQD = smem;                                          // [2 heads][Q | dO]   (all query rows of the head)
@@ -625,9 +639,9 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
     auto advance = [&](int done) {     // (a) TMEM buffer free, (b) K_j / V_j slot released, (c) Q / dO slot: head hl - 2 is finished
       while (next_ss < N && next_ss < done + NB && (next_ss / NCH - 2) * NCH + kRel + 1 <= done &&
              (next_ss / head_items - 1) * head_items <= done) {
-        if (p.stats) tc0 = clock64();
+        if (dstats) tc0 = clock64();
         issue_ss(next_ss);
-        if (p.stats) w_ss += clock64() - tc0;
+        if (dstats) w_ss += clock64() - tc0;
         ++next_ss;
       }
     };
@@ -636,11 +650,11 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
       const int g = i / NCH, qc = i % NCH;
       const int hl = g / TK, j = g % TK;
       const int qdb = hl & 1, kb = g & 1;
-      if (p.stats) tc0 = clock64();
+      if (dstats) tc0 = clock64();
       ptx::mbar_wait(&pds_ready[i % NB], (i / NB) & 1);
-      if (p.stats) { const long long n_ = clock64(); w_ds += n_ - tc0; tc0 = n_; }
+      if (dstats) { const long long n_ = clock64(); w_ds += n_ - tc0; tc0 = n_; }
       if (qc == 0) ptx::mbar_wait(out_free, (g & 1) ^ 1);     // the previous tile's dK / dV accumulators have been read out
-      if (p.stats) w_free += clock64() - tc0;
+      if (dstats) w_free += clock64() - tc0;
       ptx::tcgen05_fence_after();
       const uint32_t sq = sQD_u32 + qdb * 2 * C::kHeadBytes + qc * 64 * 128;
       const uint32_t sdo = sq + C::kHeadBytes;
@@ -671,8 +685,8 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
       __syncwarp();
       advance(i + 1);
     }
-    if (p.stats && lane == 0) {
-      unsigned long long* o = p.stats + (256 + blockIdx.x) * 16;
+    if (dstats && lane == 0) {
+      unsigned long long* o = dstats + (256 + blockIdx.x) * 16;
       o[0] = clock64() - tbeg; o[1] = w_ss; o[2] = w_ds; o[3] = w_free;
     }
   } else if (warp >= 4) {
@@ -686,7 +700,7 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
     float* sDelta = sLse + NKT;
     long long c_delta = 0, c_wait = 0, c_math = 0, c_epi = 0, tc0 = clock64();
     const long long tbeg = tc0;
-    auto lap = [&](long long& acc) { if (p.stats) { const long long n_ = clock64(); acc += n_ - tc0; tc0 = n_; } };
+    auto lap = [&](long long& acc) { if (dstats) { const long long n_ = clock64(); acc += n_ - tc0; tc0 = n_; } };
     int cur_hl = -1;
     // lse / delta of the NEXT head this warpgroup will meet travel in registers (fetched one head ahead, so their DRAM latency
     // is never exposed): thread rit holds queries rit, rit + 128, rit + 256
@@ -728,12 +742,12 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
       ptx::mbar_wait(&sdp_ready[buf], (i / NB) & 1);
       ptx::tcgen05_fence_after();
       lap(c_wait);
-      if (warp_active && !(p.flags & 2)) {
+      if (warp_active && !(dflags & 2)) {
         const uint32_t tS = tb + (uint32_t)(buf * 128);
         const int qbase = qc * 64;
         const int valid = L - qbase;
         if (C::kWLast == 64 || qc != NCH - 1) {
-          if (p.flags & 1) {
+          if (dflags & 1) {
             a3_dkv_chunk<32>(tS, tS + 64, tS, tS + 64, valid, c, sLse + qbase, sDelta + qbase);
             a3_dkv_chunk<32>(tS + 32, tS + 96, tS + 16, tS + 80, valid - 32, c, sLse + qbase + 32, sDelta + qbase + 32);
           } else {
@@ -778,8 +792,8 @@ attn3_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_kt, const __grid_c
         lap(c_epi);
       }
     }
-    if (p.stats && (warp & 3) == 0 && lane == 0) {
-      unsigned long long* o = p.stats + (256 + blockIdx.x) * 16 + 4 + 6 * wg;
+    if (dstats && (warp & 3) == 0 && lane == 0) {
+      unsigned long long* o = dstats + (256 + blockIdx.x) * 16 + 4 + 6 * wg;
       o[0] = clock64() - tbeg; o[1] = c_delta; o[2] = c_wait; o[3] = c_math; o[4] = c_epi;
     }
   }
