@@ -56,6 +56,9 @@ int peft_set_pdl(int enabled);
  * on 74 SM pairs at M = 6304): 0 = off, 1 = automatic (default), 2 = whenever the shape allows it (tests).  Partial tiles
  * travel through ONE per-device workspace, so stream-K products of one device must be issued on one stream at a time. */
 int peft_set_gemm_streamk(int mode);
+/* The in-kernel diagnostics behind the next two calls (and the PEFT_GEMM_DBG / PEFT_ATTN3_FLAGS modes) exist only in a library built
+ * with `make DIAG=1` (-DPEFT_GEMM_DIAG=1); the production build compiles them out — they cost 14 % of the GEMM kernel's code and
+ * measurably lengthen short launches — and the two calls then fail with a message. */
 /* diagnostics (tests/bench_ops.py gemm_stats): with PEFT_GEMM_STATS=1 in the environment the 2-CTA GEMM records, per CTA,
  * the cycles its TMA producer, MMA issuer and first epilogue warp spent waiting on their mbarriers during the LAST launch:
  * host_out[cta*8 + {0: producer wait-empty, 1: producer total, 2: issuer wait-full, 3: issuer wait-tmem-empty, 4: issuer

@@ -1,5 +1,8 @@
 """Micro-benchmarks (not a test): CUDA-event timing of individual C-ABI ops at the headline shapes.
 
+The *_stats / *_phases / gemm_dbg entries read in-kernel counters that exist only in a diagnostics build of the library:
+`make -C <package>/csrc clean && make -C <package>/csrc DIAG=1` (the production build compiles them out).
+
     python tests/bench_ops.py attn|ln|reduce|all
 """
 import os
