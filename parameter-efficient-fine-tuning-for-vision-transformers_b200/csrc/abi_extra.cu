@@ -108,7 +108,12 @@ extern "C" int peft_colsum_bf16(const void* in, long long ldin, int rows, int co
   PEFT_REQUIRE(rows > 0 && cols > 0 && in && colsum, "peft_colsum_bf16: bad shape rows=%d cols=%d or null operand", rows, cols);
   PEFT_REQUIRE(al16(in) && ldin % 8 == 0 && ldin >= cols, "peft_colsum_bf16: needs a 16-byte aligned operand and pitch %% 8 == 0");
   const int colblocks = (cols + 255) / 256, nrb = (rows + 63) / 64;
-  int gy = (2 * sm_count() + colblocks - 1) / colblocks;       // ~2 CTAs per SM in total; each walks nrb / gy row blocks
+  // ~4 CTAs per SM in total, each walking nrb / gy row blocks, but at most 100 CTAs (= same-address atomics) per column block.
+  // Measured r02 at 12 800 rows (graph replay): 768 columns 10.9 us (2 / SM, gy = 99) vs 17.6 us (4 / SM, gy = 198); 2304 columns
+  // 13.8 -> 10.7 us and 3072 columns 19.7 -> 12.4 us going from 2 to 4 CTAs per SM; 8 and 16 per SM are slower again.
+  static const int per_sm = [] { const char* e = getenv("PEFT_COLSUM_CTAS"); return (e && atoi(e) > 0) ? atoi(e) : 4; }();
+  int gy = (per_sm * sm_count() + colblocks - 1) / colblocks;
+  if (gy > 100) gy = 100;
   if (gy > nrb) gy = nrb;
   if (gy < 1) gy = 1;
   (void)launch_pdl(PDL_MISC, colsum_bf16_kernel, dim3(dim3(colblocks, gy)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), (const __nv_bfloat16*)in, ldin, rows,
