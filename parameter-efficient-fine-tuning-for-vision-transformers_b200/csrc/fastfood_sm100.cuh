@@ -354,8 +354,12 @@ __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
   const int2 it = a.items[s_ticket];
   const peft_ff_tensor t = a.tensors[it.x];
   const int tid = threadIdx.x;
-  const int tile = it.y & 0x3fffffff;
   const bool high = (it.y >> 30) != 0;
+  // a high item is a RUN of consecutive tiles of one tensor (count - 1 in bits 20..27): they are folded into the same shared-memory
+  // bins, so a bin gets one global atomic per run instead of one per tile (the wn bins of a tensor are shared by all its tiles —
+  // 512 for an fc1 weight — and same-address atomics serialise in L2)
+  const int tile = high ? (it.y & 0xfffff) : (it.y & 0x3fffffff);
+  const int ntile = high ? ((it.y >> 20) & 0xff) + 1 : 1;
   const uint16_t* pi = a.pi_lo + t.off_ll;
   const float* gg = a.gg + t.off_ll;
   float* scr = a.scratch + t.off_ll;
@@ -393,7 +397,9 @@ __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
     return;
   }
   const int lc = 2 * kFfTileBits - t.ll;
-  const int tc = ff_hi_tconst(tid, lc) + (tile << lc);
+#pragma unroll 1
+  for (int q = 0; q < ntile; ++q) {
+  const int tc = ff_hi_tconst(tid, lc) + ((tile + q) << lc);
   uint16_t pv[16];
   float gv[16];
 #pragma unroll
@@ -402,7 +408,8 @@ __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
     pv[i] = pi[j];
     gv[i] = gg[j];
   }
-  ff_wait(a.counters + it.x, nblk);
+  if (q == 0) ff_wait(a.counters + it.x, nblk);
+  else __syncthreads();                                  // the previous tile's transform is done with the shared tile
   if (lc < 9) {
     const int S = 1 << (22 - lc), r0 = tc >> kFfTileBits, rs = S >> kFfTileBits;
     const float* p = scr + tc;
@@ -419,6 +426,7 @@ __global__ void __launch_bounds__(kFfThreads, 3) ff_bwd_kernel(FfArgs a) {
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < 16; ++i) atomicAdd(&bins[pv[i]], x[i] * gv[i]);
+  }
   __syncthreads();
   for (int k = tid; k < a.wn; k += kFfThreads) atomicAdd(&u[k], bins[k]);
 }

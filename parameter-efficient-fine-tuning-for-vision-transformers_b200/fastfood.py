@@ -13,6 +13,7 @@ Layout in HBM (ViT-B/32 visual tower: 152 tensors, sum DD = 87.8 M, sum LL = 143
 from __future__ import annotations
 
 import math
+import os
 
 import numpy as np
 import torch
@@ -37,6 +38,9 @@ def fastfood_vars(DD, device="cpu"):
     GG = torch.empty(LL, dtype=torch.float32).normal_()
     divisor = torch.sqrt(LL * torch.sum(torch.pow(GG, 2)))
     return [BB, Pi, GG, divisor, LL]
+
+
+_BWD_GROUP = max(1, min(256, int(os.environ.get("PEFT_FF_BWD_GROUP", "4"))))   # tiles per backward high item
 
 
 def _schedule(phases, lag=_LAG):
@@ -97,7 +101,12 @@ class FastfoodPlan:
             hi = [(t, k | (1 << 30)) for k in range(LL // _TILE)] if ll > 13 else []
             lo = [(t, k) for k in range((DD + _TILE - 1) // _TILE)]
             fwd_ph.append((hi, lo) if hi else (lo, []))   # forward: high tiles, then the low blocks that wait for them
-            bwd_ph.append((lo, hi) if hi else (lo, []))   # backward: the other way round
+            # backward: the other way round; its high items are RUNS of `grp` consecutive tiles (count - 1 in bits 20..27) that
+            # share one set of bins and one round of global atomics (csrc/fastfood_sm100.cuh: ff_bwd_kernel)
+            grp = _BWD_GROUP
+            nt = LL // _TILE
+            hi_b = [(t, k | ((min(grp, nt - k) - 1) << 20) | (1 << 30)) for k in range(0, nt, grp)] if ll > 13 else []
+            bwd_ph.append((lo, hi_b) if hi_b else (lo, []))
             self.offsets.append(off_dd)
             self.numels.append(DD)
             off_ll += LL + pad
@@ -111,7 +120,7 @@ class FastfoodPlan:
         self.gg = torch.cat(gg_parts).to(dev)
         self.bsign = bsign.to(dev)
         mk = lambda items: torch.tensor(items, dtype=torch.int32).reshape(-1, 2).contiguous().to(dev)
-        self.items_fwd, self.items_bwd, self.n_items = mk(fwd_items), mk(bwd_items), len(fwd_items)
+        self.items_fwd, self.items_bwd, self.n_items, self.n_items_bwd = mk(fwd_items), mk(bwd_items), len(fwd_items), len(bwd_items)
         self.counters = torch.zeros(T + 1, dtype=torch.int32, device=dev)      # per-tensor completion counters + the backward's item ticket
         self.scratch = torch.empty(off_ll, dtype=torch.float32, device=dev)
         self.wu = torch.zeros(T, self.wn, dtype=torch.float32, device=dev)
@@ -148,7 +157,7 @@ class FastfoodPlan:
         dV = torch.zeros(self.d, dtype=torch.float32, device=self.device)
         s = torch.cuda.current_stream().cuda_stream
         _lib.check(_lib.load().peft_fastfood_bwd(dtheta_flat.data_ptr(), self.d, self.wn, self.desc.data_ptr(), self.T,
-                                                 self.items_bwd.data_ptr(), self.n_items,
+                                                 self.items_bwd.data_ptr(), self.n_items_bwd,
                                                  self.pi_lo.data_ptr(), self.gg.data_ptr(), self.bsign.data_ptr(),
                                                  self.wu.data_ptr(), self.scratch.data_ptr(), self.counters.data_ptr(),
                                                  dV.data_ptr(), s), "peft_fastfood_bwd")
