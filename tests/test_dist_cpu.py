@@ -134,3 +134,26 @@ def test_fused_sgd_bucket_two_ranks_cpu():
     for p in procs:
         p.join(timeout=60)
     assert all(ok for _, ok in res), res
+
+
+def test_kind_major_order_and_stack_fallback():
+    """dist.kind_major: the same tensor of consecutive layers becomes adjacent, kinds in order of first appearance, layer order kept;
+    timm_vit.stack_params on CPU tensors (or any layout that is not stacked in memory) is plain torch.stack with ordinary
+    per-parameter gradients."""
+    import torch
+    from peft_b200 import timm_vit
+    from peft_b200.dist import kind_major
+    names = ["vit.blocks.0.attn.W_left1", "vit.blocks.0.attn.W_right1", "vit.blocks.1.attn.W_left1", "vit.blocks.1.attn.W_right1",
+             "vit.blocks.10.attn.W_left1", "vit.blocks.10.attn.W_right1", "layers.0.weight", "layers.0.bias", "vit.cls_token"]
+    named = [(n, torch.nn.Parameter(torch.full((2, 3), float(i)))) for i, n in enumerate(names)]
+    order = [names[[id(p) for _, p in named].index(id(q))] for q in kind_major(named)]
+    assert order == ["vit.blocks.0.attn.W_left1", "vit.blocks.1.attn.W_left1", "vit.blocks.10.attn.W_left1",
+                     "vit.blocks.0.attn.W_right1", "vit.blocks.1.attn.W_right1", "vit.blocks.10.attn.W_right1",
+                     "layers.0.weight", "layers.0.bias", "vit.cls_token"]
+    ps = [p for n, p in named if n.endswith("W_left1")]
+    hits = timm_vit.STACK_FAST_HITS
+    st = timm_vit.stack_params(ps)
+    assert timm_vit.STACK_FAST_HITS == hits and torch.equal(st, torch.stack(ps))
+    (st * torch.arange(3.0).reshape(3, 1, 1)).sum().backward()
+    for i, p in enumerate(ps):
+        assert torch.equal(p.grad, torch.full((2, 3), float(i)))
