@@ -195,6 +195,19 @@ int peft_transpose_colsum_bf16(const void* in, long long ldin, int rows, int col
  *   backward == 1:  out[p, i] = sum_j dH[p, j] * rule[i, j]     dH [2, n*n],      out = ds [2, n]      (rule is frozen) */
 int peft_phm_fold(const float* rule, const float* s_or_dH, float* out, int n, int backward, void* stream);
 
+/* Small-n KAdaptation: the reshape-trick operands of ALL layers in one launch per direction (csrc/factors_sm100.cuh).
+ * replaces: the stack / einsum / eye / zeros / cat chain (and its autograd) that builds, from the reference-named parameters
+ * phm_rule A [dep,n,n,n] (frozen), W_left{1,2} u^s [dep,n,K,r], W_right{1,2} v^s [dep,n,r,P] (FS/kadaptation.py:81-115,143-187),
+ *   Dn  [dep, 2nrn, nK]:  Dn[l,(s,i,r,c),(a,k)] = A_i[a,c] u^s_i[k,r]      UpT [dep, 2nrn, 3nP]: UpT[l,(s,i,r,c),(slot_s,c,p)] = v^s_i[r,p]
+ * (s = 0: q, column slot 0; s = 1: v, column slot 2; zero elsewhere).
+ *   backward == 0: a..d = wl1, wr1, wl2, wr2 (read), out0 = Dn, out1 = UpT (written)
+ *   backward != 0: out0 = dDn, out1 = dUpT (read), a..d = dW_left1, dW_right1, dW_left2, dW_right2 (written, not accumulated) */
+int peft_kron_factors(const float* rule, float* a, float* b, float* c, float* d, float* out0, float* out1, int dep, int n, int K,
+                      int r, int P, int backward, void* stream);
+/* ... and the gradient of a trainable phm_rule: drule[l,i,a,c] = sum_{s,r,k} W_left{s}[l,i,k,r] dDn[l,(s,i,r,c),(a,k)] (written). */
+int peft_kron_factors_drule(const float* dDn, const float* wl1, const float* wl2, float* drule, int dep, int n, int K, int r,
+                            void* stream);
+
 /* Fastfood intrinsic-dimension projection over a SET of wrapped parameter tensors in one call.
  * replaces: FastfoodWrap.forward / fastfood_torched / fast_walsh_hadamard_torched and their autograd backward —
  * FL/intrinsic/fastfood.py:61-77,81-121,151-187.

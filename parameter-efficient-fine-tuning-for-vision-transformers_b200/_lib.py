@@ -48,6 +48,8 @@ SIGNATURES = {
     "peft_transpose_bf16": [_vp, _c_ll, C.c_int, C.c_int, _vp, _c_ll, _vp],
     "peft_transpose_colsum_bf16": [_vp, _c_ll, C.c_int, C.c_int, _vp, _c_ll, _vp, _vp],
     "peft_phm_fold": [_vp, _vp, _vp, C.c_int, C.c_int, _vp],
+    "peft_kron_factors": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp],
+    "peft_kron_factors_drule": [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp],
     "peft_fastfood_fwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "peft_fastfood_bwd": [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "peft_allreduce_sgd": [_vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _c_ll, _vp, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, _vp],

@@ -5,6 +5,7 @@
 #include "fastfood_sm100.cuh"
 #include "allreduce_sgd_sm100.cuh"
 #include "preprocess_sm100.cuh"
+#include "factors_sm100.cuh"
 
 using namespace peft;
 
@@ -215,6 +216,36 @@ extern "C" int peft_preprocess_clip(const uint8_t* img, int H, int W, const int*
   pp_horizontal_kernel<<<(unsigned)b1, 256, 0, s>>>(img, W, hb, hk, hksize, left, n, r0, r1, tmp);
   PEFT_LAUNCH_CHECK();
   pp_vertical_kernel<<<(unsigned)b2, 256, 0, s>>>(tmp, vb, vk, vksize, top, n, r0, mean, stdv, out);
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+
+// Reshape-trick operands of the small-n KAdaptation update for all layers (factors_sm100.cuh).  backward == 0: a = wl1, b = wr1,
+// c = wl2, d = wr2 (inputs), out0 = Dn, out1 = UpT;  backward != 0: out0 = dDn, out1 = dUpT (inputs), a..d = the four gradients.
+extern "C" int peft_kron_factors(const float* rule, float* a, float* b, float* c, float* d, float* out0, float* out1, int dep, int n,
+                                 int K, int r, int P, int backward, void* stream) {
+  PEFT_REQUIRE(dep > 0 && n > 0 && K > 0 && r > 0 && P > 0, "peft_kron_factors: bad shape dep=%d n=%d K=%d r=%d P=%d", dep, n, K, r, P);
+  PEFT_REQUIRE(rule && a && b && c && d && out0 && out1, "peft_kron_factors: null operand");
+  PEFT_REQUIRE(dep <= 65535 && 2ll * n * r * n <= 2147483647ll, "peft_kron_factors: too many layers / rows");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (!backward) {
+    kron_factors_fwd_kernel<<<dim3(2 * n * r * n, dep), 256, 0, s>>>(rule, a, b, c, d, out0, out1, n, K, r, P);
+  } else {
+    const long long total = 2ll * dep * n * K * r + 2ll * dep * n * r * P;
+    kron_factors_bwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(rule, out0, out1, a, b, c, d, dep, n, K, r, P);
+  }
+  PEFT_LAUNCH_CHECK();
+  return 0;
+}
+
+// gradient of a trainable phm_rule [dep,n,n,n] from dDn and the two left factors (written, not accumulated)
+extern "C" int peft_kron_factors_drule(const float* dDn, const float* wl1, const float* wl2, float* drule, int dep, int n, int K, int r,
+                                       void* stream) {
+  PEFT_REQUIRE(dep > 0 && n > 0 && K > 0 && r > 0 && dDn && wl1 && wl2 && drule, "peft_kron_factors_drule: bad shape or null operand");
+  const long long warps = (long long)dep * n * n * n;
+  kron_factors_drule_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(dDn, wl1, wl2, drule,
+                                                                                                                    dep, n, K, r);
   PEFT_LAUNCH_CHECK();
   return 0;
 }

@@ -283,11 +283,70 @@ def stack_params(params):
     return _StackParams.apply(pview, gview, *params)
 
 
+class _KronFactors(torch.autograd.Function):
+    """(phm_rule [dep,n,n,n], W_left1, W_right1, W_left2, W_right2 stacked over the layers) -> (Dn, UpT) through
+    peft_kron_factors: one launch per direction instead of ~40 tiny ATen launches (csrc/factors_sm100.cuh)."""
+
+    @staticmethod
+    def forward(ctx, rule, wl1, wr1, wl2, wr2):
+        from . import _lib
+        dep, n, K, r = wl1.shape
+        P = wr1.shape[3]
+        rule, wl1, wr1, wl2, wr2 = (t.detach().contiguous() for t in (rule, wl1, wr1, wl2, wr2))
+        Dn = torch.empty(dep, 2 * n * r * n, n * K, device=wl1.device, dtype=torch.float32)
+        UpT = torch.empty(dep, 2 * n * r * n, 3 * n * P, device=wl1.device, dtype=torch.float32)
+        _lib.check(_lib.load().peft_kron_factors(rule.data_ptr(), wl1.data_ptr(), wr1.data_ptr(), wl2.data_ptr(), wr2.data_ptr(),
+                                                 Dn.data_ptr(), UpT.data_ptr(), dep, n, K, r, P, 0,
+                                                 torch.cuda.current_stream().cuda_stream), "peft_kron_factors")
+        ctx.save_for_backward(rule, wl1, wl2)
+        ctx.dims = (dep, n, K, r, P)
+        return Dn, UpT
+
+    @staticmethod
+    def backward(ctx, dDn, dUpT):
+        from . import _lib
+        rule, wl1, wl2 = ctx.saved_tensors
+        dep, n, K, r, P = ctx.dims
+        dDn, dUpT = dDn.contiguous(), dUpT.contiguous()
+        gl1, gl2 = (torch.empty(dep, n, K, r, device=rule.device, dtype=torch.float32) for _ in range(2))
+        gr1, gr2 = (torch.empty(dep, n, r, P, device=rule.device, dtype=torch.float32) for _ in range(2))
+        _lib.check(_lib.load().peft_kron_factors(rule.data_ptr(), gl1.data_ptr(), gr1.data_ptr(), gl2.data_ptr(), gr2.data_ptr(),
+                                                 dDn.data_ptr(), dUpT.data_ptr(), dep, n, K, r, P, 1,
+                                                 torch.cuda.current_stream().cuda_stream), "peft_kron_factors")
+        grule = None
+        if ctx.needs_input_grad[0]:
+            grule = torch.empty_like(rule)
+            _lib.check(_lib.load().peft_kron_factors_drule(dDn.data_ptr(), wl1.data_ptr(), wl2.data_ptr(), grule.data_ptr(), dep, n, K, r,
+                                                           torch.cuda.current_stream().cuda_stream), "peft_kron_factors_drule")
+        return grule, gl1, gr1, gl2, gr2
+
+
+_RULE_CACHE = {}     # id(first rule) -> (versions, stacked frozen phm_rule): the rule is frozen, stack it once
+
+
+def _stack_frozen(ts):
+    if torch.cuda.is_current_stream_capturing():      # a tensor allocated during graph capture must not outlive / precede its graph
+        return torch.stack([t.detach() for t in ts])
+    key = tuple((t.data_ptr(), t._version) for t in ts)
+    hit = _RULE_CACHE.get(id(ts[0]))
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    st = torch.stack([t.detach() for t in ts])
+    _RULE_CACHE[id(ts[0])] = (key, st)
+    return st
+
+
 def lowrank_operands(attns, kind):
     """Dn [depth, r', D], UpT [depth, r', 3D] from the attention modules' reference-named adapter parameters
     (`phm_rule / W_left{1,2} / W_right{1,2}` or `{q,v}_proj_adapter{1,2}.weight`); shared by both dialects."""
     if kind == "kron" and kron_is_dense(attns[0]):
         return dense_kron_operands(attns)
+    if kind == "kron" and attns[0].phm_rule.is_cuda and attns[0].phm_rule.dtype == torch.float32:
+        # both operands of every layer from one kernel per direction (csrc/factors_sm100.cuh)
+        rules = [a.phm_rule for a in attns]
+        return _KronFactors.apply(stack_params(rules) if any(t.requires_grad for t in rules) else _stack_frozen(rules),
+                                  stack_params([a.W_left1 for a in attns]), stack_params([a.W_right1 for a in attns]),
+                                  stack_params([a.W_left2 for a in attns]), stack_params([a.W_right2 for a in attns]))
     if kind == "kron":
         rule = torch.stack([a.phm_rule for a in attns])
         dq, uq = lowrank_factors_kron(rule, stack_params([a.W_left1 for a in attns]), stack_params([a.W_right1 for a in attns]))

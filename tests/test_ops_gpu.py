@@ -225,6 +225,32 @@ def test_tn_reduce(ops, M, I, J):
     assert rel(out, 2 * ref) < 1e-4
 
 
+@pytest.mark.parametrize("dep,n,K,r", [(12, 4, 192, 1), (3, 8, 96, 2), (2, 4, 16, 3)])
+def test_kron_factors_kernel_matches_aten_chain(dep, n, K, r):
+    """peft_kron_factors (all layers' reshape-trick operands in one launch per direction) against the ATen chain it replaces
+    (timm_vit.lowrank_factors_kron + cat, FS/kadaptation.py:81-115): operands bit-identical (each element is one product), the four
+    parameter gradients to fp32 summation order."""
+    from peft_b200 import timm_vit
+    P = K
+    g = torch.Generator(device="cuda").manual_seed(11)
+    rnd = lambda *sh: torch.randn(*sh, device="cuda", generator=g)
+    ws = [rnd(dep, n, n, n), rnd(dep, n, K, r), rnd(dep, n, r, P), rnd(dep, n, K, r), rnd(dep, n, r, P)]     # rule first: trainable too
+    a = [w.clone().requires_grad_(True) for w in ws]
+    b = [w.clone().requires_grad_(True) for w in ws]
+    Dn, UpT = timm_vit._KronFactors.apply(*a)
+    dq, uq = timm_vit.lowrank_factors_kron(b[0], b[1], b[2])
+    dv, uv = timm_vit.lowrank_factors_kron(b[0], b[3], b[4])
+    z = torch.zeros_like(uq)
+    Dn_ref = torch.cat([dq, dv], dim=1)
+    UpT_ref = torch.cat([torch.cat([uq, z, z], dim=2), torch.cat([z, z, uv], dim=2)], dim=1)
+    assert torch.equal(Dn, Dn_ref) and torch.equal(UpT, UpT_ref)
+    gD, gU = rnd(*Dn.shape), rnd(*UpT.shape)
+    torch.autograd.backward([Dn, UpT], [gD, gU])
+    torch.autograd.backward([Dn_ref, UpT_ref], [gD, gU])
+    for x, y in zip(a, b):
+        assert rel(x.grad, y.grad) < 1e-6
+
+
 def test_patch_embed_pieces(ops):
     B, S, p, D = 3, 64, 16, 768
     img = _r(B, 3, S, S, seed=1)
